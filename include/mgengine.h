@@ -1,0 +1,136 @@
+/*
+ * mgengine.h -- C ABI of the B200-native multigrid cycle engine.
+ *
+ * This is the only native boundary of the system.  It replaces, for one evolved
+ * solver, everything the reference does *below* ProgramGenerator.generate_and_evaluate
+ * (/root/reference/evostencils/code_generation/exastencils.py:485-537): ExaSlang
+ * emission (:318-336, :684-925), the two ExaStencils compiler runs (:381-409, :495-503),
+ * `make` (:411-415) and the runs of the generated binary whose stdout is parsed
+ * (:417-443, :539-584).  The reference has no FFI for this path (it shells out to
+ * java / make / ./exastencils); the entry points below are what a binding for the path
+ * needs: set up the level hierarchy and operators once per problem, hand over one
+ * lowered op list per individual, solve, read back the residual history.
+ *
+ * Conventions
+ *   - every function returns 0 on success and a negative mg_status on failure; nothing
+ *     throws across the boundary; mg_last_error() returns a thread-local message;
+ *   - plain pointers and sizes only; host arrays are dense, row-major
+ *     [i_{d-1}]...[i1][i0] with n = 2^level + 1 nodes per dimension
+ *     (exastencils.py:97-103), complex values as interleaved (re, im) doubles;
+ *   - arrays passed in are borrowed for the duration of the call;
+ *   - one workspace is bound to one CUDA device and one stream; calls on the same
+ *     workspace must be serialised by the caller (the reference evaluates individuals
+ *     strictly sequentially per generator, optimization/program.py:491, 577).
+ */
+#ifndef MGENGINE_H
+#define MGENGINE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mg_workspace mg_workspace;
+
+typedef enum {
+    MG_OK = 0,
+    MG_ERR_INVALID = -1,      /* bad argument / unsupported construct */
+    MG_ERR_CUDA = -2,         /* a CUDA runtime call failed */
+    MG_ERR_STATE = -3,        /* call sequence violated (e.g. operator missing) */
+    MG_ERR_NOMEM = -4
+} mg_status;
+
+typedef enum { MG_F64 = 0, MG_C128 = 1 } mg_dtype;
+
+/* field kinds of one level's storage (CycleStorage, exastencils.py:14-26) */
+typedef enum { MG_SOL = 0, MG_RHS = 1, MG_RES = 2, MG_COR = 3 } mg_field;
+
+/* boundary treatment of solution-type fields */
+typedef enum {
+    MG_BC_DIRICHLET = 0,        /* boundary nodes are never written */
+    MG_BC_HELMHOLTZ_ROBIN = 1   /* x-boundaries slaved: u_0 = u_1 / (1 - i k h); y-boundaries 0
+                                   (Helmholtz/2D_FD_Helmholtz_fromL3.exa4:25-59) */
+} mg_bc;
+
+typedef enum { MG_CGS_CG = 0, MG_CGS_BICGSTAB = 1 } mg_cgs_kind;
+
+/* op kinds: the statement vocabulary generate_multigrid emits (exastencils.py:684-925) */
+typedef enum {
+    MG_OP_SMOOTH = 0,             /* solve locally ... relax w         (:769-822)  */
+    MG_OP_RESIDUAL = 1,           /* res = rhs - A*sol                  (:827-853)  */
+    MG_OP_RESTRICT = 2,           /* rhs@level = R * src@(level+1)      (:855-873)  */
+    MG_OP_RESIDUAL_RESTRICT = 3,  /* fused 1+2, residual field not stored            */
+    MG_OP_ZERO = 4,               /* sol@level = 0                      (:706-709)  */
+    MG_OP_PROLONG_ADD = 5,        /* sol@level += w * P * src@(level-1) (:727-743)  */
+    MG_OP_PROLONG = 6,            /* cor@level = P * src@(level-1)      (:855-873)  */
+    MG_OP_CGS = 7                 /* coarse-grid solve on min_level     (:874-911)  */
+} mg_op_kind;
+
+typedef struct {
+    int32_t kind;        /* mg_op_kind */
+    int32_t level;       /* level of the field that is written */
+    double  omega;       /* relaxation factor (SMOOTH uses the one baked into its W table) */
+    int32_t src;         /* mg_field read by RESTRICT / PROLONG* */
+    int32_t smoother;    /* SMOOTH: handle returned by mg_add_smoother */
+} mg_op;
+
+/* ---- lifetime ------------------------------------------------------------------------ */
+int mg_create(mg_workspace** out, int dimension, int min_level, int max_level, int n_fields,
+              int dtype, int device);
+int mg_destroy(mg_workspace* ws);
+const char* mg_last_error(void);
+/* number of kernels launched (directly or through graph replays) since creation */
+int mg_launch_count(mg_workspace* ws, int64_t* out);
+
+/* ---- problem definition (once per problem / level range) ------------------------------ */
+/* Constant stencil of block (row, col) on `level`; offsets[n][dimension] with component 0
+ * = x; values[n] (or [n][2] for MG_C128), in the accumulation order to be used. */
+int mg_set_operator(mg_workspace* ws, int level, int row, int col, int n_entries,
+                    const int32_t* offsets, const double* values);
+int mg_set_boundary(mg_workspace* ws, int bc_kind, double k);
+int mg_set_coarse_solver(mg_workspace* ws, int kind, int max_iterations, double reduction);
+
+/* One `solve locally` statement shape.  period[d] = tile shape (1 = point smoother);
+ * slots = unknowns of the local system (field, position in tile); the table holds
+ * W = omega * inv(L) for every validity mask of the slots that occurs
+ * (bit s of mask set <=> slot s is an interior node): w_table[n_masks][n_slots][n_slots]
+ * doubles (x2 for complex), row-major.  jacobi != 0: values are read from the old
+ * iterate; colored != 0: red-black, colour (sum i_d) % 2 == 0 first. */
+int mg_add_smoother(mg_workspace* ws, int level, int jacobi, int colored, const int32_t* period,
+                    int n_slots, const int32_t* slot_field, const int32_t* slot_pos,
+                    int n_masks, const uint32_t* masks, const double* w_table, int* handle);
+int mg_clear_smoothers(mg_workspace* ws);
+
+/* ---- data ------------------------------------------------------------------------------ */
+int mg_upload(mg_workspace* ws, int field_kind, int level, int field, const void* host);
+int mg_download(mg_workspace* ws, int field_kind, int level, int field, void* host);
+/* copy of device-resident dense data (same layout as the host arrays) */
+int mg_upload_device(mg_workspace* ws, int field_kind, int level, int field, const void* device_ptr);
+/* remember / restore the finest-level solution (initial guess for repeated samples) */
+int mg_save_initial_guess(mg_workspace* ws);
+int mg_restore_initial_guess(mg_workspace* ws);
+
+/* ---- execution ------------------------------------------------------------------------- */
+/* run ops immediately on the workspace stream (no graph); used by the parity tests */
+int mg_exec_ops(mg_workspace* ws, const mg_op* ops, int n_ops);
+/* capture the op list (plus the fused residual-norm of the finest level) as a CUDA graph */
+int mg_build_cycle(mg_workspace* ws, const mg_op* ops, int n_ops, int* cycle);
+int mg_free_cycles(mg_workspace* ws);
+/* replay `n_cycles` cycles without convergence checks (throughput measurements) */
+int mg_run_cycles(mg_workspace* ws, int cycle, int n_cycles, float* ms);
+/* sqrt(sum over interior nodes and fields of (rhs - A sol)^2) on `level` */
+int mg_residual_norm(mg_workspace* ws, int level, double* out);
+/* outer iteration of the generated solver: res_hist[0] = initial residual norm, then one
+ * cycle + norm per iteration until norm < tol * res_hist[0] (strict), a non-finite norm, or
+ * max_its.  *n_its = iterations done; *converged = 1 iff the tolerance was met.
+ * res_hist must hold max_its + 1 doubles.  *ms = device time of the solve phase. */
+int mg_solve(mg_workspace* ws, int cycle, double tol, int max_its, double* res_hist,
+             int* n_its, int* converged, float* ms);
+int mg_synchronize(mg_workspace* ws);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MGENGINE_H */
