@@ -1,0 +1,75 @@
+// mg_common.cuh -- shared types of the B200 multigrid engine (sm_100a only).
+//
+// Numerical contract: every kernel evaluates stencils in the entry order it
+// is given, with separate multiply and add -- this translation unit is compiled with
+// --fmad=false so that results are bit-identical to the numpy oracle for real fp64.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define MG_MAX_DIM 3
+#define MG_MAX_FIELDS 2
+#define MG_MAX_ENTRIES 27          // full 3x3x3 stencil
+#define MG_MAX_SLOTS 8             // maximum_local_system_size (optimization/program.py:774)
+
+namespace mg {
+
+struct cplx {
+    double re, im;
+};
+
+__host__ __device__ inline cplx make_cplx(double a, double b) { cplx c; c.re = a; c.im = b; return c; }
+
+// ---- arithmetic traits: T = double or cplx ------------------------------------------------
+__host__ __device__ inline double t_zero(double) { return 0.0; }
+__host__ __device__ inline cplx t_zero(cplx) { return make_cplx(0.0, 0.0); }
+__host__ __device__ inline double t_add(double a, double b) { return a + b; }
+__host__ __device__ inline cplx t_add(cplx a, cplx b) { return make_cplx(a.re + b.re, a.im + b.im); }
+__host__ __device__ inline double t_sub(double a, double b) { return a - b; }
+__host__ __device__ inline cplx t_sub(cplx a, cplx b) { return make_cplx(a.re - b.re, a.im - b.im); }
+__host__ __device__ inline double t_mul(double a, double b) { return a * b; }
+__host__ __device__ inline cplx t_mul(cplx a, cplx b) {
+    return make_cplx(a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re);
+}
+__host__ __device__ inline double t_scale(double s, double a) { return s * a; }
+__host__ __device__ inline cplx t_scale(double s, cplx a) { return make_cplx(s * a.re, s * a.im); }
+__host__ __device__ inline cplx t_div(cplx a, cplx b) {
+    double d = b.re * b.re + b.im * b.im;
+    return make_cplx((a.re * b.re + a.im * b.im) / d, (a.im * b.re - a.re * b.im) / d);
+}
+__host__ __device__ inline double t_div(double a, double b) { return a / b; }
+
+// ---- geometry of one level -------------------------------------------------------------------
+struct Geom {
+    int dim;
+    int n;                 // nodes per dimension = 2^level + 1
+    int pitch;             // elements per x-row (n rounded up to 16)
+    long long plane;       // pitch * n (3D) ; total elements = plane * n (3D) or pitch * n (2D)
+    long long total;       // allocated elements of one field array
+};
+
+// Block operator of one level: F x F constant stencils, linear element offsets precomputed.
+template <typename T>
+struct OperatorTable {
+    int n_entries[MG_MAX_FIELDS][MG_MAX_FIELDS];
+    int off[MG_MAX_FIELDS][MG_MAX_FIELDS][MG_MAX_ENTRIES];     // linear offset in elements
+    T val[MG_MAX_FIELDS][MG_MAX_FIELDS][MG_MAX_ENTRIES];
+};
+
+// One `solve locally` statement.
+template <typename T>
+struct SmootherTable {
+    int n_slots;
+    int period[MG_MAX_DIM];
+    int slot_field[MG_MAX_SLOTS];
+    int slot_pos[MG_MAX_SLOTS][MG_MAX_DIM];
+    int mask_index[1 << MG_MAX_SLOTS];      // validity mask -> index into w (or -1)
+    // w[k][s][t] follows in device memory (n_masks * n_slots * n_slots values of T)
+};
+
+template <typename T>
+struct FieldSet {
+    T* p[MG_MAX_FIELDS];
+};
+
+}  // namespace mg

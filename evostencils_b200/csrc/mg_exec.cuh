@@ -1,0 +1,319 @@
+// mg_exec.cuh -- op dispatch: one lowered op -> kernel launches on the workspace stream.
+// Buffer (ping-pong) state is tracked per level and field at issue time, so the same code path
+// serves direct execution (mg_exec_ops) and CUDA-graph capture (mg_build_cycle).
+#pragma once
+#include "mg_coarse.cuh"
+#include "mg_kernels_fast.cuh"
+#include "mg_workspace.cuh"
+
+namespace mg {
+
+template <typename T>
+inline FieldSet<T> fieldset(void* const* arr) {
+    FieldSet<T> fs;
+    for (int i = 0; i < MG_MAX_FIELDS; ++i) fs.p[i] = static_cast<T*>(arr[i] ? arr[i] : arr[0]);
+    return fs;
+}
+
+template <typename T>
+inline FieldSet<T> cur_sol(Level& lv) {
+    FieldSet<T> fs;
+    for (int i = 0; i < MG_MAX_FIELDS; ++i) {
+        void* p = lv.sol[lv.cur[i]][i];
+        fs.p[i] = static_cast<T*>(p ? p : lv.sol[lv.cur[0]][0]);
+    }
+    return fs;
+}
+
+template <int D>
+inline dim3 node_grid(const Geom& g, int bx = 128) {
+    return dim3((g.n + bx - 1) / bx, g.n, D == 3 ? g.n : 1);
+}
+
+inline void count(mg_workspace* ws, int k = 1) { ws->pending_count += k; }
+
+// ---- operator upload ------------------------------------------------------------------------------
+template <typename T>
+inline T host_value(const double* v);
+template <>
+inline double host_value<double>(const double* v) { return v[0]; }
+template <>
+inline cplx host_value<cplx>(const double* v) { return make_cplx(v[0], v[1]); }
+
+template <typename T>
+int upload_operator(mg_workspace* ws, Level& lv) {
+    if (!lv.op_dirty) return MG_OK;
+    OperatorTable<T> tab;
+    memset(&tab, 0, sizeof(tab));
+    for (int i = 0; i < ws->n_fields; ++i)
+        for (int j = 0; j < ws->n_fields; ++j) {
+            if (!lv.hop.set[i][j])
+                return fail(MG_ERR_STATE, "operator block not set on level " + std::to_string(lv.level));
+            tab.n_entries[i][j] = lv.hop.n_entries[i][j];
+            for (int k = 0; k < lv.hop.n_entries[i][j]; ++k) {
+                const int* o = lv.hop.offs[i][j][k];
+                long long lin = o[0] + (long long)o[1] * lv.g.pitch + (ws->dim == 3 ? (long long)o[2] * lv.g.plane : 0);
+                tab.off[i][j][k] = (int)lin;
+                tab.val[i][j][k] = host_value<T>(lv.hop.val[i][j][k]);
+            }
+        }
+    if (!lv.d_op) MG_CUDA(cudaMalloc(&lv.d_op, sizeof(OperatorTable<T>)));
+    MG_CUDA(cudaMemcpyAsync(lv.d_op, &tab, sizeof(tab), cudaMemcpyHostToDevice, ws->stream));
+    MG_CUDA(cudaStreamSynchronize(ws->stream));
+    // classify: scalar real star stencil in canonical order (z-, y-, x-, c, x+, y+, z+) with
+    // symmetric coefficients per axis -> specialised kernels apply
+    lv.star = false;
+    if (ws->dtype == MG_F64 && ws->n_fields == 1) {
+        const HostOperator& h = lv.hop;
+        const int d = ws->dim, ne = h.n_entries[0][0];
+        if (ne == 2 * d + 1) {
+            static const int want2[5][3] = {{0, -1, 0}, {-1, 0, 0}, {0, 0, 0}, {1, 0, 0}, {0, 1, 0}};
+            static const int want3[7][3] = {{0, 0, -1}, {0, -1, 0}, {-1, 0, 0}, {0, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+            bool ok = true;
+            for (int k = 0; k < ne && ok; ++k)
+                for (int c = 0; c < d; ++c)
+                    ok = ok && h.offs[0][0][k][c] == (d == 2 ? want2[k][c] : want3[k][c]);
+            if (ok) {
+                if (d == 2) {
+                    ok = h.val[0][0][0][0] == h.val[0][0][4][0] && h.val[0][0][1][0] == h.val[0][0][3][0];
+                    lv.star_y = h.val[0][0][0][0]; lv.star_x = h.val[0][0][1][0]; lv.star_c = h.val[0][0][2][0];
+                } else {
+                    ok = h.val[0][0][0][0] == h.val[0][0][6][0] && h.val[0][0][1][0] == h.val[0][0][5][0] &&
+                         h.val[0][0][2][0] == h.val[0][0][4][0];
+                    lv.star_z = h.val[0][0][0][0]; lv.star_y = h.val[0][0][1][0]; lv.star_x = h.val[0][0][2][0];
+                    lv.star_c = h.val[0][0][3][0];
+                }
+                lv.star = ok;
+            }
+        }
+    }
+    lv.op_dirty = false;
+    return MG_OK;
+}
+
+// ---- boundary condition on the current solution buffers ----------------------------------------------
+template <typename T>
+inline int apply_bc(mg_workspace*, Level&) { return MG_OK; }
+template <>
+inline int apply_bc<cplx>(mg_workspace* ws, Level& lv) {
+    if (ws->bc_kind != MG_BC_HELMHOLTZ_ROBIN) return MG_OK;
+    double h = 1.0 / (double)(lv.g.n - 1);
+    cplx c = t_div(make_cplx(1.0, 0.0), make_cplx(1.0, -ws->bc_k * h));
+    int blocks = (lv.g.n + 127) / 128;
+    for (int f = 0; f < ws->n_fields; ++f) {
+        cplx* u = static_cast<cplx*>(lv.sol[lv.cur[f]][f]);
+        k_bc_helmholtz<<<blocks, 128, 0, ws->stream>>>(lv.g, u, c);
+        k_bc_helmholtz_rows<<<blocks, 128, 0, ws->stream>>>(lv.g, u);
+        count(ws, 2);
+    }
+    return MG_OK;
+}
+
+// ---- stages ------------------------------------------------------------------------------------------
+template <typename T, int D, int F>
+int exec_smooth(mg_workspace* ws, const mg_op& op) {
+    if (op.smoother < 0 || op.smoother >= (int)ws->smoothers.size()) return fail(MG_ERR_INVALID, "bad smoother handle");
+    Smoother& sm = ws->smoothers[op.smoother];
+    if (sm.level != op.level) return fail(MG_ERR_INVALID, "smoother registered for another level");
+    Level& lv = ws->L(op.level);
+    int rc = upload_operator<T>(ws, lv);
+    if (rc) return rc;
+    const OperatorTable<T>* tab = static_cast<const OperatorTable<T>*>(lv.d_op);
+    const SmootherTable<T>* st = static_cast<const SmootherTable<T>*>(sm.d_table);
+    const T* w = static_cast<const T*>(sm.d_w);
+    FieldSet<T> rhs = fieldset<T>(lv.rhs);
+    if (sm.point) {
+        if (ws->use_fast && fast_smooth<T, D, F>(ws, lv, sm)) return MG_OK;
+        const int colours = sm.colored ? 2 : 1;
+        for (int c = 0; c < colours; ++c) {
+            FieldSet<T> src = cur_sol<T>(lv);
+            FieldSet<T> dst = src;
+            for (int s = 0; s < sm.m; ++s) {
+                int f = sm.slot_field[s];
+                dst.p[f] = static_cast<T*>(lv.sol[lv.cur[f] ^ 1][f]);
+            }
+            k_smooth_point<T, D, F><<<node_grid<D>(lv.g), 128, 0, ws->stream>>>(lv.g, tab, st, w, src, rhs, dst,
+                                                                               sm.colored ? c : -1);
+            count(ws);
+            for (int s = 0; s < sm.m; ++s) lv.cur[sm.slot_field[s]] ^= 1;
+            rc = apply_bc<T>(ws, lv);
+            if (rc) return rc;
+        }
+    } else {
+        FieldSet<T> src = cur_sol<T>(lv);
+        FieldSet<T> dst = src;
+        bool flip[MG_MAX_FIELDS] = {};
+        for (int s = 0; s < sm.m; ++s) flip[sm.slot_field[s]] = true;
+        for (int f = 0; f < F; ++f)
+            if (flip[f]) dst.p[f] = static_cast<T*>(lv.sol[lv.cur[f] ^ 1][f]);
+        int tiles[3] = {1, 1, 1};
+        for (int d = 0; d < D; ++d) tiles[d] = (lv.g.n - 1) / sm.period[d] + 1;
+        dim3 grid((tiles[0] + 63) / 64, tiles[1], tiles[2]);
+        k_smooth_tile<T, D, F><<<grid, 64, 0, ws->stream>>>(lv.g, tab, st, w, src, rhs, dst, tiles[0]);
+        count(ws);
+        for (int f = 0; f < F; ++f)
+            if (flip[f]) lv.cur[f] ^= 1;
+        rc = apply_bc<T>(ws, lv);
+        if (rc) return rc;
+    }
+    return MG_OK;
+}
+
+template <typename T, int D, int F>
+int exec_residual(mg_workspace* ws, int level) {
+    Level& lv = ws->L(level);
+    int rc = upload_operator<T>(ws, lv);
+    if (rc) return rc;
+    if (ws->use_fast && fast_residual<T, D, F>(ws, lv)) return MG_OK;
+    k_residual<T, D, F><<<node_grid<D>(lv.g), 128, 0, ws->stream>>>(
+        lv.g, static_cast<const OperatorTable<T>*>(lv.d_op), cur_sol<T>(lv), fieldset<T>(lv.rhs), fieldset<T>(lv.res));
+    count(ws);
+    return MG_OK;
+}
+
+template <typename T>
+inline FieldSet<T> field_by_kind(mg_workspace* ws, Level& lv, int kind) {
+    switch (kind) {
+        case MG_RHS: return fieldset<T>(lv.rhs);
+        case MG_RES: return fieldset<T>(lv.res);
+        case MG_COR: return lv.level == ws->max_level ? fieldset<T>(lv.cor) : cur_sol<T>(lv);
+        default: return cur_sol<T>(lv);
+    }
+}
+
+template <typename T, int D, int F>
+int exec_restrict(mg_workspace* ws, const mg_op& op, bool fused) {
+    if (!ws->has_level(op.level) || !ws->has_level(op.level + 1)) return fail(MG_ERR_INVALID, "restrict: level out of range");
+    Level& lc = ws->L(op.level);
+    Level& lf = ws->L(op.level + 1);
+    if (fused) {
+        int rc = upload_operator<T>(ws, lf);
+        if (rc) return rc;
+        if (ws->use_fast && fast_residual_restrict<T, D, F>(ws, lf, lc)) return MG_OK;
+        k_residual_restrict<T, D, F><<<node_grid<D>(lc.g), 128, 0, ws->stream>>>(
+            lc.g, lf.g, static_cast<const OperatorTable<T>*>(lf.d_op), cur_sol<T>(lf), fieldset<T>(lf.rhs),
+            fieldset<T>(lc.rhs));
+    } else {
+        k_restrict<T, D, F><<<node_grid<D>(lc.g), 128, 0, ws->stream>>>(lc.g, lf.g, field_by_kind<T>(ws, lf, op.src),
+                                                                         fieldset<T>(lc.rhs));
+    }
+    count(ws);
+    return MG_OK;
+}
+
+template <typename T, int D, int F>
+int exec_prolong(mg_workspace* ws, const mg_op& op, bool add) {
+    if (!ws->has_level(op.level) || !ws->has_level(op.level - 1)) return fail(MG_ERR_INVALID, "prolong: level out of range");
+    Level& lf = ws->L(op.level);
+    Level& lc = ws->L(op.level - 1);
+    FieldSet<T> src = field_by_kind<T>(ws, lc, op.src);
+    FieldSet<T> dst = add ? cur_sol<T>(lf) : field_by_kind<T>(ws, lf, MG_COR);
+    if (!(add && ws->use_fast && fast_prolong_add<T, D, F>(ws, lf, lc, src, op.omega))) {
+        k_prolong<T, D, F><<<node_grid<D>(lf.g), 128, 0, ws->stream>>>(lf.g, lc.g, src, dst, op.omega, add ? 1 : 0);
+        count(ws);
+    }
+    if (add) return apply_bc<T>(ws, lf);
+    return MG_OK;
+}
+
+template <typename T>
+int exec_zero(mg_workspace* ws, int level) {
+    Level& lv = ws->L(level);
+    for (int f = 0; f < ws->n_fields; ++f) {
+        lv.cur[f] = 0;
+        MG_CUDA(cudaMemsetAsync(lv.sol[0][f], 0, (size_t)lv.g.total * sizeof(T), ws->stream));
+    }
+    return MG_OK;
+}
+
+// everything that must not happen during stream capture: operator uploads, scratch allocation,
+// dynamic shared memory opt-in
+template <typename T, int D, int F>
+int prepare(mg_workspace* ws) {
+    for (auto& lv : ws->levels) {
+        bool any = false;
+        for (int i = 0; i < ws->n_fields; ++i)
+            for (int j = 0; j < ws->n_fields; ++j) any = any || lv.hop.set[i][j];
+        if (!any) continue;
+        int rc = upload_operator<T>(ws, lv);
+        if (rc) return rc;
+    }
+    Level& lv = ws->L(ws->min_level);
+    const int nvec = ws->cgs_kind == MG_CGS_CG ? 4 : 7;
+    size_t bytes = (size_t)nvec * F * lv.g.total * sizeof(T);
+    if (bytes <= 200 * 1024) {
+        MG_CUDA(cudaFuncSetAttribute(k_coarse_cg<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        MG_CUDA(cudaFuncSetAttribute(k_coarse_bicgstab<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    } else if (ws->cgs_work_bytes < bytes) {
+        if (ws->cgs_work) cudaFree(ws->cgs_work);
+        MG_CUDA(cudaMalloc(&ws->cgs_work, bytes));
+        ws->cgs_work_bytes = bytes;
+    }
+    return MG_OK;
+}
+
+template <typename T, int D, int F>
+int exec_cgs(mg_workspace* ws, int level) {
+    if (level != ws->min_level) return fail(MG_ERR_INVALID, "coarse-grid solver op must be on the workspace's min level");
+    Level& lv = ws->L(level);
+    if (lv.op_dirty) return fail(MG_ERR_STATE, "operator not uploaded (prepare not run)");
+    for (int f = 0; f < F; ++f) lv.cur[f] = 0;
+    const int nvec = ws->cgs_kind == MG_CGS_CG ? 4 : 7;
+    size_t bytes = (size_t)nvec * F * lv.g.total * sizeof(T);
+    const bool smem = bytes <= 200 * 1024;
+    const OperatorTable<T>* tab = static_cast<const OperatorTable<T>*>(lv.d_op);
+    FieldSet<T> sol = cur_sol<T>(lv), rhs = fieldset<T>(lv.rhs);
+    T* gwork = static_cast<T*>(ws->cgs_work);
+    double h = 1.0 / (double)(lv.g.n - 1);
+    cplx bcf = t_div(make_cplx(1.0, 0.0), make_cplx(1.0, -ws->bc_k * h));
+    int robin = ws->bc_kind == MG_BC_HELMHOLTZ_ROBIN ? 1 : 0;
+    if (ws->cgs_kind == MG_CGS_CG) {
+        if (smem) {
+            k_coarse_cg<T, D, F, true><<<1, 256, bytes, ws->stream>>>(lv.g, tab, sol, rhs, nullptr, ws->cgs_max_its, ws->cgs_reduction);
+        } else {
+            k_coarse_cg<T, D, F, false><<<1, 256, 0, ws->stream>>>(lv.g, tab, sol, rhs, gwork, ws->cgs_max_its, ws->cgs_reduction);
+        }
+    } else {
+        if (smem) {
+            k_coarse_bicgstab<T, D, F, true><<<1, 256, bytes, ws->stream>>>(lv.g, tab, sol, rhs, nullptr, ws->cgs_max_its, ws->cgs_reduction, robin, bcf);
+        } else {
+            k_coarse_bicgstab<T, D, F, false><<<1, 256, 0, ws->stream>>>(lv.g, tab, sol, rhs, gwork, ws->cgs_max_its, ws->cgs_reduction, robin, bcf);
+        }
+    }
+    count(ws);
+    return MG_OK;
+}
+
+template <typename T, int D, int F>
+int exec_norm(mg_workspace* ws, int level) {
+    Level& lv = ws->L(level);
+    int rc = upload_operator<T>(ws, lv);
+    if (rc) return rc;
+    if (!(ws->use_fast && fast_norm<T, D, F>(ws, lv))) {
+        k_norm_partial<T, D, F><<<lv.norm_blocks, 256, 0, ws->stream>>>(
+            lv.g, static_cast<const OperatorTable<T>*>(lv.d_op), cur_sol<T>(lv), fieldset<T>(lv.rhs),
+            static_cast<T*>(lv.partial));
+        count(ws);
+    }
+    k_norm_final<T><<<1, 256, 0, ws->stream>>>(static_cast<const T*>(lv.partial), lv.norm_blocks, ws->d_norm);
+    count(ws);
+    return MG_OK;
+}
+
+template <typename T, int D, int F>
+int exec_op(mg_workspace* ws, const mg_op& op) {
+    if (!ws->has_level(op.level)) return fail(MG_ERR_INVALID, "op level out of range");
+    switch (op.kind) {
+        case MG_OP_SMOOTH: return exec_smooth<T, D, F>(ws, op);
+        case MG_OP_RESIDUAL: return exec_residual<T, D, F>(ws, op.level);
+        case MG_OP_RESTRICT: return exec_restrict<T, D, F>(ws, op, false);
+        case MG_OP_RESIDUAL_RESTRICT: return exec_restrict<T, D, F>(ws, op, true);
+        case MG_OP_ZERO: return exec_zero<T>(ws, op.level);
+        case MG_OP_PROLONG_ADD: return exec_prolong<T, D, F>(ws, op, true);
+        case MG_OP_PROLONG: return exec_prolong<T, D, F>(ws, op, false);
+        case MG_OP_CGS: return exec_cgs<T, D, F>(ws, op.level);
+        default: return fail(MG_ERR_INVALID, "unknown op kind");
+    }
+}
+
+}  // namespace mg

@@ -1,0 +1,317 @@
+// mg_kernels_generic.cuh -- generic stage kernels: any dimension (2/3), 1-2 fields, real or
+// complex, arbitrary constant stencils.  One thread per node, x fastest (coalesced).  These are
+// the reference-semantics kernels every configuration can fall back on; the hot 2D/3D scalar
+// Poisson stages have specialised versions in mg_kernels_fast.cuh.
+#pragma once
+#include "mg_common.cuh"
+
+namespace mg {
+
+template <int D>
+__device__ __forceinline__ bool node_coords(const Geom& g, int& x, int& y, int& z) {
+    x = blockIdx.x * blockDim.x + threadIdx.x;
+    y = blockIdx.y;
+    z = (D == 3) ? blockIdx.z : 0;
+    return x < g.n;
+}
+
+template <int D>
+__device__ __forceinline__ bool is_interior(const Geom& g, int x, int y, int z) {
+    bool in = x >= 1 && x <= g.n - 2 && y >= 1 && y <= g.n - 2;
+    if (D == 3) in = in && z >= 1 && z <= g.n - 2;
+    return in;
+}
+
+template <int D>
+__device__ __forceinline__ long long node_index(const Geom& g, int x, int y, int z) {
+    return (D == 3 ? (long long)z * g.plane : 0ll) + (long long)y * g.pitch + x;
+}
+
+// (A u)_row at element idx, canonical accumulation order (block column ascending, entries as given)
+template <typename T, int F>
+__device__ __forceinline__ T apply_row(const OperatorTable<T>* __restrict__ op, const FieldSet<T>& u, int row,
+                                       long long idx) {
+    T acc = t_zero(T());
+    bool first = true;
+#pragma unroll
+    for (int j = 0; j < F; ++j) {
+        const int ne = op->n_entries[row][j];
+        for (int k = 0; k < ne; ++k) {
+            T term = t_mul(op->val[row][j][k], u.p[j][idx + op->off[row][j][k]]);
+            acc = first ? term : t_add(acc, term);
+            first = false;
+        }
+    }
+    return acc;
+}
+
+// res = rhs - A sol
+template <typename T, int D, int F>
+__global__ void k_residual(Geom g, const OperatorTable<T>* __restrict__ op, FieldSet<T> sol, FieldSet<T> rhs,
+                           FieldSet<T> res) {
+    int x, y, z;
+    if (!node_coords<D>(g, x, y, z) || !is_interior<D>(g, x, y, z)) return;
+    long long idx = node_index<D>(g, x, y, z);
+#pragma unroll
+    for (int i = 0; i < F; ++i) res.p[i][idx] = t_sub(rhs.p[i][idx], apply_row<T, F>(op, sol, i, idx));
+}
+
+// Point smoother, out of place: dst_s = src_s + sum_t W[s][t] r_t on the selected colour
+// (colour < 0: all interior nodes), dst_s = src_s elsewhere (including the boundary).
+template <typename T, int D, int F>
+__global__ void k_smooth_point(Geom g, const OperatorTable<T>* __restrict__ op,
+                               const SmootherTable<T>* __restrict__ sm, const T* __restrict__ w, FieldSet<T> src,
+                               FieldSet<T> rhs, FieldSet<T> dst, int colour) {
+    int x, y, z;
+    if (!node_coords<D>(g, x, y, z)) return;
+    long long idx = node_index<D>(g, x, y, z);
+    const int m = sm->n_slots;
+    bool active = is_interior<D>(g, x, y, z) && (colour < 0 || ((x + y + z) & 1) == colour);
+    if (!active) {
+        for (int s = 0; s < m; ++s) {
+            int f = sm->slot_field[s];
+            dst.p[f][idx] = src.p[f][idx];
+        }
+        return;
+    }
+    T r[MG_MAX_FIELDS];
+    for (int s = 0; s < m; ++s) {
+        int f = sm->slot_field[s];
+        r[s] = t_sub(rhs.p[f][idx], apply_row<T, F>(op, src, f, idx));
+    }
+    const T* wk = w + (long long)sm->mask_index[(1 << m) - 1] * m * m;
+    for (int s = 0; s < m; ++s) {
+        T delta = t_mul(wk[s * m + 0], r[0]);
+        for (int t = 1; t < m; ++t) delta = t_add(delta, t_mul(wk[s * m + t], r[t]));
+        int f = sm->slot_field[s];
+        dst.p[f][idx] = t_add(src.p[f][idx], delta);
+    }
+}
+
+// Tile smoother (Jacobi), one thread per tile, out of place.
+template <typename T, int D, int F>
+__global__ void k_smooth_tile(Geom g, const OperatorTable<T>* __restrict__ op,
+                              const SmootherTable<T>* __restrict__ sm, const T* __restrict__ w, FieldSet<T> src,
+                              FieldSet<T> rhs, FieldSet<T> dst, int tiles_x) {
+    int tx = blockIdx.x * blockDim.x + threadIdx.x;
+    int ty = blockIdx.y;
+    int tz = (D == 3) ? blockIdx.z : 0;
+    if (tx >= tiles_x) return;
+    const int m = sm->n_slots;
+    T r[MG_MAX_SLOTS];
+    long long idx[MG_MAX_SLOTS];
+    unsigned mask = 0;
+    for (int s = 0; s < m; ++s) {
+        int x = tx * sm->period[0] + sm->slot_pos[s][0];
+        int y = ty * sm->period[1] + sm->slot_pos[s][1];
+        int z = (D == 3) ? tz * sm->period[2] + sm->slot_pos[s][2] : 0;
+        bool exists = x < g.n && y < g.n && (D < 3 || z < g.n);
+        idx[s] = exists ? node_index<D>(g, x, y, z) : -1;
+        r[s] = t_zero(T());
+        if (exists && is_interior<D>(g, x, y, z)) {
+            mask |= 1u << s;
+            int f = sm->slot_field[s];
+            r[s] = t_sub(rhs.p[f][idx[s]], apply_row<T, F>(op, src, f, idx[s]));
+        }
+    }
+    int k = sm->mask_index[mask];
+    const T* wk = w + (long long)(k < 0 ? 0 : k) * m * m;
+    for (int s = 0; s < m; ++s) {
+        if (idx[s] < 0) continue;
+        int f = sm->slot_field[s];
+        T old = src.p[f][idx[s]];
+        if ((mask >> s) & 1u) {
+            T delta = t_zero(T());
+            bool first = true;
+            for (int t = 0; t < m; ++t) {
+                if (!((mask >> t) & 1u)) continue;
+                T term = t_mul(wk[s * m + t], r[t]);
+                delta = first ? term : t_add(delta, term);
+                first = false;
+            }
+            dst.p[f][idx[s]] = t_add(old, delta);
+        } else {
+            dst.p[f][idx[s]] = old;
+        }
+    }
+}
+
+// full weighting: coarse(I) = sum_o w_o fine(2I + o), offsets in memory order
+template <typename T, int D>
+__device__ __forceinline__ T restrict_at(const T* __restrict__ fine, const Geom& gf, int X, int Y, int Z) {
+    T acc = t_zero(T());
+    bool first = true;
+    const double w1[3] = {0.25, 0.5, 0.25};
+    for (int oz = (D == 3 ? -1 : 0); oz <= (D == 3 ? 1 : 0); ++oz)
+        for (int oy = -1; oy <= 1; ++oy)
+            for (int ox = -1; ox <= 1; ++ox) {
+                double wgt = w1[ox + 1] * w1[oy + 1];   // products of powers of two: exact
+                if (D == 3) wgt = w1[oz + 1] * wgt;
+                T term = t_scale(wgt, fine[node_index<D>(gf, 2 * X + ox, 2 * Y + oy, 2 * Z + oz)]);
+                acc = first ? term : t_add(acc, term);
+                first = false;
+            }
+    return acc;
+}
+
+template <typename T, int D, int F>
+__global__ void k_restrict(Geom gc, Geom gf, FieldSet<T> fine, FieldSet<T> coarse_rhs) {
+    int x, y, z;
+    if (!node_coords<D>(gc, x, y, z) || !is_interior<D>(gc, x, y, z)) return;
+    long long idx = node_index<D>(gc, x, y, z);
+#pragma unroll
+    for (int i = 0; i < F; ++i) coarse_rhs.p[i][idx] = restrict_at<T, D>(fine.p[i], gf, x, y, z);
+}
+
+// fused residual + restriction (generic: each coarse thread recomputes its 3^D fine residuals)
+template <typename T, int D, int F>
+__global__ void k_residual_restrict(Geom gc, Geom gf, const OperatorTable<T>* __restrict__ op, FieldSet<T> sol,
+                                    FieldSet<T> rhs, FieldSet<T> coarse_rhs) {
+    int X, Y, Z;
+    if (!node_coords<D>(gc, X, Y, Z) || !is_interior<D>(gc, X, Y, Z)) return;
+    long long cidx = node_index<D>(gc, X, Y, Z);
+    const double w1[3] = {0.25, 0.5, 0.25};
+#pragma unroll
+    for (int i = 0; i < F; ++i) {
+        T acc = t_zero(T());
+        bool first = true;
+        for (int oz = (D == 3 ? -1 : 0); oz <= (D == 3 ? 1 : 0); ++oz)
+            for (int oy = -1; oy <= 1; ++oy)
+                for (int ox = -1; ox <= 1; ++ox) {
+                    double wgt = w1[ox + 1] * w1[oy + 1];
+                    if (D == 3) wgt = w1[oz + 1] * wgt;
+                    long long fidx = node_index<D>(gf, 2 * X + ox, 2 * Y + oy, 2 * Z + oz);
+                    T r = t_sub(rhs.p[i][fidx], apply_row<T, F>(op, sol, i, fidx));
+                    T term = t_scale(wgt, r);
+                    acc = first ? term : t_add(acc, term);
+                    first = false;
+                }
+        coarse_rhs.p[i][cidx] = acc;
+    }
+}
+
+// (P e)(x): 2^-k * (sum of the 2^k enclosing coarse nodes in memory order), k = #odd coordinates
+template <typename T, int D>
+__device__ __forceinline__ T prolong_at(const T* __restrict__ coarse, const Geom& gc, int x, int y, int z) {
+    int px = x & 1, py = y & 1, pz = (D == 3) ? (z & 1) : 0;
+    int X = x >> 1, Y = y >> 1, Z = z >> 1;
+    T acc = t_zero(T());
+    bool first = true;
+    for (int cz = 0; cz <= pz; ++cz)
+        for (int cy = 0; cy <= py; ++cy)
+            for (int cx = 0; cx <= px; ++cx) {
+                T term = coarse[node_index<D>(gc, X + cx, Y + cy, Z + cz)];
+                acc = first ? term : t_add(acc, term);
+                first = false;
+            }
+    int k = px + py + pz;
+    if (k == 0) return acc;
+    const double scale = (k == 1) ? 0.5 : (k == 2 ? 0.25 : 0.125);
+    return t_scale(scale, acc);
+}
+
+// sol += omega * P coarse   (add != 0)   |   dst = P coarse   (add == 0)
+template <typename T, int D, int F>
+__global__ void k_prolong(Geom gf, Geom gc, FieldSet<T> coarse, FieldSet<T> dst, double omega, int add) {
+    int x, y, z;
+    if (!node_coords<D>(gf, x, y, z) || !is_interior<D>(gf, x, y, z)) return;
+    long long idx = node_index<D>(gf, x, y, z);
+#pragma unroll
+    for (int i = 0; i < F; ++i) {
+        T pe = prolong_at<T, D>(coarse.p[i], gc, x, y, z);
+        dst.p[i][idx] = add ? t_add(dst.p[i][idx], t_scale(omega, pe)) : pe;
+    }
+}
+
+// Robin columns of the Helmholtz problem (2D): u(0,y) = c u(1,y), u(n-1,y) = c u(n-2,y); rows y=0,n-1 -> 0
+__global__ void k_bc_helmholtz(Geom g, cplx* u, cplx c) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= g.n) return;
+    long long row = (long long)t * g.pitch;
+    u[row] = t_mul(u[row + 1], c);
+    u[row + g.n - 1] = t_mul(u[row + g.n - 2], c);
+}
+__global__ void k_bc_helmholtz_rows(Geom g, cplx* u) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= g.n) return;
+    u[t] = make_cplx(0.0, 0.0);
+    u[(long long)(g.n - 1) * g.pitch + t] = make_cplx(0.0, 0.0);
+}
+
+// ---- residual norm: deterministic two-stage reduction -------------------------------------------
+__device__ __forceinline__ double sq_acc(double r) { return r * r; }
+__device__ __forceinline__ cplx sq_acc(cplx r) { return t_mul(r, r); }   // dot without conjugation
+
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v);
+template <>
+__device__ __forceinline__ double warp_sum<double>(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+template <>
+__device__ __forceinline__ cplx warp_sum<cplx>(cplx v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v.re += __shfl_xor_sync(0xffffffffu, v.re, o);
+        v.im += __shfl_xor_sync(0xffffffffu, v.im, o);
+    }
+    return v;
+}
+
+// block of 256 threads; result valid in every thread
+template <typename T>
+__device__ __forceinline__ T block_sum_256(T v, T* smem8) {
+    v = warp_sum<T>(v);
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) smem8[warp] = v;
+    __syncthreads();
+    T a0 = t_add(smem8[0], smem8[4]), a1 = t_add(smem8[1], smem8[5]);
+    T a2 = t_add(smem8[2], smem8[6]), a3 = t_add(smem8[3], smem8[7]);
+    return t_add(t_add(a0, a2), t_add(a1, a3));
+}
+
+// partial[b] = sum over the rows owned by block b of (rhs - A sol)^2 ; rows = F * n^(D-1)
+template <typename T, int D, int F>
+__global__ void __launch_bounds__(256) k_norm_partial(Geom g, const OperatorTable<T>* __restrict__ op,
+                                                      FieldSet<T> sol, FieldSet<T> rhs, T* __restrict__ partial) {
+    __shared__ T s8[8];
+    const int rows_per_field = (D == 3) ? g.n * g.n : g.n;
+    const int rows = F * rows_per_field;
+    T acc = t_zero(T());
+    for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+        int f = row / rows_per_field;
+        int rr = row - f * rows_per_field;
+        int z = (D == 3) ? rr / g.n : 0;
+        int y = (D == 3) ? rr - z * g.n : rr;
+        if (y < 1 || y > g.n - 2 || (D == 3 && (z < 1 || z > g.n - 2))) continue;
+        for (int x = 1 + threadIdx.x; x <= g.n - 2; x += 256) {
+            long long idx = node_index<D>(g, x, y, z);
+            T r = t_sub(rhs.p[f][idx], apply_row<T, F>(op, sol, f, idx));
+            acc = t_add(acc, sq_acc(r));
+        }
+    }
+    T total = block_sum_256<T>(acc, s8);
+    if (threadIdx.x == 0) partial[blockIdx.x] = total;
+}
+
+// out[0] = |sqrt(sum partial)|  (real: sqrt; complex: modulus of the complex square root)
+template <typename T>
+__global__ void __launch_bounds__(256) k_norm_final(const T* __restrict__ partial, int n, double* __restrict__ out) {
+    __shared__ T s8[8];
+    T acc = t_zero(T());
+    for (int i = threadIdx.x; i < n; i += 256) acc = t_add(acc, partial[i]);
+    T total = block_sum_256<T>(acc, s8);
+    if (threadIdx.x == 0) {
+        if constexpr (sizeof(T) == sizeof(double)) {
+            out[0] = sqrt(*reinterpret_cast<double*>(&total));
+        } else {
+            cplx c = *reinterpret_cast<cplx*>(&total);
+            out[0] = sqrt(hypot(c.re, c.im));       // |sqrt(z)| = sqrt(|z|)
+        }
+    }
+}
+
+}  // namespace mg

@@ -1,0 +1,115 @@
+// mg_workspace.cuh -- device storage of one solver instance: level hierarchy, operator tables,
+// smoother tables, captured cycles.  Layout in HBM (DESIGN.md "Data layout"):
+//   per level and field: sol[0], sol[1] (ping-pong for out-of-place sweeps), rhs, res, and on the
+//   finest level cor and init; each array is n^(d-1) rows of `pitch` elements, pitch = n rounded
+//   up to 16 elements so that every row starts on a 128-byte boundary (256 B for complex).
+#pragma once
+#include <cuda_runtime.h>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/mgengine.h"
+#include "mg_common.cuh"
+
+namespace mg {
+
+extern thread_local std::string g_last_error;
+
+inline int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+#define MG_CUDA(call)                                                                              \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return mg::fail(MG_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));      \
+    } while (0)
+
+struct HostOperator {          // dtype-agnostic host copy (values as re/im pairs)
+    int n_entries[MG_MAX_FIELDS][MG_MAX_FIELDS] = {};
+    int offs[MG_MAX_FIELDS][MG_MAX_FIELDS][MG_MAX_ENTRIES][MG_MAX_DIM] = {};
+    double val[MG_MAX_FIELDS][MG_MAX_FIELDS][MG_MAX_ENTRIES][2] = {};
+    bool set[MG_MAX_FIELDS][MG_MAX_FIELDS] = {};
+};
+
+struct Level {
+    int level = 0;
+    Geom g{};
+    void* slab = nullptr;
+    void* sol[2][MG_MAX_FIELDS] = {};
+    void* rhs[MG_MAX_FIELDS] = {};
+    void* res[MG_MAX_FIELDS] = {};
+    void* cor[MG_MAX_FIELDS] = {};      // finest only
+    void* init[MG_MAX_FIELDS] = {};     // finest only: saved initial guess
+    int cur[MG_MAX_FIELDS] = {};        // which sol buffer is current
+    HostOperator hop;
+    void* d_op = nullptr;               // OperatorTable<T>
+    bool op_dirty = true;
+    // fast-path classification (filled when the operator is uploaded)
+    bool star = false;                  // scalar real (2d+1)-point stencil with symmetric structure
+    double star_c = 0, star_x = 0, star_y = 0, star_z = 0;
+    void* partial = nullptr;            // norm partials
+    int norm_blocks = 0;
+};
+
+struct Smoother {
+    int level = 0;
+    bool jacobi = true, colored = false;
+    int m = 0;
+    bool point = true;
+    int period[MG_MAX_DIM] = {1, 1, 1};
+    int slot_field[MG_MAX_SLOTS] = {};
+    void* d_table = nullptr;            // SmootherTable<T>
+    void* d_w = nullptr;                // W tables
+    // point smoother on a star stencil, single slot: scale = W[0][0] (real)
+    double w00 = 0;
+    bool same_colour_coupling = false;  // stencil couples nodes of equal colour -> no in-place colour sweep
+};
+
+struct GraphVariant {
+    cudaGraphExec_t exec = nullptr;
+    int end_state = 0;
+    long long kernels = 0;
+};
+
+struct Cycle {
+    std::vector<mg_op> ops;
+    std::map<int, GraphVariant> variants;      // keyed by the finest level's buffer state
+};
+
+}  // namespace mg
+
+struct mg_workspace {
+    int dim = 2, min_level = 0, max_level = 0, n_fields = 1, dtype = MG_F64, device = 0;
+    size_t elem = 8;
+    cudaStream_t stream = nullptr;
+    std::vector<mg::Level> levels;              // index = level - min_level
+    std::vector<mg::Smoother> smoothers;
+    std::vector<mg::Cycle> cycles;
+    int bc_kind = MG_BC_DIRICHLET;
+    double bc_k = 0.0;
+    int cgs_kind = MG_CGS_CG, cgs_max_its = 1000;
+    double cgs_reduction = 1e-12;
+    void* cgs_work = nullptr;                   // global scratch when the coarse level exceeds smem
+    size_t cgs_work_bytes = 0;
+    double* d_norm = nullptr;                   // device scalar
+    double* h_norm = nullptr;                   // pinned host scalar
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    long long launches = 0;                     // kernels launched (incl. graph replays)
+    long long pending_count = 0;                // kernels issued since the counter was last sampled
+    bool use_fast = true;                       // specialised kernels where applicable
+
+    mg::Level& L(int level) { return levels[level - min_level]; }
+    bool has_level(int level) const { return level >= min_level && level <= max_level; }
+    int finest_state() {
+        int s = 0;
+        for (int f = 0; f < n_fields; ++f) s |= L(max_level).cur[f] << f;
+        return s;
+    }
+    void set_finest_state(int s) {
+        for (int f = 0; f < n_fields; ++f) L(max_level).cur[f] = (s >> f) & 1;
+    }
+};

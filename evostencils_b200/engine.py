@@ -1,0 +1,322 @@
+"""ctypes binding of the C-ABI engine library (include/mgengine.h, csrc/mg_engine.cu).
+
+This is the host side of the drop-in boundary: it turns a lowered `Program`
+(lowering.py) into `mg_op` records plus smoother tables and drives one workspace.
+There is no CPU fallback: if the shared library is missing or no CUDA device is
+present, construction raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import itertools
+import os
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+
+from . import lowering
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libmgengine.so")
+
+MG_F64, MG_C128 = 0, 1
+MG_SOL, MG_RHS, MG_RES, MG_COR = 0, 1, 2, 3
+MG_BC_DIRICHLET, MG_BC_HELMHOLTZ_ROBIN = 0, 1
+MG_CGS_CG, MG_CGS_BICGSTAB = 0, 1
+(MG_OP_SMOOTH, MG_OP_RESIDUAL, MG_OP_RESTRICT, MG_OP_RESIDUAL_RESTRICT, MG_OP_ZERO, MG_OP_PROLONG_ADD,
+ MG_OP_PROLONG, MG_OP_CGS) = range(8)
+
+_FIELD = {"sol": MG_SOL, "rhs": MG_RHS, "res": MG_RES, "cor": MG_COR, "": MG_SOL}
+
+EXPORTED_SYMBOLS = [
+    "mg_create", "mg_destroy", "mg_last_error", "mg_launch_count", "mg_set_operator", "mg_set_boundary",
+    "mg_set_coarse_solver", "mg_add_smoother", "mg_clear_smoothers", "mg_upload", "mg_download",
+    "mg_upload_device", "mg_save_initial_guess", "mg_restore_initial_guess", "mg_exec_ops", "mg_build_cycle",
+    "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_synchronize",
+]
+
+
+class MgOp(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("level", C.c_int32), ("omega", C.c_double), ("src", C.c_int32),
+                ("smoother", C.c_int32)]
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library(path: Optional[str] = None):
+    """dlopen the engine; raises (loudly) when it has not been built."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise EngineError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(the engine has no CPU fallback)")
+    lib = C.CDLL(path)
+    lib.mg_last_error.restype = C.c_char_p
+    vp, i32, dbl = C.c_void_p, C.c_int, C.c_double
+    lib.mg_create.argtypes = [C.POINTER(vp), i32, i32, i32, i32, i32, i32]
+    lib.mg_destroy.argtypes = [vp]
+    lib.mg_launch_count.argtypes = [vp, C.POINTER(C.c_int64)]
+    lib.mg_set_operator.argtypes = [vp, i32, i32, i32, i32, C.POINTER(C.c_int32), C.POINTER(dbl)]
+    lib.mg_set_boundary.argtypes = [vp, i32, dbl]
+    lib.mg_set_coarse_solver.argtypes = [vp, i32, i32, dbl]
+    lib.mg_add_smoother.argtypes = [vp, i32, i32, i32, C.POINTER(C.c_int32), i32, C.POINTER(C.c_int32),
+                                    C.POINTER(C.c_int32), i32, C.POINTER(C.c_uint32), C.POINTER(dbl),
+                                    C.POINTER(C.c_int)]
+    lib.mg_clear_smoothers.argtypes = [vp]
+    lib.mg_upload.argtypes = [vp, i32, i32, i32, vp]
+    lib.mg_download.argtypes = [vp, i32, i32, i32, vp]
+    lib.mg_upload_device.argtypes = [vp, i32, i32, i32, vp]
+    lib.mg_save_initial_guess.argtypes = [vp]
+    lib.mg_restore_initial_guess.argtypes = [vp]
+    lib.mg_exec_ops.argtypes = [vp, C.POINTER(MgOp), i32]
+    lib.mg_build_cycle.argtypes = [vp, C.POINTER(MgOp), i32, C.POINTER(C.c_int)]
+    lib.mg_free_cycles.argtypes = [vp]
+    lib.mg_run_cycles.argtypes = [vp, i32, i32, C.POINTER(C.c_float)]
+    lib.mg_residual_norm.argtypes = [vp, i32, C.POINTER(dbl)]
+    lib.mg_solve.argtypes = [vp, i32, dbl, i32, C.POINTER(dbl), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                             C.POINTER(C.c_float)]
+    lib.mg_synchronize.argtypes = [vp]
+    if path == LIB_PATH:
+        _lib = lib
+    return lib
+
+
+# ----------------------------------------------------------------------------------------
+# smoother tables: W = omega * inv(L) for every boundary class of a tile
+# ----------------------------------------------------------------------------------------
+
+def _omega_inverse(matrix: np.ndarray, omega: float) -> np.ndarray:
+    m = matrix.shape[0]
+    if m == 1:
+        return np.array([[omega / matrix[0, 0]]], dtype=matrix.dtype)
+    if m == 2:
+        a, b, c, d = matrix[0, 0], matrix[0, 1], matrix[1, 0], matrix[1, 1]
+        det = a * d - b * c
+        return np.array([[omega * (d / det), omega * (-b / det)],
+                         [omega * (-c / det), omega * (a / det)]], dtype=matrix.dtype)
+    return omega * np.linalg.inv(matrix)
+
+
+def smoother_tables(stmt: lowering.LocalSolve, dimension: int, dtype):
+    """-> (masks uint32[k], W[k][m][m]) for the validity masks that occur on this level."""
+    n = 2 ** stmt.level + 1
+    m = len(stmt.slots)
+    matrix = np.array(stmt.matrix, dtype=dtype)
+    per_dim = []
+    for ax in range(dimension):
+        b = stmt.period[ax]
+        classes = set()
+        for t in range((n - 1) // b + 1):
+            classes.add(tuple(1 <= t * b + p <= n - 2 for p in range(b)))
+        per_dim.append(sorted(classes))
+    tables: Dict[int, np.ndarray] = {}
+    for combo in itertools.product(*per_dim):
+        valid = [all(combo[ax][pos[ax]] for ax in range(dimension)) for _, pos in stmt.slots]
+        mask = sum(1 << s for s in range(m) if valid[s])
+        if mask == 0 or mask in tables:
+            continue
+        idx = [s for s in range(m) if valid[s]]
+        w = np.zeros((m, m), dtype=dtype)
+        w[np.ix_(idx, idx)] = _omega_inverse(matrix[np.ix_(idx, idx)], stmt.omega)
+        tables[mask] = w
+    full = (1 << m) - 1
+    if full not in tables:      # grid smaller than a tile: the kernel still needs the slot
+        tables[full] = _omega_inverse(matrix, stmt.omega)
+    masks = np.array(sorted(tables), dtype=np.uint32)
+    w_all = np.ascontiguousarray(np.stack([tables[int(k)] for k in masks]))
+    return masks, w_all
+
+
+class Workspace:
+    """One level hierarchy on one GPU.  Reused across individuals of the same problem."""
+
+    def __init__(self, dimension, min_level, max_level, n_fields, dtype="f64", device=0, lib=None):
+        self.lib = lib or load_library()
+        self.dimension, self.min_level, self.max_level = dimension, min_level, max_level
+        self.n_fields = n_fields
+        self.dtype = dtype
+        self.np_dtype = np.complex128 if dtype == "c128" else np.float64
+        self.device = device
+        self._h = C.c_void_p()
+        self._check(self.lib.mg_create(C.byref(self._h), dimension, min_level, max_level, n_fields,
+                                       MG_C128 if dtype == "c128" else MG_F64, device))
+        self._smoother_cache: Dict[tuple, int] = {}
+        self._operators: Dict[int, list] = {}
+
+    # -- plumbing ------------------------------------------------------------------------
+    def _check(self, rc):
+        if rc != 0:
+            raise EngineError(f"mgengine error {rc}: {self.lib.mg_last_error().decode()}")
+
+    def close(self):
+        if self._h:
+            self.lib.mg_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- problem definition ----------------------------------------------------------------
+    def set_operator(self, level, table):
+        """`table` = F x F canonical stencils [(offset, value), ...] (lowering.operator_table)."""
+        if self._operators.get(level) == table:
+            return
+        for i, row in enumerate(table):
+            for j, entries in enumerate(row):
+                n = len(entries)
+                offs = (C.c_int32 * max(1, n * self.dimension))()
+                vals = (C.c_double * max(1, n * (2 if self.dtype == "c128" else 1)))()
+                for k, (off, val) in enumerate(entries):
+                    for c in range(self.dimension):
+                        offs[k * self.dimension + c] = off[c]
+                    if self.dtype == "c128":
+                        v = complex(val)
+                        vals[2 * k], vals[2 * k + 1] = v.real, v.imag
+                    else:
+                        vals[k] = float(val)
+                self._check(self.lib.mg_set_operator(self._h, level, i, j, n, offs, vals))
+        self._operators[level] = table
+
+    def set_boundary(self, kind: str, k: float = 0.0):
+        self._check(self.lib.mg_set_boundary(
+            self._h, MG_BC_HELMHOLTZ_ROBIN if kind == "helmholtz_robin" else MG_BC_DIRICHLET, float(k)))
+
+    def set_coarse_solver(self, kind: str, max_iterations: int, reduction: float):
+        self._check(self.lib.mg_set_coarse_solver(
+            self._h, MG_CGS_CG if kind == "CG" else MG_CGS_BICGSTAB, int(max_iterations), float(reduction)))
+
+    def smoother_handle(self, stmt: lowering.LocalSolve) -> int:
+        key = (stmt.key(), stmt.matrix)
+        if key in self._smoother_cache:
+            return self._smoother_cache[key]
+        masks, w = smoother_tables(stmt, self.dimension, self.np_dtype)
+        m = len(stmt.slots)
+        period = (C.c_int32 * 3)(*(list(stmt.period) + [1] * (3 - len(stmt.period))))
+        slot_field = (C.c_int32 * m)(*[f for f, _ in stmt.slots])
+        slot_pos = (C.c_int32 * (m * self.dimension))(*[c for _, pos in stmt.slots for c in pos])
+        handle = C.c_int()
+        wflat = np.ascontiguousarray(w).view(np.float64).reshape(-1)
+        self._check(self.lib.mg_add_smoother(
+            self._h, stmt.level, int(stmt.jacobi), int(stmt.colored), period, m, slot_field, slot_pos,
+            len(masks), masks.ctypes.data_as(C.POINTER(C.c_uint32)), wflat.ctypes.data_as(C.POINTER(C.c_double)),
+            C.byref(handle)))
+        self._smoother_cache[key] = handle.value
+        return handle.value
+
+    def clear_programs(self):
+        """Drop captured cycles and smoother tables (between individuals)."""
+        self._check(self.lib.mg_clear_smoothers(self._h))
+        self._smoother_cache.clear()
+
+    # -- op encoding -------------------------------------------------------------------------
+    def encode(self, ops: Sequence[object], default_cycle=None) -> "C.Array":
+        flat: List[MgOp] = []
+
+        def add(kind, level, omega=1.0, src=MG_SOL, smoother=-1):
+            flat.append(MgOp(kind, level, float(omega), src, smoother))
+
+        def walk(seq):
+            for op in seq:
+                k = op.kind
+                if k == "smooth":
+                    add(MG_OP_SMOOTH, op.level, op.omega, MG_SOL, self.smoother_handle(op))
+                elif k == "residual":
+                    add(MG_OP_RESIDUAL, op.level)
+                elif k == "restrict":
+                    add(MG_OP_RESTRICT, op.level, 1.0, _FIELD[op.src or "res"])
+                elif k == "residual_restrict":
+                    add(MG_OP_RESIDUAL_RESTRICT, op.level)
+                elif k == "zero":
+                    add(MG_OP_ZERO, op.level)
+                elif k == "prolong_add":
+                    add(MG_OP_PROLONG_ADD, op.level, op.omega, _FIELD[op.src or "sol"])
+                elif k == "prolong":
+                    add(MG_OP_PROLONG, op.level, 1.0, _FIELD[op.src or "sol"])
+                elif k == "cgs":
+                    if op.level == self.min_level:
+                        add(MG_OP_CGS, op.level)
+                    else:
+                        inner = op.inner if op.inner else (default_cycle(op.level) if default_cycle else None)
+                        if inner is None:
+                            raise EngineError(f"coarse-grid solver on level {op.level} above the workspace's "
+                                              f"min level {self.min_level} needs an inner cycle")
+                        add(MG_OP_ZERO, op.level)
+                        walk(lowering.fuse(inner))
+                else:
+                    raise EngineError(f"op kind '{k}' is not executable")
+
+        walk(ops)
+        return (MgOp * len(flat))(*flat)
+
+    # -- data ------------------------------------------------------------------------------------
+    def _dense(self, level, array):
+        n = 2 ** level + 1
+        a = np.ascontiguousarray(array, dtype=self.np_dtype)
+        if a.shape != (n,) * self.dimension:
+            raise EngineError(f"array shape {a.shape} does not match level {level}")
+        return a
+
+    def upload(self, kind: str, level: int, field: int, array):
+        a = self._dense(level, array)
+        self._check(self.lib.mg_upload(self._h, _FIELD[kind], level, field, a.ctypes.data_as(C.c_void_p)))
+
+    def upload_device(self, kind: str, level: int, field: int, device_ptr: int):
+        self._check(self.lib.mg_upload_device(self._h, _FIELD[kind], level, field, C.c_void_p(device_ptr)))
+
+    def download(self, kind: str, level: int, field: int) -> np.ndarray:
+        n = 2 ** level + 1
+        out = np.empty((n,) * self.dimension, dtype=self.np_dtype)
+        self._check(self.lib.mg_download(self._h, _FIELD[kind], level, field, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def save_initial_guess(self):
+        self._check(self.lib.mg_save_initial_guess(self._h))
+
+    def restore_initial_guess(self):
+        self._check(self.lib.mg_restore_initial_guess(self._h))
+
+    # -- execution ---------------------------------------------------------------------------------
+    def exec_ops(self, ops, default_cycle=None, fused=False):
+        enc = self.encode(lowering.fuse(ops) if fused else ops, default_cycle)
+        self._check(self.lib.mg_exec_ops(self._h, enc, len(enc)))
+
+    def build_cycle(self, ops, default_cycle=None, fused=True) -> int:
+        enc = self.encode(lowering.fuse(ops) if fused else ops, default_cycle)
+        cycle = C.c_int()
+        self._check(self.lib.mg_build_cycle(self._h, enc, len(enc), C.byref(cycle)))
+        return cycle.value
+
+    def run_cycles(self, cycle: int, n: int) -> float:
+        ms = C.c_float()
+        self._check(self.lib.mg_run_cycles(self._h, cycle, n, C.byref(ms)))
+        return ms.value
+
+    def residual_norm(self, level=None) -> float:
+        out = C.c_double()
+        self._check(self.lib.mg_residual_norm(self._h, self.max_level if level is None else level, C.byref(out)))
+        return out.value
+
+    def solve(self, cycle: int, tol: float, max_its: int):
+        """-> (residual history, converged, ms)."""
+        hist = (C.c_double * (max_its + 1))()
+        n_its, conv, ms = C.c_int(), C.c_int(), C.c_float()
+        self._check(self.lib.mg_solve(self._h, cycle, tol, max_its, hist, C.byref(n_its), C.byref(conv), C.byref(ms)))
+        return list(hist[: n_its.value + 1]), bool(conv.value), ms.value
+
+    def synchronize(self):
+        self._check(self.lib.mg_synchronize(self._h))
+
+    def launch_count(self) -> int:
+        out = C.c_int64()
+        self._check(self.lib.mg_launch_count(self._h, C.byref(out)))
+        return out.value

@@ -1,0 +1,261 @@
+"""GPU parity tests: every CUDA stage and whole solves against the numpy oracle, through the C ABI.
+
+Bar (DESIGN.md "Numerical contract"): real fp64 fields bit-identical to the oracle for point
+smoothers, residual, restriction, prolongation and the coarse CG; <= 1e-12 relative for tile
+smoothers (LAPACK vs closed-form inverse is shared, summation identical -> in practice exact) and
+complex arithmetic; residual norms <= 1e-10 relative (north_star), iteration counts identical."""
+import numpy as np
+import pytest
+
+from evostencils_b200 import ir, lowering, problems
+from evostencils_b200.grammar import Grammar, v_cycle_string
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "poisson2d": (problems.POISSON_2D, 3, 6),
+    "poisson3d": (problems.POISSON_3D, 2, 4),
+    "elasticity": (problems.LINEAR_ELASTICITY_2D, 3, 5),
+    "helmholtz": (problems.HELMHOLTZ_2D, 3, 5),
+}
+
+
+def make_pair(problem, lo, hi, seed=0, use_fast=True):
+    """Engine workspace + oracle hierarchy holding identical random data on every level."""
+    from evostencils_b200.engine import Workspace
+    from oracle import driver
+    ws = Workspace(problem.dimension, lo, hi, problem.n_fields, problem.dtype, 0)
+    h = driver.make_hierarchy(problem, lo, hi)
+    p = dict(problem.parameters)
+    for level in range(lo, hi + 1):
+        ws.set_operator(level, h.operators[level])
+    ws.set_boundary(problem.boundary, p.get("k", 0.0))
+    ws.set_coarse_solver(problem.solver.cgs, problem.solver.cgs_max_iterations, problem.solver.cgs_target_reduction)
+    rng = np.random.default_rng(seed)
+    for level in range(lo, hi + 1):
+        shape = (2 ** level + 1,) * problem.dimension
+        for f in range(problem.n_fields):
+            def rnd():
+                a = rng.standard_normal(shape)
+                if problem.dtype == "c128":
+                    a = a + 1j * rng.standard_normal(shape)
+                return a.astype(h.dtype)
+            u, r, s = rnd(), rnd(), rnd()
+            interior = tuple([slice(1, -1)] * problem.dimension)
+            if level < hi:               # error equations: zero Dirichlet rim
+                rim = np.ones(shape, bool)
+                rim[interior] = False
+                u[rim] = 0
+            h.sol[level][f][...] = u
+            h.rhs[level][f][...] = r
+            h.res[level][f][...] = s
+        h.apply_bc(level, h.sol[level])
+        for f in range(problem.n_fields):
+            ws.upload("sol", level, f, h.sol[level][f])
+            ws.upload("rhs", level, f, h.rhs[level][f])
+            ws.upload("res", level, f, h.res[level][f])
+    return ws, h
+
+
+def compare(ws, h, kind, level, exact, what):
+    for f in range(h.n_fields):
+        got = ws.download(kind, level, f)
+        want = h.field(kind, level)[f]
+        if exact:
+            bad = np.argwhere(got != want)
+            assert bad.size == 0, f"{what}: {len(bad)} mismatching nodes, first {bad[:3].tolist()}, " \
+                                  f"max abs diff {np.max(np.abs(got - want))}"
+        else:
+            scale = np.max(np.abs(want)) + 1e-300
+            assert np.max(np.abs(got - want)) <= 1e-12 * scale, what
+
+
+def run_both(ws, h, ops, problem, fused=False):
+    from oracle import driver, mg_oracle
+    ws.exec_ops(ops, fused=fused)
+    mg_oracle.run_ops(h, ops, driver.settings_for(problem))
+
+
+def smoother_statements(problem, level, kind, partitioning, omega=0.8, block=None):
+    op = problem.system_operator(level, 0)
+    if kind == "collective":
+        marker = ir.ElementwiseDiagonal(op)
+    elif kind == "decoupled":
+        marker = ir.Diagonal(op)
+    else:
+        marker = ir.BlockDiagonalOperator(op, block)
+    return lowering.local_solve_statements(marker, op, level, omega, partitioning)
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_residual_restrict_prolong(name):
+    problem, lo, hi = CASES[name]
+    exact = problem.dtype == "f64"
+    ws, h = make_pair(problem, lo, hi, seed=1)
+    run_both(ws, h, [lowering.Op("residual", hi, dst="res")], problem)
+    compare(ws, h, "res", hi, exact, "residual")
+    run_both(ws, h, [lowering.Op("restrict", hi - 1, src="res", dst="rhs")], problem)
+    compare(ws, h, "rhs", hi - 1, exact, "restrict")
+    run_both(ws, h, [lowering.Op("prolong_add", hi, omega=0.55, src="sol", dst="sol")], problem)
+    compare(ws, h, "sol", hi, exact, "prolong_add")
+    # fused residual+restriction equals the two separate stages
+    ops = [lowering.Op("residual", hi, dst="res"), lowering.Op("restrict", hi - 1, src="res", dst="rhs")]
+    from oracle import driver, mg_oracle
+    mg_oracle.run_ops(h, ops, driver.settings_for(problem))
+    ws.exec_ops(ops, fused=True)
+    compare(ws, h, "rhs", hi - 1, exact, "residual_restrict")
+    run_both(ws, h, [lowering.Op("zero", hi - 1, dst="sol")], problem)
+    compare(ws, h, "sol", hi - 1, True, "zero")
+    ws.close()
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+@pytest.mark.parametrize("partitioning", ["single", "red_black"])
+@pytest.mark.parametrize("kind", ["collective", "decoupled"])
+def test_point_smoothers(name, partitioning, kind):
+    problem, lo, hi = CASES[name]
+    if kind == "decoupled" and problem.n_fields == 1:
+        pytest.skip("decoupled == collective for one field")
+    exact = problem.dtype == "f64"
+    part = ir.Single if partitioning == "single" else ir.RedBlack
+    ws, h = make_pair(problem, lo, hi, seed=2)
+    for level in (hi, lo + 1):
+        stmts = smoother_statements(problem, level, kind, part, omega=1.15)
+        for sweep in range(3):          # odd number of Jacobi sweeps exercises the ping-pong state
+            run_both(ws, h, stmts, problem)
+        compare(ws, h, "sol", level, exact, f"{kind} {partitioning} level {level}")
+    ws.close()
+
+
+@pytest.mark.parametrize("name,block", [
+    ("poisson2d", ((2, 2),)), ("poisson2d", ((1, 3),)), ("poisson2d", ((4, 1),)), ("poisson2d", ((3, 1),)),
+    ("poisson3d", ((2, 1, 2),)), ("poisson3d", ((1, 1, 3),)),
+    ("elasticity", ((2, 1), (2, 1))), ("elasticity", ((1, 2), (1, 2))),
+    ("helmholtz", ((2, 2),)),
+])
+def test_tile_smoothers(name, block):
+    problem, lo, hi = CASES[name]
+    ws, h = make_pair(problem, lo, hi, seed=3)
+    for level in (hi, lo):
+        stmts = smoother_statements(problem, level, "block", ir.Single, omega=0.6, block=block)
+        for sweep in range(2):
+            run_both(ws, h, stmts, problem)
+        compare(ws, h, "sol", level, False, f"block {block} level {level}")
+    ws.close()
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_coarse_solver_and_norm(name):
+    problem, lo, hi = CASES[name]
+    exact = problem.dtype == "f64"
+    from oracle import mg_oracle
+    ws, h = make_pair(problem, lo, hi, seed=4)
+    for level in (hi, lo):
+        got = ws.residual_norm(level)
+        want = mg_oracle.residual_norm(h, level)
+        assert abs(got - want) <= 1e-12 * want
+    run_both(ws, h, [lowering.Op("cgs", lo, src="rhs", dst="sol")], problem)
+    compare(ws, h, "sol", lo, exact, "coarse solve")
+    ws.close()
+
+
+def test_coarse_cg_on_the_config1_level():
+    """CG on 33x33 (config 1: levels 5..9) -- hundreds of iterations, still bit-identical."""
+    problem = problems.POISSON_2D
+    ws, h = make_pair(problem, 5, 6, seed=5)
+    run_both(ws, h, [lowering.Op("cgs", 5, src="rhs", dst="sol")], problem)
+    compare(ws, h, "sol", 5, True, "coarse CG 33x33")
+    ws.close()
+
+
+SOLVES = [
+    ("poisson2d_v21_rbgs", problems.POISSON_2D, 5, 9, lambda d: v_cycle_string(d, 2, 1, 21, "red_black")),
+    ("poisson2d_v22_jacobi", problems.POISSON_2D, 4, 8, lambda d: v_cycle_string(d, 2, 2, 14, "single")),
+    ("poisson2d_v11_jacobi_odd", problems.POISSON_2D, 3, 6, lambda d: v_cycle_string(d, 2, 1, 14, "single")),
+    ("poisson3d_v21_rbgs", problems.POISSON_3D, 2, 6, lambda d: v_cycle_string(d, 2, 1, 23, "red_black")),
+    ("elasticity_v21_rb", problems.LINEAR_ELASTICITY_2D, 4, 7, lambda d: v_cycle_string(d, 2, 1, 23, "red_black")),
+    ("elasticity_v11_decoupled", problems.LINEAR_ELASTICITY_2D, 4, 6,
+     lambda d: v_cycle_string(d, 1, 1, 14, "single", smoother="decoupled_jacobi")),
+]
+
+
+@pytest.mark.parametrize("name,problem,lo,hi,make", SOLVES, ids=[s[0] for s in SOLVES])
+def test_solve_residual_history(name, problem, lo, hi, make):
+    """north_star: identical iteration count, per-iteration residual norms <= 1e-10 relative."""
+    from evostencils_b200.generator import B200ProgramGenerator
+    from oracle import driver
+    grammar = Grammar(problem, lo, hi, maximum_local_system_size=4)
+    expression, _ = grammar.compile(make(hi - lo))
+    gen = B200ProgramGenerator(problem=problem, min_level=lo, max_level=hi, device=0)
+    gen.initialize_code_generation(lo, hi)
+    t, rho, n = gen.generate_and_evaluate(expression, gen.generate_storage(lo, hi, gen.finest_grid), lo, hi, "",
+                                          evaluation_samples=2)
+    program = lowering.lower(expression, lo, hi)
+    h, hist, rho_ref, n_ref = driver.solve(problem, program)
+    got, want = np.array(gen.last_residual_history), np.array(hist)
+    assert n == n_ref
+    assert got.shape == want.shape
+    assert np.all(np.abs(got - want) <= 1e-10 * np.abs(want)), np.max(np.abs(got - want) / np.abs(want))
+    assert abs(rho - rho_ref) <= 1e-10 * rho_ref
+    assert t > 0
+    # the converged iterate itself is bit-identical for real problems
+    for f in range(problem.n_fields):
+        u = gen._workspace.download("sol", hi, f)
+        assert np.array_equal(u, h.sol[hi][f])
+    gen.close()
+
+
+def test_solve_with_golden_individuals():
+    """The reference-emitted golden individuals (tests/golden) run and match the oracle."""
+    import json, os
+    from evostencils_b200.generator import B200ProgramGenerator
+    from oracle import driver
+    golden = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "lowering_golden.json")))
+    for case in ("survey_3_2", "poisson2d_block22", "poisson2d_wlike", "elasticity_block"):
+        g = golden[case]
+        problem = problems.get_problem(g["problem"])
+        lo, hi = g["min_level"], g["max_level"]
+        grammar = Grammar(problem, lo, hi, maximum_local_system_size=g["maximum_local_system_size"])
+        expression, _ = grammar.compile(g["grammar"])
+        gen = B200ProgramGenerator(problem=problem, min_level=lo, max_level=hi, device=0)
+        gen.initialize_code_generation(lo, hi)
+        t, rho, n = gen.generate_and_evaluate(expression, None, lo, hi, "", evaluation_samples=1)
+        program = lowering.lower(expression, lo, hi)
+        _, hist, rho_ref, n_ref = driver.solve(problem, program)
+        got, want = np.array(gen.last_residual_history), np.array(hist)
+        assert n == n_ref, case
+        assert got.shape == want.shape, case
+        assert np.all(np.abs(got - want) <= 1e-10 * np.abs(want)), case
+        gen.close()
+
+
+def test_determinism():
+    """Same input twice -> bitwise identical residual history (fixed reduction order)."""
+    from evostencils_b200.generator import B200ProgramGenerator
+    problem, lo, hi = problems.POISSON_2D, 4, 9
+    grammar = Grammar(problem, lo, hi)
+    expression, _ = grammar.compile(v_cycle_string(hi - lo, 2, 1, 21, "red_black"))
+    hists = []
+    for _ in range(2):
+        gen = B200ProgramGenerator(problem=problem, min_level=lo, max_level=hi, device=0)
+        gen.generate_and_evaluate(expression, None, lo, hi, "", evaluation_samples=1)
+        hists.append(list(gen.last_residual_history))
+        gen.close()
+    assert hists[0] == hists[1]
+
+
+def test_inner_default_cycle_below_the_grammar():
+    """Workspace deeper than the grammar: CGS on the grammar's coarsest level = one default cycle."""
+    from evostencils_b200.generator import B200ProgramGenerator
+    from oracle import driver
+    problem, lo, hi, engine_lo = problems.POISSON_2D, 5, 8, 2
+    grammar = Grammar(problem, lo, hi)
+    expression, _ = grammar.compile(v_cycle_string(hi - lo, 2, 1, 21, "red_black"))
+    gen = B200ProgramGenerator(problem=problem, min_level=lo, max_level=hi, device=0, engine_min_level=engine_lo)
+    t, rho, n = gen.generate_and_evaluate(expression, None, lo, hi, "", evaluation_samples=1)
+    program = lowering.lower(expression, lo, hi)
+    _, hist, rho_ref, n_ref = driver.solve(problem, program, engine_min_level=engine_lo)
+    got, want = np.array(gen.last_residual_history), np.array(hist)
+    assert n == n_ref and got.shape == want.shape
+    assert np.all(np.abs(got - want) <= 1e-10 * np.abs(want))
+    gen.close()
