@@ -53,6 +53,8 @@ extern "C" int mg_create(mg_workspace** out, int dimension, int min_level, int m
     MG_CUDA(cudaStreamCreateWithFlags(&ws->stream, cudaStreamNonBlocking));
     MG_CUDA(cudaEventCreate(&ws->ev0));
     MG_CUDA(cudaEventCreate(&ws->ev1));
+    MG_CUDA(cudaEventCreate(&ws->mark[0]));
+    MG_CUDA(cudaEventCreate(&ws->mark[1]));
     MG_CUDA(cudaMalloc(&ws->d_norm, sizeof(double)));
     MG_CUDA(cudaMallocHost(&ws->h_norm, sizeof(double)));
     ws->levels.resize(max_level - min_level + 1);
@@ -125,6 +127,9 @@ extern "C" int mg_destroy(mg_workspace* ws) {
     if (ws->h_norm) cudaFreeHost(ws->h_norm);
     if (ws->ev0) cudaEventDestroy(ws->ev0);
     if (ws->ev1) cudaEventDestroy(ws->ev1);
+    if (ws->mark[0]) cudaEventDestroy(ws->mark[0]);
+    if (ws->mark[1]) cudaEventDestroy(ws->mark[1]);
+    if (ws->flush_buf) cudaFree(ws->flush_buf);
     if (ws->stream) cudaStreamDestroy(ws->stream);
     delete ws;
     return MG_OK;

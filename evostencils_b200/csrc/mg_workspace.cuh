@@ -97,7 +97,9 @@ struct mg_workspace {
     size_t cgs_work_bytes = 0;
     double* d_norm = nullptr;                   // device scalar
     double* h_norm = nullptr;                   // pinned host scalar
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, mark[2] = {nullptr, nullptr};
+    void* flush_buf = nullptr;
+    size_t flush_bytes = 0;
     long long launches = 0;                     // kernels launched (incl. graph replays)
     long long pending_count = 0;                // kernels issued since the counter was last sampled
     bool use_fast = true;                       // specialised kernels where applicable

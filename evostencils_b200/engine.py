@@ -33,6 +33,7 @@ EXPORTED_SYMBOLS = [
     "mg_set_coarse_solver", "mg_add_smoother", "mg_clear_smoothers", "mg_upload", "mg_download",
     "mg_upload_device", "mg_save_initial_guess", "mg_restore_initial_guess", "mg_exec_ops", "mg_build_cycle",
     "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_synchronize",
+    "mg_time_ops", "mg_mark", "mg_elapsed", "mg_flush_l2", "mg_set_fast_kernels",
 ]
 
 
@@ -83,6 +84,11 @@ def load_library(path: Optional[str] = None):
     lib.mg_solve.argtypes = [vp, i32, dbl, i32, C.POINTER(dbl), C.POINTER(C.c_int), C.POINTER(C.c_int),
                              C.POINTER(C.c_float)]
     lib.mg_synchronize.argtypes = [vp]
+    lib.mg_time_ops.argtypes = [vp, C.POINTER(MgOp), i32, i32, C.POINTER(C.c_float)]
+    lib.mg_mark.argtypes = [vp, i32]
+    lib.mg_elapsed.argtypes = [vp, C.POINTER(C.c_float)]
+    lib.mg_flush_l2.argtypes = [vp, C.c_size_t]
+    lib.mg_set_fast_kernels.argtypes = [vp, i32]
     if path == LIB_PATH:
         _lib = lib
     return lib
@@ -320,3 +326,25 @@ class Workspace:
         out = C.c_int64()
         self._check(self.lib.mg_launch_count(self._h, C.byref(out)))
         return out.value
+
+    # -- measurement -------------------------------------------------------------------------------
+    def time_ops(self, ops, reps=1, default_cycle=None, fused=False) -> float:
+        """Device time (ms) of `reps` back-to-back executions of the op list."""
+        enc = self.encode(lowering.fuse(ops) if fused else ops, default_cycle)
+        ms = C.c_float()
+        self._check(self.lib.mg_time_ops(self._h, enc, len(enc), reps, C.byref(ms)))
+        return ms.value
+
+    def mark(self, which: int):
+        self._check(self.lib.mg_mark(self._h, which))
+
+    def elapsed(self) -> float:
+        ms = C.c_float()
+        self._check(self.lib.mg_elapsed(self._h, C.byref(ms)))
+        return ms.value
+
+    def flush_l2(self, nbytes=256 << 20):
+        self._check(self.lib.mg_flush_l2(self._h, nbytes))
+
+    def set_fast_kernels(self, enabled: bool):
+        self._check(self.lib.mg_set_fast_kernels(self._h, int(bool(enabled))))

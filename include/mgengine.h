@@ -130,6 +130,17 @@ int mg_solve(mg_workspace* ws, int cycle, double tol, int max_its, double* res_h
              int* n_its, int* converged, float* ms);
 int mg_synchronize(mg_workspace* ws);
 
+/* ---- measurement (CUDA events on the workspace stream) ---------------------------------- */
+/* issue the op list `reps` times back to back; *ms = device time of all repetitions */
+int mg_time_ops(mg_workspace* ws, const mg_op* ops, int n_ops, int reps, float* ms);
+/* record mark 0 / mark 1 on the workspace stream; elapsed = time between the two marks */
+int mg_mark(mg_workspace* ws, int which);
+int mg_elapsed(mg_workspace* ws, float* ms);
+/* write `bytes` bytes of scratch (allocated on first use) to evict the L2 between timed runs */
+int mg_flush_l2(mg_workspace* ws, size_t bytes);
+/* 0: generic kernels only, 1: specialised kernels where applicable (default) */
+int mg_set_fast_kernels(mg_workspace* ws, int enabled);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,7 +13,7 @@ HEADER = os.path.join(os.path.dirname(__file__), "..", "include", "mgengine.h")
 def declared_symbols():
     text = open(HEADER).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(mg_[a-z_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(mg_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_header_and_binding_agree():
