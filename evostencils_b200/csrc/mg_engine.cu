@@ -89,7 +89,7 @@ extern "C" int mg_create(mg_workspace** out, int dimension, int min_level, int m
         }
         const int rows = n_fields * (dimension == 3 ? g.n * g.n : g.n);
         lv.norm_blocks = rows < 1184 ? rows : 1184;          // 8 CTAs of 256 threads per SM x 148 SMs
-        MG_CUDA(cudaMalloc(&lv.partial, (size_t)lv.norm_blocks * ws->elem));
+        MG_CUDA(cudaMalloc(&lv.partial, (size_t)MAX_PARTIALS * ws->elem));
     }
     MG_CUDA(cudaStreamSynchronize(ws->stream));
     *out = ws;

@@ -293,9 +293,10 @@ int exec_norm(mg_workspace* ws, int level) {
         k_norm_partial<T, D, F><<<lv.norm_blocks, 256, 0, ws->stream>>>(
             lv.g, static_cast<const OperatorTable<T>*>(lv.d_op), cur_sol<T>(lv), fieldset<T>(lv.rhs),
             static_cast<T*>(lv.partial));
+        lv.norm_count = lv.norm_blocks;
         count(ws);
     }
-    k_norm_final<T><<<1, 256, 0, ws->stream>>>(static_cast<const T*>(lv.partial), lv.norm_blocks, ws->d_norm);
+    k_norm_final<T><<<1, 256, 0, ws->stream>>>(static_cast<const T*>(lv.partial), lv.norm_count, ws->d_norm);
     count(ws);
     return MG_OK;
 }

@@ -1,0 +1,349 @@
+// mg_fast2d.cuh -- specialised 2D kernels for scalar real 5-point star stencils (2D Poisson).
+//
+// Design (B200, HBM-bound; 24 B/DoF for a sweep, 18 B/DoF for the inter-grid stages):
+//   * every thread owns two adjacent columns (one aligned 16-byte double2 per row and array);
+//     a CTA of NT threads covers a strip of 2*NT columns and marches down `rows` rows keeping the
+//     live rows of u in registers -> each u value is read from memory once per CTA (plus the halo
+//     rows of the strip segment), f once, the result written once;
+//   * left/right neighbours come from the adjacent lane by warp shuffle; only the two edge lanes of
+//     a warp issue extra 8-byte loads (L1/L2 hits: the neighbouring warp streams those lines);
+//   * loads of the next row are issued one iteration ahead (software prefetch);
+//   * strips cover the columns [0, n-1) = 2^L exactly, so there is no partially filled CTA; the
+//     last Dirichlet column n-1 is handled by the thread that owns column n-3;
+//   * operand order is the canonical stencil order S, W, C, E, N with separate multiply and add
+//     (the translation unit is compiled with --fmad=false), so results are bit-identical to the
+//     generic kernels and to the oracle.
+// Applicable when (n-1) is a multiple of 2*NT (levels >= 8 for NT = 128); smaller levels are
+// latency-bound and use the generic kernels.
+#pragma once
+#include "mg_kernels_generic.cuh"
+
+namespace mg {
+
+struct Star2D {
+    double cs, cw, cc;     // south/north, west/east, centre coefficients
+};
+
+__device__ __forceinline__ double2 ld2(const double* p) { return *reinterpret_cast<const double2*>(p); }
+__device__ __forceinline__ void st2(double* p, double2 v) { *reinterpret_cast<double2*>(p) = v; }
+
+// (A u) at one node, canonical order S, W, C, E, N
+__device__ __forceinline__ double star_at(const Star2D& s, double S, double W, double Cc, double E, double N) {
+    double a = s.cs * S;
+    a = a + s.cw * W;
+    a = a + s.cc * Cc;
+    a = a + s.cw * E;
+    a = a + s.cs * N;
+    return a;
+}
+
+// left neighbour of column x0 and right neighbour of column x0+1 in `row` (uc = own two values)
+__device__ __forceinline__ void row_neighbours(const double* __restrict__ row, int x0, double2 uc, int lane,
+                                               double& left, double& right) {
+    left = __shfl_up_sync(0xffffffffu, uc.y, 1);
+    right = __shfl_down_sync(0xffffffffu, uc.x, 1);
+    if (lane == 0) left = x0 > 0 ? row[x0 - 1] : 0.0;
+    if (lane == 31) right = row[x0 + 2];
+}
+
+enum { STAR_JACOBI = 0, STAR_RESIDUAL = 1, STAR_NORM = 2 };
+
+// MODE 0: out = u + w (f - A u) on interior nodes, out = u on the boundary   (Jacobi sweep)
+// MODE 1: out = f - A u on interior nodes                                      (residual)
+// MODE 2: partial[cta] = sum (f - A u)^2                                        (residual norm)
+template <int MODE, int NT>
+__global__ void __launch_bounds__(NT) k_star2d(Geom g, Star2D s, const double* __restrict__ u,
+                                                const double* __restrict__ f, double* __restrict__ out, double w,
+                                                int rows, double* __restrict__ partial) {
+    const int lane = threadIdx.x & 31;
+    const int x0 = (blockIdx.x * NT + threadIdx.x) * 2;       // 0 <= x0 <= n-3
+    const int n = g.n;
+    const long long pitch = g.pitch;
+    const int y_begin = 1 + blockIdx.y * rows;
+    int y_end = y_begin + rows;
+    if (y_end > n - 1) y_end = n - 1;
+    const bool in0 = x0 >= 1;                                  // column x0+1 is always interior
+    const bool last = x0 == n - 3;                             // also owns the Dirichlet column n-1
+    double acc = 0.0;
+    const double* p = u + (long long)(y_begin - 1) * pitch + x0;
+    double2 um = ld2(p);
+    double2 uc = ld2(p + pitch);
+    double2 un = ld2(p + 2 * pitch);
+    double2 fc = ld2(f + (long long)y_begin * pitch + x0);
+    if (MODE == STAR_JACOBI && blockIdx.y == 0) {              // Dirichlet row 0
+        st2(out + x0, um);
+        if (last) out[n - 1] = u[n - 1];
+    }
+    for (int y = y_begin; y < y_end; ++y) {
+        const long long base = (long long)y * pitch + x0;
+        double2 u2 = ld2(u + base + 2 * pitch);                // prefetch row y+2 (guard rows past the array)
+        double2 fn = ld2(f + base + pitch);                    // prefetch f row y+1
+        double left, right;
+        row_neighbours(u + (long long)y * pitch, x0, uc, lane, left, right);
+        const double r0 = fc.x - star_at(s, um.x, left, uc.x, uc.y, un.x);
+        const double r1 = fc.y - star_at(s, um.y, uc.x, uc.y, right, un.y);
+        if (MODE == STAR_JACOBI) {
+            double2 o;
+            o.x = in0 ? uc.x + w * r0 : uc.x;
+            o.y = uc.y + w * r1;
+            st2(out + base, o);
+            if (last) out[base + 2] = right;                   // Dirichlet column n-1
+        } else if (MODE == STAR_RESIDUAL) {
+            if (in0) {
+                double2 o;
+                o.x = r0; o.y = r1;
+                st2(out + base, o);
+            } else {
+                out[base + 1] = r1;
+            }
+        } else {
+            if (in0) acc = acc + r0 * r0;
+            acc = acc + r1 * r1;
+        }
+        um = uc; uc = un; un = u2; fc = fn;
+    }
+    if (MODE == STAR_JACOBI && y_end == n - 1) {               // Dirichlet row n-1 (uc holds it now)
+        st2(out + (long long)(n - 1) * pitch + x0, uc);
+        if (last) out[(long long)(n - 1) * pitch + n - 1] = u[(long long)(n - 1) * pitch + n - 1];
+    }
+    if (MODE == STAR_NORM) {
+        __shared__ double s32[32];
+        double v = warp_sum<double>(acc);
+        if (lane == 0) s32[threadIdx.x >> 5] = v;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = s32[0];
+            for (int i = 1; i < NT / 32; ++i) t = t + s32[i];
+            partial[blockIdx.y * gridDim.x + blockIdx.x] = t;
+        }
+    }
+}
+
+// ---- fused two-colour Gauss-Seidel sweep, out of place ------------------------------------------
+// R_j = row j after the red half-sweep (red nodes (x+j) even updated from the old black
+// neighbours); the black half-sweep of row y reads R_{y-1}, R_y, R_{y+1}.  One pass over memory:
+// reads u (+4 halo rows per strip segment) and f (+2), writes the finished row.  The red values a
+// warp needs just outside its 64 columns are recomputed by its edge lanes.
+__device__ __forceinline__ double red_value(const Star2D& s, double w, double S, double W, double Cc, double E,
+                                            double N, double fv) {
+    return Cc + w * (fv - star_at(s, S, W, Cc, E, N));
+}
+
+template <int NT>
+__global__ void __launch_bounds__(NT) k_rbgs2d(Geom g, Star2D s, const double* __restrict__ u,
+                                                const double* __restrict__ f, double* __restrict__ out, double w,
+                                                int rows) {
+    const int lane = threadIdx.x & 31;
+    const int x0 = (blockIdx.x * NT + threadIdx.x) * 2;       // even column; x0+1 odd
+    const int n = g.n;
+    const long long pitch = g.pitch;
+    const int y_begin = 1 + blockIdx.y * rows;
+    int y_end = y_begin + rows;
+    if (y_end > n - 1) y_end = n - 1;
+    const bool in0 = x0 >= 1;
+    const bool last = x0 == n - 3;
+
+    // R row j from old rows j-1, j, j+1 (interior rows only; boundary rows are returned unchanged)
+    auto red_row = [&](int j, double2 om, double2 oc, double2 on, double2 fj) -> double2 {
+        double left, right;
+        row_neighbours(u + (long long)j * pitch, x0, oc, lane, left, right);
+        double2 r = oc;
+        if (j >= 1 && j <= n - 2) {
+            if ((j & 1) == 0) {                                 // column x0 (even) is red on even rows
+                if (in0) r.x = red_value(s, w, om.x, left, oc.x, oc.y, on.x, fj.x);
+            } else {                                            // column x0+1 (odd) is red on odd rows
+                r.y = red_value(s, w, om.y, oc.x, oc.y, right, on.y, fj.y);
+            }
+        }
+        return r;
+    };
+    // red value at a single halo node (x, j), recomputed from global memory
+    auto red_halo = [&](int x, int j) -> double {
+        const double* c = u + (long long)j * pitch + x;
+        if (x < 1 || x > n - 2 || j < 1 || j > n - 2) return c[0];
+        return red_value(s, w, c[-pitch], c[-1], c[0], c[1], c[pitch], f[(long long)j * pitch + x]);
+    };
+
+    const double* p = u + (long long)(y_begin - 2) * pitch + x0;      // row y_begin-2 >= -1: guard row
+    double2 o0 = ld2(p), o1 = ld2(p + pitch), o2 = ld2(p + 2 * pitch), o3 = ld2(p + 3 * pitch);
+    const double* fp = f + (long long)(y_begin - 1) * pitch + x0;
+    double2 f0 = ld2(fp), f1 = ld2(fp + pitch);
+    double2 Rm = red_row(y_begin - 1, o0, o1, o2, f0);               // R_{y-1}
+    double2 Rc = red_row(y_begin, o1, o2, o3, f1);                    // R_y
+    if (blockIdx.y == 0) {                                            // Dirichlet row 0
+        st2(out + x0, Rm);
+        if (last) out[n - 1] = u[n - 1];
+    }
+    // o2 = old row y, o3 = old row y+1 from here on
+    double2 fy = f1;
+    for (int y = y_begin; y < y_end; ++y) {
+        const long long base = (long long)y * pitch + x0;
+        double2 o4 = ld2(u + base + 2 * pitch);                       // old row y+2
+        double2 fn = ld2(f + base + pitch);                           // f row y+1
+        double2 Rn = red_row(y + 1, o2, o3, o4, fn);                  // R_{y+1}
+        // neighbours of R_y outside this thread
+        double left = __shfl_up_sync(0xffffffffu, Rc.y, 1);
+        double right = __shfl_down_sync(0xffffffffu, Rc.x, 1);
+        if (y & 1) {                       // black node: column x0 (even) on odd rows -> needs R at x0-1
+            if (lane == 0) left = x0 > 0 ? red_halo(x0 - 1, y) : 0.0;
+        } else {                           // black node: column x0+1 (odd) on even rows -> needs R at x0+2
+            if (lane == 31) right = red_halo(x0 + 2, y);
+        }
+        double2 o = Rc;
+        if (y & 1) {
+            if (in0) o.x = Rc.x + w * (fy.x - star_at(s, Rm.x, left, Rc.x, Rc.y, Rn.x));
+        } else {
+            o.y = Rc.y + w * (fy.y - star_at(s, Rm.y, Rc.x, Rc.y, right, Rn.y));
+        }
+        st2(out + base, o);
+        if (last) out[base + 2] = u[base + 2];                        // Dirichlet column n-1
+        Rm = Rc; Rc = Rn; o2 = o3; o3 = o4; fy = fn;
+    }
+    if (y_end == n - 1) {                                             // Dirichlet row n-1: Rc = R_{n-1} = old
+        st2(out + (long long)(n - 1) * pitch + x0, Rc);
+        if (last) out[(long long)(n - 1) * pitch + n - 1] = u[(long long)(n - 1) * pitch + n - 1];
+    }
+}
+
+// ---- fused residual + full-weighting restriction ----------------------------------------------------
+// Thread owns coarse columns X0, X0+1 (one double2 store per coarse row) = fine columns 2X0 .. 2X0+3;
+// the fine residual at column 2X0-1 comes from the left lane (its column 2X0'+3), lane 0 recomputes it.
+// The CTA marches over fine rows; every fine residual row is computed once and feeds the coarse rows
+// above and below.  Accumulation order per coarse node: fine rows 2Y-1, 2Y, 2Y+1, columns -1, 0, +1
+// (memory order), term = (w_x * w_y) * r  -- identical to the generic kernel.
+template <int NT>
+__global__ void __launch_bounds__(NT) k_resrestrict2d(Geom gc, Geom gf, Star2D s, const double* __restrict__ u,
+                                                       const double* __restrict__ f, double* __restrict__ coarse,
+                                                       int rows) {
+    const int lane = threadIdx.x & 31;
+    const int X0 = (blockIdx.x * NT + threadIdx.x) * 2;        // coarse columns X0, X0+1 ; X0 <= nc-3
+    const int x0 = 2 * X0;                                      // fine columns x0 .. x0+3
+    const int nc = gc.n, nf = gf.n;
+    const long long pf = gf.pitch, pc = gc.pitch;
+    const int Y_begin = 1 + blockIdx.y * rows;
+    int Y_end = Y_begin + rows;
+    if (Y_end > nc - 1) Y_end = nc - 1;
+    const bool in0 = X0 >= 1;                                   // coarse column X0 interior; X0+1 always is
+
+    // residuals of fine row y at columns x0-1 .. x0+3 (r[0] = column x0-1)
+    struct Row { double2 a, b; };
+    auto load_row = [&](int y) -> Row {
+        Row r;
+        const double* q = u + (long long)y * pf + x0;
+        r.a = ld2(q); r.b = ld2(q + 2);
+        return r;
+    };
+    auto residual_row = [&](int y, const Row& m, const Row& c, const Row& n_, double r[5]) {
+        const double* frow = f + (long long)y * pf + x0;
+        double2 fa = ld2(frow), fb = ld2(frow + 2);
+        const double* urow = u + (long long)y * pf;
+        // own columns x0 .. x0+3
+        double wl = __shfl_up_sync(0xffffffffu, c.b.y, 1);      // u at x0-1
+        double er = __shfl_down_sync(0xffffffffu, c.a.x, 1);    // u at x0+4
+        if (lane == 0) wl = x0 > 0 ? urow[x0 - 1] : 0.0;
+        if (lane == 31) er = urow[x0 + 4];
+        r[1] = fa.x - star_at(s, m.a.x, wl, c.a.x, c.a.y, n_.a.x);
+        r[2] = fa.y - star_at(s, m.a.y, c.a.x, c.a.y, c.b.x, n_.a.y);
+        r[3] = fb.x - star_at(s, m.b.x, c.a.y, c.b.x, c.b.y, n_.b.x);
+        r[4] = fb.y - star_at(s, m.b.y, c.b.x, c.b.y, er, n_.b.y);
+        double rl = __shfl_up_sync(0xffffffffu, r[4], 1);       // residual at x0-1 from the left lane
+        if (lane == 0) {
+            rl = 0.0;
+            if (x0 > 0) {
+                const double* c1 = urow + x0 - 1;
+                rl = f[(long long)y * pf + x0 - 1] - star_at(s, c1[-pf], c1[-1], c1[0], c.a.x, c1[pf]);
+            }
+        }
+        r[0] = rl;
+    };
+
+    int y = 2 * Y_begin - 1;                                    // first fine row needed
+    Row um = load_row(y - 1), uc = load_row(y), un = load_row(y + 1);
+    double rm[5];
+    residual_row(y, um, uc, un, rm);                            // fine row 2Y-1
+    for (int Y = Y_begin; Y < Y_end; ++Y) {
+        // fine rows 2Y and 2Y+1
+        Row u2 = load_row(2 * Y + 1), u3 = load_row(2 * Y + 2);
+        double rc[5], rn[5];
+        residual_row(2 * Y, uc, un, u2, rc);
+        residual_row(2 * Y + 1, un, u2, u3, rn);
+        double2 o;
+        {
+            double a = 0.0625 * rm[0];
+            a = a + 0.125 * rm[1];
+            a = a + 0.0625 * rm[2];
+            a = a + 0.125 * rc[0];
+            a = a + 0.25 * rc[1];
+            a = a + 0.125 * rc[2];
+            a = a + 0.0625 * rn[0];
+            a = a + 0.125 * rn[1];
+            a = a + 0.0625 * rn[2];
+            o.x = a;
+            double b = 0.0625 * rm[2];
+            b = b + 0.125 * rm[3];
+            b = b + 0.0625 * rm[4];
+            b = b + 0.125 * rc[2];
+            b = b + 0.25 * rc[3];
+            b = b + 0.125 * rc[4];
+            b = b + 0.0625 * rn[2];
+            b = b + 0.125 * rn[3];
+            b = b + 0.0625 * rn[4];
+            o.y = b;
+        }
+        double* dst = coarse + (long long)Y * pc + X0;
+        if (in0) st2(dst, o); else dst[1] = o.y;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) rm[k] = rn[k];
+        uc = u2; un = u3;
+    }
+    (void)nf;
+}
+
+// ---- fused prolongation + correction: u += omega * (P e) --------------------------------------------
+// Thread owns fine columns x0 .. x0+3 (x0 = 4 t) <- coarse columns X0 = x0/2, X0+1 and, for the odd fine
+// column x0+3, X0+2 (from the right lane; lane 31 loads it).  The CTA marches over coarse rows: coarse
+// row Y and Y+1 give the fine rows 2Y (even) and 2Y+1 (odd).  In place (each fine node is touched by
+// exactly one thread).
+template <int NT>
+__global__ void __launch_bounds__(NT) k_prolong2d(Geom gf, Geom gc, const double* __restrict__ e,
+                                                   double* __restrict__ u, double omega, int rows) {
+    const int lane = threadIdx.x & 31;
+    const int x0 = (blockIdx.x * NT + threadIdx.x) * 4;        // fine columns x0..x0+3 ; x0 <= nf-5
+    const int X0 = x0 >> 1;
+    const int nf = gf.n, nc = gc.n;
+    const long long pf = gf.pitch, pc = gc.pitch;
+    const int Y_begin = blockIdx.y * rows;                      // coarse rows [Y_begin, Y_end)
+    int Y_end = Y_begin + rows;
+    if (Y_end > nc - 1) Y_end = nc - 1;                         // coarse row nc-1 only serves fine row nf-2
+    auto load_c = [&](int Y, double& c0, double& c1, double& c2) {
+        const double* row = e + (long long)Y * pc;
+        double2 v = ld2(row + X0);
+        c0 = v.x; c1 = v.y;
+        c2 = __shfl_down_sync(0xffffffffu, v.x, 1);
+        if (lane == 31) c2 = row[X0 + 2];
+    };
+    auto update = [&](int y, double p0, double p1, double p2, double p3) {
+        double* q = u + (long long)y * pf + x0;
+        double2 a = ld2(q), b = ld2(q + 2);
+        if (x0 >= 1) a.x = a.x + omega * p0;                    // column 0 is Dirichlet
+        a.y = a.y + omega * p1;
+        b.x = b.x + omega * p2;
+        b.y = b.y + omega * p3;
+        st2(q, a); st2(q + 2, b);
+    };
+    double a0, a1, a2;
+    load_c(Y_begin, a0, a1, a2);
+    for (int Y = Y_begin; Y < Y_end; ++Y) {
+        double b0, b1, b2;
+        load_c(Y + 1, b0, b1, b2);
+        if (Y >= 1)                                             // even fine row 2Y (row 0 is Dirichlet)
+            update(2 * Y, a0, 0.5 * (a0 + a1), a1, 0.5 * (a1 + a2));
+        // odd fine row 2Y+1 <= nf-2
+        update(2 * Y + 1, 0.5 * (a0 + b0), 0.25 * (((a0 + a1) + b0) + b1), 0.5 * (a1 + b1),
+               0.25 * (((a1 + a2) + b1) + b2));
+        a0 = b0; a1 = b1; a2 = b2;
+    }
+    (void)nf;
+}
+
+}  // namespace mg

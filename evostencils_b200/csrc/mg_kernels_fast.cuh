@@ -1,22 +1,120 @@
-// mg_kernels_fast.cuh -- specialised stage kernels for the hot configurations (scalar real
-// (2d+1)-point star stencils: 2D/3D Poisson).  Each fast_* hook returns true when it issued the
-// stage; false falls through to the generic kernel.  Results are bit-identical to the generic
-// kernels (same operand order, no FMA contraction).
+// mg_kernels_fast.cuh -- dispatch of the specialised stage kernels (scalar real star stencils:
+// 2D/3D Poisson).  Each fast_* hook returns true when it issued the stage; false falls through to
+// the generic kernel.  Results are bit-identical to the generic kernels (same operand order, no
+// FMA contraction), which tests/test_gpu_parity.py checks against the oracle on both paths.
 #pragma once
-#include "mg_kernels_generic.cuh"
+#include <cstdlib>
+
+#include "mg_fast2d.cuh"
 #include "mg_workspace.cuh"
 
 namespace mg {
 
+constexpr int FAST_NT = 128;            // threads per CTA of the marching kernels
+constexpr int MAX_PARTIALS = 16384;     // capacity of Level::partial
+
+inline int tunable(const char* name, int dflt) {
+    const char* v = std::getenv(name);
+    return v ? std::atoi(v) : dflt;
+}
+
+inline void fast_count(mg_workspace* ws, int k = 1) { ws->pending_count += k; }
+
+template <int D>
+inline bool star_level_ok(const mg_workspace* ws, const Level& lv, int cols_per_thread) {
+    return D == 2 && ws->dtype == MG_F64 && ws->n_fields == 1 && lv.star &&
+           (lv.g.n - 1) % (cols_per_thread * FAST_NT) == 0;
+}
+
+inline Star2D star2d(const Level& lv) {
+    Star2D s;
+    s.cs = lv.star_y; s.cw = lv.star_x; s.cc = lv.star_c;
+    return s;
+}
+
+inline dim3 strip_grid(const Level& lv, int cols_per_thread, int rows, int n_rows) {
+    return dim3((lv.g.n - 1) / (cols_per_thread * FAST_NT), (n_rows + rows - 1) / rows, 1);
+}
+
 template <typename T, int D, int F>
-inline bool fast_smooth(mg_workspace*, Level&, Smoother&) { return false; }
+inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm) {
+    if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
+        if (!star_level_ok<D>(ws, lv, 2) || !sm.point || sm.m != 1) return false;
+        static const int rows_j = tunable("MG_JACOBI_ROWS", 32), rows_rb = tunable("MG_RBGS_ROWS", 32);
+        const double* src = static_cast<const double*>(lv.sol[lv.cur[0]][0]);
+        double* dst = static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]);
+        const double* rhs = static_cast<const double*>(lv.rhs[0]);
+        if (sm.colored) {
+            k_rbgs2d<FAST_NT><<<strip_grid(lv, 2, rows_rb, lv.g.n - 2), FAST_NT, 0, ws->stream>>>(
+                lv.g, star2d(lv), src, rhs, dst, sm.w00, rows_rb);
+        } else {
+            k_star2d<STAR_JACOBI, FAST_NT><<<strip_grid(lv, 2, rows_j, lv.g.n - 2), FAST_NT, 0, ws->stream>>>(
+                lv.g, star2d(lv), src, rhs, dst, sm.w00, rows_j, nullptr);
+        }
+        lv.cur[0] ^= 1;
+        fast_count(ws);
+        return true;
+    }
+    return false;
+}
+
 template <typename T, int D, int F>
-inline bool fast_residual(mg_workspace*, Level&) { return false; }
+inline bool fast_residual(mg_workspace* ws, Level& lv) {
+    if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
+        if (!star_level_ok<D>(ws, lv, 2)) return false;
+        static const int rows = tunable("MG_RESIDUAL_ROWS", 32);
+        k_star2d<STAR_RESIDUAL, FAST_NT><<<strip_grid(lv, 2, rows, lv.g.n - 2), FAST_NT, 0, ws->stream>>>(
+            lv.g, star2d(lv), static_cast<const double*>(lv.sol[lv.cur[0]][0]), static_cast<const double*>(lv.rhs[0]),
+            static_cast<double*>(lv.res[0]), 0.0, rows, nullptr);
+        fast_count(ws);
+        return true;
+    }
+    return false;
+}
+
 template <typename T, int D, int F>
-inline bool fast_residual_restrict(mg_workspace*, Level&, Level&) { return false; }
+inline bool fast_norm(mg_workspace* ws, Level& lv) {
+    if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
+        if (!star_level_ok<D>(ws, lv, 2)) return false;
+        static const int rows = tunable("MG_NORM_ROWS", 32);
+        dim3 grid = strip_grid(lv, 2, rows, lv.g.n - 2);
+        if ((int)(grid.x * grid.y) > MAX_PARTIALS) return false;
+        k_star2d<STAR_NORM, FAST_NT><<<grid, FAST_NT, 0, ws->stream>>>(
+            lv.g, star2d(lv), static_cast<const double*>(lv.sol[lv.cur[0]][0]), static_cast<const double*>(lv.rhs[0]),
+            nullptr, 0.0, rows, static_cast<double*>(lv.partial));
+        lv.norm_count = grid.x * grid.y;
+        fast_count(ws);
+        return true;
+    }
+    return false;
+}
+
 template <typename T, int D, int F>
-inline bool fast_prolong_add(mg_workspace*, Level&, Level&, const FieldSet<T>&, double) { return false; }
+inline bool fast_residual_restrict(mg_workspace* ws, Level& lf, Level& lc) {
+    if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
+        if (!star_level_ok<D>(ws, lf, 4) || (lc.g.n - 1) % (2 * FAST_NT) != 0) return false;
+        static const int rows = tunable("MG_RESTRICT_ROWS", 16);
+        k_resrestrict2d<FAST_NT><<<strip_grid(lc, 2, rows, lc.g.n - 2), FAST_NT, 0, ws->stream>>>(
+            lc.g, lf.g, star2d(lf), static_cast<const double*>(lf.sol[lf.cur[0]][0]),
+            static_cast<const double*>(lf.rhs[0]), static_cast<double*>(lc.rhs[0]), rows);
+        fast_count(ws);
+        return true;
+    }
+    return false;
+}
+
 template <typename T, int D, int F>
-inline bool fast_norm(mg_workspace*, Level&) { return false; }
+inline bool fast_prolong_add(mg_workspace* ws, Level& lf, Level& lc, const FieldSet<T>& src, double omega) {
+    if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
+        if (ws->dtype != MG_F64 || (lf.g.n - 1) % (4 * FAST_NT) != 0) return false;
+        static const int rows = tunable("MG_PROLONG_ROWS", 16);
+        k_prolong2d<FAST_NT><<<strip_grid(lf, 4, rows, lc.g.n - 1), FAST_NT, 0, ws->stream>>>(
+            lf.g, lc.g, reinterpret_cast<const double*>(src.p[0]), static_cast<double*>(lf.sol[lf.cur[0]][0]), omega,
+            rows);
+        fast_count(ws);
+        return true;
+    }
+    return false;
+}
 
 }  // namespace mg

@@ -53,6 +53,7 @@ struct Level {
     double star_c = 0, star_x = 0, star_y = 0, star_z = 0;
     void* partial = nullptr;            // norm partials
     int norm_blocks = 0;
+    int norm_count = 0;                 // partials written by the last norm kernel
 };
 
 struct Smoother {

@@ -259,3 +259,59 @@ def test_inner_default_cycle_below_the_grammar():
     assert n == n_ref and got.shape == want.shape
     assert np.all(np.abs(got - want) <= 1e-10 * np.abs(want))
     gen.close()
+
+
+# ---- specialised (row-marching) 2D kernels: levels >= 8 -------------------------------------------
+
+@pytest.mark.parametrize("lo,hi", [(7, 9), (9, 10)])
+def test_fast_2d_stages_bit_identical(lo, hi):
+    problem = problems.POISSON_2D
+    ws, h = make_pair(problem, lo, hi, seed=7)
+    run_both(ws, h, [lowering.Op("residual", hi, dst="res")], problem)
+    compare(ws, h, "res", hi, True, "fast residual")
+    from oracle import mg_oracle
+    got, want = ws.residual_norm(hi), mg_oracle.residual_norm(h, hi)
+    assert abs(got - want) <= 1e-12 * want
+    for partitioning in (ir.Single, ir.RedBlack):
+        for level in (hi, hi - 1):
+            stmts = smoother_statements(problem, level, "collective", partitioning, omega=1.15)
+            for sweep in range(3):
+                run_both(ws, h, stmts, problem)
+            compare(ws, h, "sol", level, True, f"fast smoother {partitioning.get_name()} level {level}")
+    ops = [lowering.Op("residual", hi, dst="res"), lowering.Op("restrict", hi - 1, src="res", dst="rhs")]
+    from oracle import driver
+    mg_oracle.run_ops(h, ops, driver.settings_for(problem))
+    ws.exec_ops(ops, fused=True)
+    compare(ws, h, "rhs", hi - 1, True, "fast residual_restrict")
+    run_both(ws, h, [lowering.Op("prolong_add", hi, omega=0.55, src="sol", dst="sol")], problem)
+    compare(ws, h, "sol", hi, True, "fast prolong_add")
+    ws.close()
+
+
+def test_fast_and_generic_kernels_agree_on_a_solve():
+    from evostencils_b200.generator import B200ProgramGenerator
+    from oracle import driver
+    problem, lo, hi = problems.POISSON_2D, 5, 10
+    grammar = Grammar(problem, lo, hi)
+    for string in (v_cycle_string(hi - lo, 2, 1, 21, "red_black"), v_cycle_string(hi - lo, 2, 1, 14, "single")):
+        expression, _ = grammar.compile(string)
+        hists = []
+        for fast in (True, False):
+            gen = B200ProgramGenerator(problem=problem, min_level=lo, max_level=hi, device=0)
+            gen.initialize_code_generation(lo, hi)
+            gen._workspace.set_fast_kernels(fast)
+            gen.generate_and_evaluate(expression, None, lo, hi, "", evaluation_samples=1)
+            hists.append(np.array(gen.last_residual_history))
+            u = gen._workspace.download("sol", hi, 0)
+            gen.close()
+            if fast:
+                u_fast = u
+            else:
+                assert np.array_equal(u, u_fast)
+        assert hists[0].shape == hists[1].shape
+        assert np.allclose(hists[0], hists[1], rtol=1e-12, atol=0)
+        program = lowering.lower(expression, lo, hi)
+        h, hist, rho, n = driver.solve(problem, program)
+        assert len(hist) == len(hists[0])
+        assert np.all(np.abs(hists[0] - np.array(hist)) <= 1e-10 * np.abs(hist))
+        assert np.array_equal(u_fast, h.sol[hi][0])
