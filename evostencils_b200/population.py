@@ -1,0 +1,132 @@
+"""Population-level sharding of fitness evaluations over the GPUs of one node.
+
+Mirrors the reference's only parallelism strategy: data-parallel evaluation of the GP population
+over MPI ranks (/root/reference/evostencils/optimization/program.py:285-310 `allgather`/`gather`,
+:478-502 initial population, :534-535 re-evaluation striding `i % nprocs == rank`).  Here one
+process per GPU (torchrun) owns one `B200ProgramGenerator`; individual `i` of the de-duplicated
+population is evaluated by rank `i % world`; the three doubles per individual
+`(time_ms, convergence_factor, iterations)` are combined on every rank.  Evaluations are
+independent, so there is no data-path collective -- only this result exchange.
+
+`torch.distributed` is plumbing: NCCL on the GPU box, gloo in the CPU tests.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional, Sequence, Tuple
+
+Result = Tuple[float, float, float]
+
+
+def shard_indices(n_items: int, rank: int, world: int) -> List[int]:
+    """Indices owned by `rank`: the reference's striding (program.py:534-535)."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("bad rank/world")
+    return list(range(rank, n_items, world))
+
+
+def deduplicate(strings: Sequence[str]):
+    """Unique individuals in first-seen order + the map back.  The reference's cache key is
+    `str(individual)` (program.py:191-204): equal strings are evaluated once."""
+    unique: List[str] = []
+    index = {}
+    back = []
+    for s in strings:
+        if s not in index:
+            index[s] = len(unique)
+            unique.append(s)
+        back.append(index[s])
+    return unique, back
+
+
+def _world(group=None):
+    try:
+        import torch.distributed as dist
+    except Exception:       # pragma: no cover
+        return 0, 1, None
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(group), dist.get_world_size(group), dist
+    return 0, 1, None
+
+
+def gather_results(local: dict, n_items: int, group=None, device=None) -> List[Result]:
+    """Combine `{index: (t, rho, n)}` of every rank into the full list on every rank.
+
+    Each slot is written by exactly one rank and is 0.0 elsewhere, so the SUM all-reduce is exact
+    (x + 0.0 == x for every finite x and for +inf) and independent of the reduction order."""
+    rank, world, dist = _world(group)
+    if world == 1:
+        missing = [i for i in range(n_items) if i not in local]
+        if missing:
+            raise ValueError(f"results missing for individuals {missing[:5]}")
+        return [tuple(float(v) for v in local[i]) for i in range(n_items)]
+    import torch
+    if device is None:
+        device = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+    buf = torch.zeros((n_items, 4), dtype=torch.float64)
+    for i, r in local.items():
+        buf[i, 0], buf[i, 1], buf[i, 2], buf[i, 3] = float(r[0]), float(r[1]), float(r[2]), 1.0
+    buf = buf.to(device)
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+    buf = buf.cpu()
+    counts = buf[:, 3]
+    if not bool((counts == 1.0).all()):
+        bad = [i for i in range(n_items) if counts[i] != 1.0]
+        raise RuntimeError(f"individuals evaluated {counts[bad[0]].item():.0f} times (expected once): {bad[:5]}")
+    return [(buf[i, 0].item(), buf[i, 1].item(), buf[i, 2].item()) for i in range(n_items)]
+
+
+def evaluate_population(evaluate: Callable[[str], Result], strings: Sequence[str], group=None, device=None,
+                        costs: Optional[Sequence[float]] = None) -> List[Result]:
+    """Evaluate every individual once across the ranks of `group`; every rank gets all results.
+
+    `evaluate(grammar_string) -> (time_ms, rho, n)` runs on this rank's GPU.  With `costs`
+    (e.g. op-list byte counts) the unique individuals are dealt longest-first so that the ranks
+    finish together; without, plain `i % world` striding."""
+    rank, world, _ = _world(group)
+    unique, back = deduplicate(strings)
+    order = list(range(len(unique)))
+    if costs is not None:
+        if len(costs) != len(strings):
+            raise ValueError("one cost per individual expected")
+        first = {}
+        for i, b in enumerate(back):
+            first.setdefault(b, costs[i])
+        order.sort(key=lambda u: (-first[u], u))
+    mine = [order[k] for k in shard_indices(len(order), rank, world)]
+    local = {u: evaluate(unique[u]) for u in mine}
+    results = gather_results(local, len(unique), group, device)
+    return [results[b] for b in back]
+
+
+def make_evaluator(generator, grammar, min_level: int, max_level: int, evaluation_samples: int = 1,
+                   infinity: float = 1e100) -> Callable[[str], Result]:
+    """`evaluate` for `evaluate_population`: grammar string -> Cycle graph -> generate_and_evaluate
+    (the path of program.py:904-929 `generate_and_evaluate_program_from_grammar_representation`)."""
+    def evaluate(string: str) -> Result:
+        try:
+            expression, _ = grammar.compile(string)
+        except Exception:
+            return (infinity, infinity, infinity)
+        return tuple(generator.generate_and_evaluate(expression, None, min_level, max_level, "",
+                                                     infinity=infinity, evaluation_samples=evaluation_samples))
+    return evaluate
+
+
+def batched_map(generator, grammar, min_level, max_level, evaluation_samples=1, group=None, infinity=1e100):
+    """A `toolbox.map` replacement (the reference's extension point, program.py:491, 577):
+    `toolbox.register("map", batched_map(...))` makes one generation's evaluations run sharded.
+    The mapped function is ignored for individuals given as grammar strings / PrimitiveTrees:
+    they are evaluated through `generate_and_evaluate` and returned as (rho, t/n) fitness tuples
+    like `evaluate_multiple_objectives` (program.py:419-453)."""
+    evaluator = make_evaluator(generator, grammar, min_level, max_level, evaluation_samples, infinity)
+
+    def _map(_function, individuals):
+        strings = [str(ind) for ind in individuals]
+        out = []
+        for t, rho, n in evaluate_population(evaluator, strings, group):
+            if n >= infinity:                            # program.py:447-448
+                out.append((rho, infinity))
+            else:
+                out.append((rho, t / n))
+        return out
+    return _map

@@ -1,0 +1,108 @@
+"""Population sharding: host logic on CPU, world_size 2 over gloo."""
+import os
+import socket
+import sys
+
+import pytest
+
+from evostencils_b200 import population
+
+REPO = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+
+
+def fake_evaluate(string):
+    """Deterministic stand-in for a GPU evaluation: depends on the string only."""
+    h = sum(ord(c) * (i + 1) for i, c in enumerate(string))
+    if h % 7 == 0:
+        return (1e100, 1e100, 1e100)
+    return (float(h % 1000) / 8.0, float(h % 97) / 97.0, float(h % 13 + 1))
+
+
+STRINGS = ["ind_%d" % (i % 11) for i in range(29)]       # duplicates on purpose
+
+
+def test_shard_indices_cover_everything_once():
+    for world in (1, 2, 3, 8):
+        seen = sorted(i for r in range(world) for i in population.shard_indices(29, r, world))
+        assert seen == list(range(29))
+    with pytest.raises(ValueError):
+        population.shard_indices(4, 2, 2)
+
+
+def test_deduplicate_is_first_seen_order():
+    unique, back = population.deduplicate(STRINGS)
+    assert unique == ["ind_%d" % i for i in range(11)]
+    assert [unique[b] for b in back] == STRINGS
+
+
+def test_single_process_matches_direct_evaluation():
+    got = population.evaluate_population(fake_evaluate, STRINGS)
+    assert got == [fake_evaluate(s) for s in STRINGS]
+    costs = [float(len(s)) for s in STRINGS]
+    assert population.evaluate_population(fake_evaluate, STRINGS, costs=costs) == got
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, with_costs, queue):
+    sys.path.insert(0, REPO)
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    calls = []
+
+    def evaluate(s):
+        calls.append(s)
+        return fake_evaluate(s)
+
+    costs = [float((i * 7) % 5) for i in range(len(STRINGS))] if with_costs else None
+    out = population.evaluate_population(evaluate, STRINGS, costs=costs)
+    queue.put((rank, out, calls))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("with_costs", [False, True])
+def test_world_size_2_gloo(with_costs):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    queue = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, with_costs, queue)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = [queue.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    want = [fake_evaluate(s) for s in STRINGS]
+    all_calls = []
+    for rank, out, calls in got:
+        assert out == want, rank              # every rank holds the full, identical result list
+        all_calls += calls
+    assert sorted(all_calls) == sorted(set(STRINGS))      # every unique individual exactly once
+    sizes = sorted(len(c) for _, _, c in got)
+    assert sizes[1] - sizes[0] <= 1                       # balanced
+
+
+def test_batched_map_fitness_conventions():
+    class Gen:
+        def generate_and_evaluate(self, expression, storages, lo, hi, solver, infinity=1e100, evaluation_samples=1):
+            return fake_evaluate(expression)
+
+    class Gram:
+        def compile(self, s):
+            if s == "broken":
+                raise SyntaxError(s)
+            return s, None
+
+    m = population.batched_map(Gen(), Gram(), 2, 4)
+    out = m(None, ["ind_1", "broken", "ind_3"])
+    t, rho, n = fake_evaluate("ind_1")
+    assert out[0] == ((rho, t / n) if n < 1e100 else (rho, 1e100))
+    assert out[1] == (1e100, 1e100)
