@@ -48,62 +48,82 @@ __device__ __forceinline__ void row_neighbours(const double* __restrict__ row, i
 
 enum { STAR_JACOBI = 0, STAR_RESIDUAL = 1, STAR_NORM = 2 };
 
+__device__ __forceinline__ int imin(int a, int b) { return a < b ? a : b; }
+__device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }
+
 // MODE 0: out = u + w (f - A u) on interior nodes, out = u on the boundary   (Jacobi sweep)
 // MODE 1: out = f - A u on interior nodes                                      (residual)
 // MODE 2: partial[cta] = sum (f - A u)^2                                        (residual norm)
-template <int MODE, int NT>
+//
+// One CTA = strip of 2*NT columns x band of R rows (R small, compile time).  Every load of the
+// band (R+2 rows of u, R rows of f, the edge lanes' halo column) is issued before the first use,
+// so a thread has 2R+2 16-byte loads in flight and the band costs one memory latency; the halo
+// rows shared with the neighbouring bands are served by L2 (measured DRAM traffic = algorithmic).
+template <int MODE, int NT, int R>
 __global__ void __launch_bounds__(NT) k_star2d(Geom g, Star2D s, const double* __restrict__ u,
                                                 const double* __restrict__ f, double* __restrict__ out, double w,
-                                                int rows, double* __restrict__ partial) {
+                                                double* __restrict__ partial) {
     const int lane = threadIdx.x & 31;
     const int x0 = (blockIdx.x * NT + threadIdx.x) * 2;       // 0 <= x0 <= n-3
     const int n = g.n;
     const long long pitch = g.pitch;
-    const int y_begin = 1 + blockIdx.y * rows;
-    int y_end = y_begin + rows;
-    if (y_end > n - 1) y_end = n - 1;
+    const int y0 = 1 + blockIdx.y * R;                         // rows y0 .. y0+R-1 (those <= n-2)
     const bool in0 = x0 >= 1;                                  // column x0+1 is always interior
     const bool last = x0 == n - 3;                             // also owns the Dirichlet column n-1
-    double acc = 0.0;
-    const double* p = u + (long long)(y_begin - 1) * pitch + x0;
-    double2 um = ld2(p);
-    double2 uc = ld2(p + pitch);
-    double2 un = ld2(p + 2 * pitch);
-    double2 fc = ld2(f + (long long)y_begin * pitch + x0);
+    const bool edge = (lane == 0 && x0 > 0) || lane == 31;
+    const int xe = lane == 0 ? x0 - 1 : x0 + 2;
+    double2 uu[R + 2], ff[R];
+    double ue[R];
+#pragma unroll
+    for (int i = 0; i < R + 2; ++i) uu[i] = ld2(u + (long long)imin(y0 - 1 + i, n) * pitch + x0);   // row n: guard
+#pragma unroll
+    for (int i = 0; i < R; ++i) ff[i] = ld2(f + (long long)imin(y0 + i, n) * pitch + x0);
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+        ue[i] = 0.0;
+        if (edge) ue[i] = u[(long long)imin(y0 + i, n) * pitch + xe];
+    }
     if (MODE == STAR_JACOBI && blockIdx.y == 0) {              // Dirichlet row 0
-        st2(out + x0, um);
+        st2(out + x0, uu[0]);
         if (last) out[n - 1] = u[n - 1];
     }
-    for (int y = y_begin; y < y_end; ++y) {
-        const long long base = (long long)y * pitch + x0;
-        double2 u2 = ld2(u + base + 2 * pitch);                // prefetch row y+2 (guard rows past the array)
-        double2 fn = ld2(f + base + pitch);                    // prefetch f row y+1
-        double left, right;
-        row_neighbours(u + (long long)y * pitch, x0, uc, lane, left, right);
-        const double r0 = fc.x - star_at(s, um.x, left, uc.x, uc.y, un.x);
-        const double r1 = fc.y - star_at(s, um.y, uc.x, uc.y, right, un.y);
-        if (MODE == STAR_JACOBI) {
-            double2 o;
-            o.x = in0 ? uc.x + w * r0 : uc.x;
-            o.y = uc.y + w * r1;
-            st2(out + base, o);
-            if (last) out[base + 2] = right;                   // Dirichlet column n-1
-        } else if (MODE == STAR_RESIDUAL) {
-            if (in0) {
+    double acc = 0.0;
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+        const int y = y0 + i;
+        const double2 um = uu[i], uc = uu[i + 1], un = uu[i + 2];
+        double left = __shfl_up_sync(0xffffffffu, uc.y, 1);
+        double right = __shfl_down_sync(0xffffffffu, uc.x, 1);
+        if (lane == 0) left = ue[i];
+        if (lane == 31) right = ue[i];
+        if (y <= n - 2) {
+            const long long base = (long long)y * pitch + x0;
+            const double r0 = ff[i].x - star_at(s, um.x, left, uc.x, uc.y, un.x);
+            const double r1 = ff[i].y - star_at(s, um.y, uc.x, uc.y, right, un.y);
+            if (MODE == STAR_JACOBI) {
                 double2 o;
-                o.x = r0; o.y = r1;
+                o.x = in0 ? uc.x + w * r0 : uc.x;
+                o.y = uc.y + w * r1;
                 st2(out + base, o);
+                if (last) out[base + 2] = right;                   // Dirichlet column n-1
+            } else if (MODE == STAR_RESIDUAL) {
+                if (in0) {
+                    double2 o;
+                    o.x = r0; o.y = r1;
+                    st2(out + base, o);
+                } else {
+                    out[base + 1] = r1;
+                }
             } else {
-                out[base + 1] = r1;
+                if (in0) acc = acc + r0 * r0;
+                acc = acc + r1 * r1;
             }
-        } else {
-            if (in0) acc = acc + r0 * r0;
-            acc = acc + r1 * r1;
         }
-        um = uc; uc = un; un = u2; fc = fn;
     }
-    if (MODE == STAR_JACOBI && y_end == n - 1) {               // Dirichlet row n-1 (uc holds it now)
-        st2(out + (long long)(n - 1) * pitch + x0, uc);
+    if (MODE == STAR_JACOBI && y0 + R >= n - 1) {              // this band reaches the Dirichlet row n-1
+#pragma unroll
+        for (int i = 1; i < R + 2; ++i)
+            if (y0 - 1 + i == n - 1) st2(out + (long long)(n - 1) * pitch + x0, uu[i]);
         if (last) out[(long long)(n - 1) * pitch + n - 1] = u[(long long)(n - 1) * pitch + n - 1];
     }
     if (MODE == STAR_NORM) {
@@ -121,86 +141,97 @@ __global__ void __launch_bounds__(NT) k_star2d(Geom g, Star2D s, const double* _
 
 // ---- fused two-colour Gauss-Seidel sweep, out of place ------------------------------------------
 // R_j = row j after the red half-sweep (red nodes (x+j) even updated from the old black
-// neighbours); the black half-sweep of row y reads R_{y-1}, R_y, R_{y+1}.  One pass over memory:
-// reads u (+4 halo rows per strip segment) and f (+2), writes the finished row.  The red values a
-// warp needs just outside its 64 columns are recomputed by its edge lanes.
+// neighbours); the black half-sweep of row y reads R_{y-1}, R_y, R_{y+1}.  One pass over memory.
+// A red node only reads black nodes, which the red half-sweep leaves unchanged, so the red rows
+// are formed in place in the registers that held the old rows.  The red values a warp needs just
+// outside its 64 columns are recomputed by its edge lanes from a halo column pair they load with
+// the rest of the band (rows y0-2 .. y0+R+1 of u, y0-1 .. y0+R of f: all loads up front).
 __device__ __forceinline__ double red_value(const Star2D& s, double w, double S, double W, double Cc, double E,
                                             double N, double fv) {
     return Cc + w * (fv - star_at(s, S, W, Cc, E, N));
 }
 
-template <int NT>
+template <int NT, int R>
 __global__ void __launch_bounds__(NT) k_rbgs2d(Geom g, Star2D s, const double* __restrict__ u,
-                                                const double* __restrict__ f, double* __restrict__ out, double w,
-                                                int rows) {
+                                                const double* __restrict__ f, double* __restrict__ out, double w) {
     const int lane = threadIdx.x & 31;
     const int x0 = (blockIdx.x * NT + threadIdx.x) * 2;       // even column; x0+1 odd
     const int n = g.n;
     const long long pitch = g.pitch;
-    const int y_begin = 1 + blockIdx.y * rows;
-    int y_end = y_begin + rows;
-    if (y_end > n - 1) y_end = n - 1;
+    const int y0 = 1 + blockIdx.y * R;
     const bool in0 = x0 >= 1;
     const bool last = x0 == n - 3;
-
-    // R row j from old rows j-1, j, j+1 (interior rows only; boundary rows are returned unchanged)
-    auto red_row = [&](int j, double2 om, double2 oc, double2 on, double2 fj) -> double2 {
-        double left, right;
-        row_neighbours(u + (long long)j * pitch, x0, oc, lane, left, right);
-        double2 r = oc;
+    const bool edge = (lane == 0 && x0 > 0) || lane == 31;
+    const int xe = lane == 0 ? x0 - 2 : x0 + 2;                // halo column pair (xe, xe+1)
+    double2 o[R + 4];          // row y0-2+k
+    double2 fr[R + 2];         // row y0-1+k
+    double2 eh[R + 2];         // halo pair of row y0-1+k (edge lanes)
+    double ef[R];              // f at the halo red node of black row y0+k
+#pragma unroll
+    for (int k = 0; k < R + 4; ++k) o[k] = ld2(u + (long long)imin(y0 - 2 + k, n) * pitch + x0);      // row -1 / n: guard rows
+#pragma unroll
+    for (int k = 0; k < R + 2; ++k) fr[k] = ld2(f + (long long)imin(y0 - 1 + k, n) * pitch + x0);
+#pragma unroll
+    for (int k = 0; k < R + 2; ++k) {
+        eh[k] = make_double2(0.0, 0.0);
+        if (edge) eh[k] = ld2(u + (long long)imin(y0 - 1 + k, n) * pitch + xe);
+    }
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+        ef[k] = 0.0;
+        if (edge) ef[k] = f[(long long)imin(y0 + k, n) * pitch + (lane == 0 ? x0 - 1 : x0 + 2)];
+    }
+    // red half-sweep of rows y0-1 .. y0+R (k = 1 .. R+2), in place
+#pragma unroll
+    for (int k = 1; k < R + 3; ++k) {
+        const int j = y0 - 2 + k;
+        double left = __shfl_up_sync(0xffffffffu, o[k].y, 1);
+        double right = __shfl_down_sync(0xffffffffu, o[k].x, 1);
+        if (lane == 0) left = eh[k - 1].y;                     // old (x0-1, j)
+        if (lane == 31) right = eh[k - 1].x;                   // old (x0+2, j)
         if (j >= 1 && j <= n - 2) {
             if ((j & 1) == 0) {                                 // column x0 (even) is red on even rows
-                if (in0) r.x = red_value(s, w, om.x, left, oc.x, oc.y, on.x, fj.x);
+                if (in0) o[k].x = red_value(s, w, o[k - 1].x, left, o[k].x, o[k].y, o[k + 1].x, fr[k - 1].x);
             } else {                                            // column x0+1 (odd) is red on odd rows
-                r.y = red_value(s, w, om.y, oc.x, oc.y, right, on.y, fj.y);
+                o[k].y = red_value(s, w, o[k - 1].y, o[k].x, o[k].y, right, o[k + 1].y, fr[k - 1].y);
             }
         }
-        return r;
-    };
-    // red value at a single halo node (x, j), recomputed from global memory
-    auto red_halo = [&](int x, int j) -> double {
-        const double* c = u + (long long)j * pitch + x;
-        if (x < 1 || x > n - 2 || j < 1 || j > n - 2) return c[0];
-        return red_value(s, w, c[-pitch], c[-1], c[0], c[1], c[pitch], f[(long long)j * pitch + x]);
-    };
-
-    const double* p = u + (long long)(y_begin - 2) * pitch + x0;      // row y_begin-2 >= -1: guard row
-    double2 o0 = ld2(p), o1 = ld2(p + pitch), o2 = ld2(p + 2 * pitch), o3 = ld2(p + 3 * pitch);
-    const double* fp = f + (long long)(y_begin - 1) * pitch + x0;
-    double2 f0 = ld2(fp), f1 = ld2(fp + pitch);
-    double2 Rm = red_row(y_begin - 1, o0, o1, o2, f0);               // R_{y-1}
-    double2 Rc = red_row(y_begin, o1, o2, o3, f1);                    // R_y
-    if (blockIdx.y == 0) {                                            // Dirichlet row 0
-        st2(out + x0, Rm);
+    }
+    if (blockIdx.y == 0) {                                      // Dirichlet row 0 (k = 1)
+        st2(out + x0, o[1]);
         if (last) out[n - 1] = u[n - 1];
     }
-    // o2 = old row y, o3 = old row y+1 from here on
-    double2 fy = f1;
-    for (int y = y_begin; y < y_end; ++y) {
-        const long long base = (long long)y * pitch + x0;
-        double2 o4 = ld2(u + base + 2 * pitch);                       // old row y+2
-        double2 fn = ld2(f + base + pitch);                           // f row y+1
-        double2 Rn = red_row(y + 1, o2, o3, o4, fn);                  // R_{y+1}
-        // neighbours of R_y outside this thread
-        double left = __shfl_up_sync(0xffffffffu, Rc.y, 1);
-        double right = __shfl_down_sync(0xffffffffu, Rc.x, 1);
-        if (y & 1) {                       // black node: column x0 (even) on odd rows -> needs R at x0-1
-            if (lane == 0) left = x0 > 0 ? red_halo(x0 - 1, y) : 0.0;
-        } else {                           // black node: column x0+1 (odd) on even rows -> needs R at x0+2
-            if (lane == 31) right = red_halo(x0 + 2, y);
+    // black half-sweep of rows y0 .. y0+R-1 (k = 2 .. R+1)
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+        const int k = i + 2;
+        const int y = y0 + i;
+        double left = __shfl_up_sync(0xffffffffu, o[k].y, 1);
+        double right = __shfl_down_sync(0xffffffffu, o[k].x, 1);
+        if (y <= n - 2) {
+            if (y & 1) {               // black node: column x0 on odd rows -> needs the red value at x0-1
+                if (lane == 0)
+                    left = x0 > 0 ? red_value(s, w, eh[i].y, eh[i + 1].x, eh[i + 1].y, o[k].x, eh[i + 2].y, ef[i]) : 0.0;
+            } else {                   // black node: column x0+1 on even rows -> needs the red value at x0+2
+                if (lane == 31)
+                    right = x0 + 2 > n - 2 ? eh[i + 1].x
+                                           : red_value(s, w, eh[i].x, o[k].y, eh[i + 1].x, eh[i + 1].y, eh[i + 2].x, ef[i]);
+            }
+            double2 v = o[k];
+            if (y & 1) {
+                if (in0) v.x = o[k].x + w * (fr[i + 1].x - star_at(s, o[k - 1].x, left, o[k].x, o[k].y, o[k + 1].x));
+            } else {
+                v.y = o[k].y + w * (fr[i + 1].y - star_at(s, o[k - 1].y, o[k].x, o[k].y, right, o[k + 1].y));
+            }
+            const long long base = (long long)y * pitch + x0;
+            st2(out + base, v);
+            if (last) out[base + 2] = eh[i + 1].x;                // Dirichlet column n-1 (old value)
         }
-        double2 o = Rc;
-        if (y & 1) {
-            if (in0) o.x = Rc.x + w * (fy.x - star_at(s, Rm.x, left, Rc.x, Rc.y, Rn.x));
-        } else {
-            o.y = Rc.y + w * (fy.y - star_at(s, Rm.y, Rc.x, Rc.y, right, Rn.y));
-        }
-        st2(out + base, o);
-        if (last) out[base + 2] = u[base + 2];                        // Dirichlet column n-1
-        Rm = Rc; Rc = Rn; o2 = o3; o3 = o4; fy = fn;
     }
-    if (y_end == n - 1) {                                             // Dirichlet row n-1: Rc = R_{n-1} = old
-        st2(out + (long long)(n - 1) * pitch + x0, Rc);
+    if (y0 + R >= n - 1) {                                      // this band reaches the Dirichlet row n-1
+#pragma unroll
+        for (int k = 2; k < R + 3; ++k)
+            if (y0 - 2 + k == n - 1) st2(out + (long long)(n - 1) * pitch + x0, o[k]);
         if (last) out[(long long)(n - 1) * pitch + n - 1] = u[(long long)(n - 1) * pitch + n - 1];
     }
 }

@@ -36,20 +36,53 @@ inline dim3 strip_grid(const Level& lv, int cols_per_thread, int rows, int n_row
     return dim3((lv.g.n - 1) / (cols_per_thread * FAST_NT), (n_rows + rows - 1) / rows, 1);
 }
 
+// rows per CTA of the tile kernels: 4 (measured best at 4096^2: R = 8 costs occupancy, R = 2 halo
+// traffic) unless the level is too small to give ~7 CTAs per SM, then 2
+inline int pick_rows(const Level& lv, int cols_per_thread, int max_ctas = 1 << 30) {
+    const int strips = (lv.g.n - 1) / (cols_per_thread * FAST_NT);
+    const int n_rows = lv.g.n - 2;
+    for (int r = 4; r >= 2; r >>= 1) {
+        const int ctas = strips * ((n_rows + r - 1) / r);
+        if ((ctas >= 1024 || r == 2) && ctas <= max_ctas) return r;
+    }
+    return 8;   // only when max_ctas forces it
+}
+
+// rows per CTA of the marching (restriction / prolongation) kernels: 16 when the level is large
+// enough to fill the machine, fewer below
+inline int march_rows(int n_rows, int strips) {
+    int r = 16;
+    while (r > 2 && strips * ((n_rows + r - 1) / r) < 1024) r >>= 1;
+    return r;
+}
+
+template <int MODE>
+inline void launch_star2d(mg_workspace* ws, Level& lv, int r, const double* u, const double* f, double* out, double w,
+                          double* partial) {
+    dim3 grid = strip_grid(lv, 2, r, lv.g.n - 2);
+    if (r == 8) k_star2d<MODE, FAST_NT, 8><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), u, f, out, w, partial);
+    else if (r == 4) k_star2d<MODE, FAST_NT, 4><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), u, f, out, w, partial);
+    else k_star2d<MODE, FAST_NT, 2><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), u, f, out, w, partial);
+}
+
+inline int valid_rows(int r, int dflt) { return (r == 2 || r == 4 || r == 8) ? r : dflt; }
+
 template <typename T, int D, int F>
 inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm) {
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         if (!star_level_ok<D>(ws, lv, 2) || !sm.point || sm.m != 1) return false;
-        static const int rows_j = tunable("MG_JACOBI_ROWS", 32), rows_rb = tunable("MG_RBGS_ROWS", 32);
+        static const int rows_j = tunable("MG_JACOBI_ROWS", 0), rows_rb = tunable("MG_RBGS_ROWS", 0);
         const double* src = static_cast<const double*>(lv.sol[lv.cur[0]][0]);
         double* dst = static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]);
         const double* rhs = static_cast<const double*>(lv.rhs[0]);
         if (sm.colored) {
-            k_rbgs2d<FAST_NT><<<strip_grid(lv, 2, rows_rb, lv.g.n - 2), FAST_NT, 0, ws->stream>>>(
-                lv.g, star2d(lv), src, rhs, dst, sm.w00, rows_rb);
+            const int r = valid_rows(rows_rb, pick_rows(lv, 2));
+            dim3 grid = strip_grid(lv, 2, r, lv.g.n - 2);
+            if (r == 8) k_rbgs2d<FAST_NT, 8><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), src, rhs, dst, sm.w00);
+            else if (r == 4) k_rbgs2d<FAST_NT, 4><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), src, rhs, dst, sm.w00);
+            else k_rbgs2d<FAST_NT, 2><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), src, rhs, dst, sm.w00);
         } else {
-            k_star2d<STAR_JACOBI, FAST_NT><<<strip_grid(lv, 2, rows_j, lv.g.n - 2), FAST_NT, 0, ws->stream>>>(
-                lv.g, star2d(lv), src, rhs, dst, sm.w00, rows_j, nullptr);
+            launch_star2d<STAR_JACOBI>(ws, lv, valid_rows(rows_j, pick_rows(lv, 2)), src, rhs, dst, sm.w00, nullptr);
         }
         lv.cur[0] ^= 1;
         fast_count(ws);
@@ -62,10 +95,10 @@ template <typename T, int D, int F>
 inline bool fast_residual(mg_workspace* ws, Level& lv) {
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         if (!star_level_ok<D>(ws, lv, 2)) return false;
-        static const int rows = tunable("MG_RESIDUAL_ROWS", 32);
-        k_star2d<STAR_RESIDUAL, FAST_NT><<<strip_grid(lv, 2, rows, lv.g.n - 2), FAST_NT, 0, ws->stream>>>(
-            lv.g, star2d(lv), static_cast<const double*>(lv.sol[lv.cur[0]][0]), static_cast<const double*>(lv.rhs[0]),
-            static_cast<double*>(lv.res[0]), 0.0, rows, nullptr);
+        static const int rows = tunable("MG_RESIDUAL_ROWS", 0);
+        launch_star2d<STAR_RESIDUAL>(ws, lv, valid_rows(rows, pick_rows(lv, 2)),
+                                     static_cast<const double*>(lv.sol[lv.cur[0]][0]),
+                                     static_cast<const double*>(lv.rhs[0]), static_cast<double*>(lv.res[0]), 0.0, nullptr);
         fast_count(ws);
         return true;
     }
@@ -76,12 +109,12 @@ template <typename T, int D, int F>
 inline bool fast_norm(mg_workspace* ws, Level& lv) {
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         if (!star_level_ok<D>(ws, lv, 2)) return false;
-        static const int rows = tunable("MG_NORM_ROWS", 32);
-        dim3 grid = strip_grid(lv, 2, rows, lv.g.n - 2);
+        static const int rows = tunable("MG_NORM_ROWS", 0);
+        const int r = valid_rows(rows, pick_rows(lv, 2, MAX_PARTIALS));
+        dim3 grid = strip_grid(lv, 2, r, lv.g.n - 2);
         if ((int)(grid.x * grid.y) > MAX_PARTIALS) return false;
-        k_star2d<STAR_NORM, FAST_NT><<<grid, FAST_NT, 0, ws->stream>>>(
-            lv.g, star2d(lv), static_cast<const double*>(lv.sol[lv.cur[0]][0]), static_cast<const double*>(lv.rhs[0]),
-            nullptr, 0.0, rows, static_cast<double*>(lv.partial));
+        launch_star2d<STAR_NORM>(ws, lv, r, static_cast<const double*>(lv.sol[lv.cur[0]][0]),
+                                 static_cast<const double*>(lv.rhs[0]), nullptr, 0.0, static_cast<double*>(lv.partial));
         lv.norm_count = grid.x * grid.y;
         fast_count(ws);
         return true;
@@ -93,7 +126,8 @@ template <typename T, int D, int F>
 inline bool fast_residual_restrict(mg_workspace* ws, Level& lf, Level& lc) {
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         if (!star_level_ok<D>(ws, lf, 4) || (lc.g.n - 1) % (2 * FAST_NT) != 0) return false;
-        static const int rows = tunable("MG_RESTRICT_ROWS", 16);
+        static const int rows_env = tunable("MG_RESTRICT_ROWS", 0);
+        const int rows = rows_env > 0 ? rows_env : march_rows(lc.g.n - 2, (lc.g.n - 1) / (2 * FAST_NT));
         k_resrestrict2d<FAST_NT><<<strip_grid(lc, 2, rows, lc.g.n - 2), FAST_NT, 0, ws->stream>>>(
             lc.g, lf.g, star2d(lf), static_cast<const double*>(lf.sol[lf.cur[0]][0]),
             static_cast<const double*>(lf.rhs[0]), static_cast<double*>(lc.rhs[0]), rows);
@@ -107,7 +141,8 @@ template <typename T, int D, int F>
 inline bool fast_prolong_add(mg_workspace* ws, Level& lf, Level& lc, const FieldSet<T>& src, double omega) {
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         if (ws->dtype != MG_F64 || (lf.g.n - 1) % (4 * FAST_NT) != 0) return false;
-        static const int rows = tunable("MG_PROLONG_ROWS", 16);
+        static const int rows_env = tunable("MG_PROLONG_ROWS", 0);
+        const int rows = rows_env > 0 ? rows_env : march_rows(lc.g.n - 1, (lf.g.n - 1) / (4 * FAST_NT));
         k_prolong2d<FAST_NT><<<strip_grid(lf, 4, rows, lc.g.n - 1), FAST_NT, 0, ws->stream>>>(
             lf.g, lc.g, reinterpret_cast<const double*>(src.p[0]), static_cast<double*>(lf.sol[lf.cur[0]][0]), omega,
             rows);
