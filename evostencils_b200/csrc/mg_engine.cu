@@ -205,6 +205,11 @@ static int add_smoother_t(mg_workspace* ws, Smoother& sm, const int32_t* slot_po
     size_t wbytes = (size_t)n_masks * sm.m * sm.m * sizeof(T);
     MG_CUDA(cudaMalloc(&sm.d_w, wbytes));
     MG_CUDA(cudaMemcpy(sm.d_w, w_table, wbytes, cudaMemcpyHostToDevice));   // same memory layout as T
+    sm.full_index = tab.mask_index[(1 << sm.m) - 1];
+    sm.canonical_slots = ws->dim == 2;
+    for (int s = 0; s < sm.m && sm.canonical_slots; ++s)
+        sm.canonical_slots = sm.slot_field[s] == 0 && slot_pos[s * ws->dim] == s / sm.period[1] &&
+                             slot_pos[s * ws->dim + 1] == s % sm.period[1];
     sm.w00 = w_table[(size_t)tab.mask_index[(1 << sm.m) - 1] * sm.m * sm.m * (sizeof(T) / sizeof(double))];
     return MG_OK;
 }

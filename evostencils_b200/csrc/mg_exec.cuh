@@ -140,6 +140,7 @@ int exec_smooth(mg_workspace* ws, const mg_op& op) {
             if (rc) return rc;
         }
     } else {
+        if (ws->use_fast && fast_tile_smooth<T, D, F>(ws, lv, sm)) return MG_OK;
         FieldSet<T> src = cur_sol<T>(lv);
         FieldSet<T> dst = src;
         bool flip[MG_MAX_FIELDS] = {};

@@ -26,6 +26,24 @@ struct Star2D {
 
 __device__ __forceinline__ double2 ld2(const double* p) { return *reinterpret_cast<const double2*>(p); }
 __device__ __forceinline__ void st2(double* p, double2 v) { *reinterpret_cast<double2*>(p) = v; }
+// "up-front" loads of the tile kernels: volatile asm keeps them ahead of the first store in program
+// order (the compiler otherwise sinks them next to their use to save registers, which serialises
+// the memory latency of a band); read-only data path.
+#ifndef MG_PLAIN_LOADS
+__device__ __forceinline__ double2 ldf2(const double* p) {
+    double2 v;
+    asm volatile("ld.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ double ldf1(const double* p) {
+    double v;
+    asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(p));
+    return v;
+}
+#else
+__device__ __forceinline__ double2 ldf2(const double* p) { return ld2(p); }
+__device__ __forceinline__ double ldf1(const double* p) { return *p; }
+#endif
 
 // (A u) at one node, canonical order S, W, C, E, N
 __device__ __forceinline__ double star_at(const Star2D& s, double S, double W, double Cc, double E, double N) {
@@ -75,14 +93,15 @@ __global__ void __launch_bounds__(NT) k_star2d(Geom g, Star2D s, const double* _
     double2 uu[R + 2], ff[R];
     double ue[R];
 #pragma unroll
-    for (int i = 0; i < R + 2; ++i) uu[i] = ld2(u + (long long)imin(y0 - 1 + i, n) * pitch + x0);   // row n: guard
+    for (int i = 0; i < R + 2; ++i) uu[i] = ldf2(u + (long long)imin(y0 - 1 + i, n) * pitch + x0);   // row n: guard
 #pragma unroll
-    for (int i = 0; i < R; ++i) ff[i] = ld2(f + (long long)imin(y0 + i, n) * pitch + x0);
+    for (int i = 0; i < R; ++i) ff[i] = ldf2(f + (long long)imin(y0 + i, n) * pitch + x0);
 #pragma unroll
     for (int i = 0; i < R; ++i) {
         ue[i] = 0.0;
-        if (edge) ue[i] = u[(long long)imin(y0 + i, n) * pitch + xe];
+        if (edge) ue[i] = ldf1(u + (long long)imin(y0 + i, n) * pitch + xe);
     }
+    __syncthreads();      // scheduling fence: keeps every load above ahead of the first use / store
     if (MODE == STAR_JACOBI && blockIdx.y == 0) {              // Dirichlet row 0
         st2(out + x0, uu[0]);
         if (last) out[n - 1] = u[n - 1];
@@ -168,19 +187,20 @@ __global__ void __launch_bounds__(NT) k_rbgs2d(Geom g, Star2D s, const double* _
     double2 eh[R + 2];         // halo pair of row y0-1+k (edge lanes)
     double ef[R];              // f at the halo red node of black row y0+k
 #pragma unroll
-    for (int k = 0; k < R + 4; ++k) o[k] = ld2(u + (long long)imin(y0 - 2 + k, n) * pitch + x0);      // row -1 / n: guard rows
+    for (int k = 0; k < R + 4; ++k) o[k] = ldf2(u + (long long)imin(y0 - 2 + k, n) * pitch + x0);      // row -1 / n: guard rows
 #pragma unroll
-    for (int k = 0; k < R + 2; ++k) fr[k] = ld2(f + (long long)imin(y0 - 1 + k, n) * pitch + x0);
+    for (int k = 0; k < R + 2; ++k) fr[k] = ldf2(f + (long long)imin(y0 - 1 + k, n) * pitch + x0);
 #pragma unroll
     for (int k = 0; k < R + 2; ++k) {
         eh[k] = make_double2(0.0, 0.0);
-        if (edge) eh[k] = ld2(u + (long long)imin(y0 - 1 + k, n) * pitch + xe);
+        if (edge) eh[k] = ldf2(u + (long long)imin(y0 - 1 + k, n) * pitch + xe);
     }
 #pragma unroll
     for (int k = 0; k < R; ++k) {
         ef[k] = 0.0;
-        if (edge) ef[k] = f[(long long)imin(y0 + k, n) * pitch + (lane == 0 ? x0 - 1 : x0 + 2)];
+        if (edge) ef[k] = ldf1(f + (long long)imin(y0 + k, n) * pitch + (lane == 0 ? x0 - 1 : x0 + 2));
     }
+    __syncthreads();      // scheduling fence (see k_star2d)
     // red half-sweep of rows y0-1 .. y0+R (k = 1 .. R+2), in place
 #pragma unroll
     for (int k = 1; k < R + 3; ++k) {
@@ -233,6 +253,111 @@ __global__ void __launch_bounds__(NT) k_rbgs2d(Geom g, Star2D s, const double* _
         for (int k = 2; k < R + 3; ++k)
             if (y0 - 2 + k == n - 1) st2(out + (long long)(n - 1) * pitch + x0, o[k]);
         if (last) out[(long long)(n - 1) * pitch + n - 1] = u[(long long)(n - 1) * pitch + n - 1];
+    }
+}
+
+// ---- block (tile) Jacobi sweep, out of place -------------------------------------------------------
+// `solve locally ... with jacobi` over non-overlapping px x py tiles anchored at node 0
+// (stencils/multiple.py:204-217, exastencils.py:769-822): u_s += sum_t W[s][t] r_t over the interior
+// nodes t of the tile of s, r = f - A u_old, W = omega * inv(L_tile) per boundary class of the tile.
+// One CTA = strip of cw columns x band of rb rows, both whole numbers of tiles (cw % px == 0,
+// rb % py == 0, anchored at 0), so every tile lives in one CTA: node-parallel and coalesced
+// (thread = 2 adjacent columns), residuals exchanged through shared memory.  All loads up front.
+// Arithmetic identical to k_smooth_tile (ascending slot order, first term initialises the sum).
+struct Tile2D {
+    int px, py, m, cw, rb, full_index;
+};
+
+template <int NT, int RMAX>
+__global__ void __launch_bounds__(NT) k_tile2d(Geom g, Star2D s, Tile2D t, const SmootherTable<double>* __restrict__ st,
+                                                const double* __restrict__ wtab, const double* __restrict__ u,
+                                                const double* __restrict__ f, double* __restrict__ out) {
+    __shared__ double r_s[RMAX][2 * NT];
+    __shared__ double w_s[16];
+    const int lane = threadIdx.x & 31;
+    const int n = g.n;
+    const long long pitch = g.pitch;
+    const int c0 = 2 * threadIdx.x;                            // column inside the strip
+    const int x0 = blockIdx.x * t.cw + c0;
+    const int xl = imin(x0, n - 1);                            // load column (even, in bounds)
+    const int yb = blockIdx.y * t.rb;                          // first row of the band (row 0 included)
+    const bool active = c0 < t.cw && x0 <= n - 2;
+    const int xe = lane == 0 ? imax(xl - 1, 0) : imin(xl + 2, n - 1);
+    if (threadIdx.x < t.m * t.m) w_s[threadIdx.x] = wtab[(long long)t.full_index * t.m * t.m + threadIdx.x];
+    double2 uu[RMAX + 2], ff[RMAX];
+    double ue[RMAX];
+#pragma unroll
+    for (int i = 0; i < RMAX + 2; ++i) uu[i] = ldf2(u + (long long)imin(yb - 1 + i, n) * pitch + xl);   // row -1 / n: guard rows
+#pragma unroll
+    for (int i = 0; i < RMAX; ++i) ff[i] = ldf2(f + (long long)imin(yb + i, n) * pitch + xl);
+#pragma unroll
+    for (int i = 0; i < RMAX; ++i) {
+        ue[i] = 0.0;
+        if (lane == 0 || lane == 31) ue[i] = ldf1(u + (long long)imin(yb + i, n) * pitch + xe);
+    }
+    const bool in0 = x0 >= 1 && x0 <= n - 2, in1 = x0 + 1 <= n - 2;
+#pragma unroll
+    for (int i = 0; i < RMAX; ++i) {
+        const int y = yb + i;
+        const double2 um = uu[i], uc = uu[i + 1], un = uu[i + 2];
+        double left = __shfl_up_sync(0xffffffffu, uc.y, 1);
+        double right = __shfl_down_sync(0xffffffffu, uc.x, 1);
+        if (lane == 0) left = ue[i];
+        if (lane == 31) right = ue[i];
+        const bool rowin = y >= 1 && y <= n - 2;
+        double r0 = 0.0, r1 = 0.0;
+        if (rowin && in0) r0 = ff[i].x - star_at(s, um.x, left, uc.x, uc.y, un.x);
+        if (rowin && in1) r1 = ff[i].y - star_at(s, um.y, uc.x, uc.y, right, un.y);
+        r_s[i][c0] = r0;
+        r_s[i][c0 + 1] = r1;
+    }
+    __syncthreads();
+    if (!active) return;
+    const int full = (1 << t.m) - 1;
+    const int sx0 = c0 % t.px, sx1 = (c0 + 1) % t.px;
+    int qdx[4], qdy[4];                                        // slot q -> position in the tile (x outer)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        qdx[q] = q / t.py;
+        qdy[q] = q - qdx[q] * t.py;
+    }
+#pragma unroll
+    for (int i = 0; i < RMAX; ++i) {
+        const int y = yb + i;
+        if (i >= t.rb || y > n - 1) continue;
+        const int sy = i % t.py;
+        double2 o = uu[i + 1];
+        if (y >= 1 && y <= n - 2) {
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const int x = x0 + c;
+                if (x < 1 || x > n - 2) continue;
+                const int sx = c ? sx1 : sx0;
+                const int bx = x - sx, by = y - sy;                 // tile origin (global)
+                const int slot = sx * t.py + sy;
+                int mask = 0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int qx = bx + qdx[q], qy = by + qdy[q];
+                    if (q < t.m && qx >= 1 && qx <= n - 2 && qy >= 1 && qy <= n - 2) mask |= 1 << q;
+                }
+                const double* wrow = mask == full ? w_s + slot * t.m
+                                                  : wtab + ((long long)st->mask_index[mask] * t.m + slot) * t.m;
+                double delta = 0.0;
+                bool first = true;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (!((mask >> q) & 1)) continue;
+                    const double term = wrow[q] * r_s[i - sy + qdy[q]][c0 + c - sx + qdx[q]];
+                    delta = first ? term : delta + term;
+                    first = false;
+                }
+                if (c) o.y = o.y + delta; else o.x = o.x + delta;
+            }
+        }
+        double* dst = out + (long long)y * pitch + x0;
+        st2(dst, o);
+        if (x0 == n - 3) dst[2] = u[(long long)y * pitch + n - 1];  // Dirichlet column n-1
     }
 }
 

@@ -67,6 +67,32 @@ inline void launch_star2d(mg_workspace* ws, Level& lv, int r, const double* u, c
 
 inline int valid_rows(int r, int dflt) { return (r == 2 || r == 4 || r == 8) ? r : dflt; }
 
+// block-Jacobi tiles (px x py <= 4 unknowns) on a scalar star stencil: any level size
+template <typename T, int D, int F>
+inline bool fast_tile_smooth(mg_workspace* ws, Level& lv, Smoother& sm) {
+    if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
+        static const int enabled = tunable("MG_FAST_TILE", 1);
+        if (!enabled || !(ws->dtype == MG_F64 && ws->n_fields == 1 && lv.star) || sm.point || !sm.jacobi || sm.colored)
+            return false;
+        const int px = sm.period[0], py = sm.period[1];
+        if (sm.m != px * py || sm.m > 4 || sm.full_index < 0 || !sm.canonical_slots) return false;
+        Tile2D t;
+        t.px = px; t.py = py; t.m = sm.m;
+        t.cw = (2 * FAST_NT) / (px == 3 ? 6 : 1) * (px == 3 ? 6 : 1);   // even multiple of px, <= 2*NT
+        t.rb = py == 3 ? 3 : 4;
+        t.full_index = sm.full_index;
+        dim3 grid((lv.g.n - 1 + t.cw - 1) / t.cw, (lv.g.n + t.rb - 1) / t.rb, 1);
+        k_tile2d<FAST_NT, 4><<<grid, FAST_NT, 0, ws->stream>>>(
+            lv.g, star2d(lv), t, static_cast<const SmootherTable<double>*>(sm.d_table),
+            static_cast<const double*>(sm.d_w), static_cast<const double*>(lv.sol[lv.cur[0]][0]),
+            static_cast<const double*>(lv.rhs[0]), static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]));
+        lv.cur[0] ^= 1;
+        fast_count(ws);
+        return true;
+    }
+    return false;
+}
+
 template <typename T, int D, int F>
 inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm) {
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {

@@ -68,6 +68,8 @@ struct Smoother {
     // point smoother on a star stencil, single slot: scale = W[0][0] (real)
     double w00 = 0;
     bool same_colour_coupling = false;  // stencil couples nodes of equal colour -> no in-place colour sweep
+    int full_index = -1;                // index of the all-valid mask in the W tables
+    bool canonical_slots = false;       // slot s sits at (s / period[1], s % period[1]) of field 0 (2D scalar tiles)
 };
 
 struct GraphVariant {

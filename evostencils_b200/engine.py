@@ -33,7 +33,7 @@ EXPORTED_SYMBOLS = [
     "mg_set_coarse_solver", "mg_add_smoother", "mg_clear_smoothers", "mg_upload", "mg_download",
     "mg_upload_device", "mg_save_initial_guess", "mg_restore_initial_guess", "mg_exec_ops", "mg_build_cycle",
     "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_synchronize",
-    "mg_time_ops", "mg_mark", "mg_elapsed", "mg_flush_l2", "mg_set_fast_kernels",
+    "mg_time_ops", "mg_profile_ops", "mg_mark", "mg_elapsed", "mg_flush_l2", "mg_set_fast_kernels",
 ]
 
 
@@ -85,6 +85,7 @@ def load_library(path: Optional[str] = None):
                              C.POINTER(C.c_float)]
     lib.mg_synchronize.argtypes = [vp]
     lib.mg_time_ops.argtypes = [vp, C.POINTER(MgOp), i32, i32, C.POINTER(C.c_float)]
+    lib.mg_profile_ops.argtypes = [vp, C.POINTER(MgOp), i32, C.POINTER(C.c_float)]
     lib.mg_mark.argtypes = [vp, i32]
     lib.mg_elapsed.argtypes = [vp, C.POINTER(C.c_float)]
     lib.mg_flush_l2.argtypes = [vp, C.c_size_t]
@@ -334,6 +335,13 @@ class Workspace:
         ms = C.c_float()
         self._check(self.lib.mg_time_ops(self._h, enc, len(enc), reps, C.byref(ms)))
         return ms.value
+
+    def profile_ops(self, ops, default_cycle=None, fused=True):
+        """-> [(kind, level, smoother handle, ms)] for one pass over the (flattened, fused) op list."""
+        arr = self.encode(lowering.fuse(ops) if fused else ops, default_cycle)
+        ms = (C.c_float * len(arr))()
+        self._check(self.lib.mg_profile_ops(self._h, arr, len(arr), ms))
+        return [(int(o.kind), int(o.level), int(o.smoother), float(t)) for o, t in zip(arr, ms)]
 
     def mark(self, which: int):
         self._check(self.lib.mg_mark(self._h, which))

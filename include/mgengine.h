@@ -133,6 +133,9 @@ int mg_synchronize(mg_workspace* ws);
 /* ---- measurement (CUDA events on the workspace stream) ---------------------------------- */
 /* issue the op list `reps` times back to back; *ms = device time of all repetitions */
 int mg_time_ops(mg_workspace* ws, const mg_op* ops, int n_ops, int reps, float* ms);
+/* run the op list once with a CUDA event after every op: ms_per_op[i] = device time of op i
+ * (launch gaps included); a per-stage view of one cycle without a profiler */
+int mg_profile_ops(mg_workspace* ws, const mg_op* ops, int n_ops, float* ms_per_op);
 /* record mark 0 / mark 1 on the workspace stream; elapsed = time between the two marks */
 int mg_mark(mg_workspace* ws, int which);
 int mg_elapsed(mg_workspace* ws, float* ms);

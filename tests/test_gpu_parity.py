@@ -315,3 +315,28 @@ def test_fast_and_generic_kernels_agree_on_a_solve():
         assert len(hist) == len(hists[0])
         assert np.all(np.abs(hists[0] - np.array(hist)) <= 1e-10 * np.abs(hist))
         assert np.array_equal(u_fast, h.sol[hi][0])
+
+
+@pytest.mark.parametrize("block", [(1, 2), (1, 3), (1, 4), (2, 1), (2, 2), (3, 1), (4, 1)])
+def test_fast_tile_smoother_bit_identical_to_generic(block):
+    """Every block shape of the config-2 grammar (maximum_local_system_size = 4): the node-parallel
+    tile kernel equals the generic one-thread-per-tile kernel bit for bit, and the oracle to 1e-12."""
+    problem = problems.POISSON_2D
+    lo, hi = 4, 9
+    results = {}
+    for fast in (True, False):
+        ws, h = make_pair(problem, lo, hi, seed=11)
+        ws.set_fast_kernels(fast)
+        for level in (hi, hi - 3, lo):
+            stmts = smoother_statements(problem, level, "block", ir.Single, omega=0.7, block=(block,))
+            for sweep in range(2):
+                if fast:
+                    run_both(ws, h, stmts, problem)
+                else:
+                    ws.exec_ops(stmts)
+            results[(fast, level)] = ws.download("sol", level, 0)
+            if fast:
+                compare(ws, h, "sol", level, False, f"fast block {block} level {level}")
+        ws.close()
+    for level in (hi, hi - 3, lo):
+        assert np.array_equal(results[(True, level)], results[(False, level)]), (block, level)
