@@ -13,6 +13,10 @@
 
 namespace mg {
 
+// thread index inside the 256-thread Krylov team; threads beyond it (the tail kernel runs 1024) idle
+// through the loops but take part in every barrier
+__device__ __forceinline__ int krylov_tid() { return threadIdx.x < 256 ? (int)threadIdx.x : (1 << 30); }
+
 template <int D>
 struct InteriorIter {
     int m, per_field, total;
@@ -43,7 +47,7 @@ __device__ __forceinline__ FieldSet<T> as_fields(T* base, const Geom& g) {
 template <typename T, int D>
 __device__ T coarse_dot(const T* a, const T* b, const Geom& g, const InteriorIter<D>& it, T* s8) {
     T acc = t_zero(T());
-    for (int e = threadIdx.x; e < it.total; e += 256) {
+    for (int e = krylov_tid(); e < it.total; e += 256) {
         int f; long long idx;
         it.decode(e, g, f, idx);
         acc = t_add(acc, t_mul(a[idx], b[idx]));
@@ -54,13 +58,13 @@ __device__ T coarse_dot(const T* a, const T* b, const Geom& g, const InteriorIte
 // slaved Robin columns + zero rows on a full-array vector (2D, single field)
 __device__ inline void coarse_bc(cplx* v, const Geom& g, cplx c) {
     __syncthreads();
-    for (int t = threadIdx.x; t < g.n; t += 256) {
+    for (int t = krylov_tid(); t < g.n; t += 256) {
         long long row = (long long)t * g.pitch;
         v[row] = t_mul(v[row + 1], c);
         v[row + g.n - 1] = t_mul(v[row + g.n - 2], c);
     }
     __syncthreads();
-    for (int t = threadIdx.x; t < g.n; t += 256) {
+    for (int t = krylov_tid(); t < g.n; t += 256) {
         v[t] = make_cplx(0.0, 0.0);
         v[(long long)(g.n - 1) * g.pitch + t] = make_cplx(0.0, 0.0);
     }
@@ -82,21 +86,18 @@ __device__ inline bool t_is_zero(cplx a) { return a.re == 0.0 && a.im == 0.0; }
 
 // ---- CG --------------------------------------------------------------------------------------------
 // work: 4 vectors of F * g.total elements (x, r, p, ap), shared or global.
-template <typename T, int D, int F, bool SMEM>
-__global__ void __launch_bounds__(256) k_coarse_cg(Geom g, const OperatorTable<T>* __restrict__ op, FieldSet<T> sol,
-                                                   FieldSet<T> rhs, T* gwork, int max_its, double reduction) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ T s8[8];
-    T* work = SMEM ? reinterpret_cast<T*>(smem_raw) : gwork;
+template <typename T, int D, int F>
+__device__ void coarse_cg_body(const Geom& g, const OperatorTable<T>* __restrict__ op, const FieldSet<T>& sol,
+                               const FieldSet<T>& rhs, T* work, int max_its, double reduction, T* s8) {
     const long long vec = (long long)F * g.total;
     T* x = work;
     T* r = work + vec;
     T* p = work + 2 * vec;
     T* ap = work + 3 * vec;
     InteriorIter<D> it(g, F);
-    for (long long i = threadIdx.x; i < 4 * vec; i += 256) work[i] = t_zero(T());
+    for (long long i = krylov_tid(); i < 4 * vec; i += 256) work[i] = t_zero(T());
     __syncthreads();
-    for (int e = threadIdx.x; e < it.total; e += 256) {
+    for (int e = krylov_tid(); e < it.total; e += 256) {
         int f; long long idx;
         it.decode(e, g, f, idx);
         T v = rhs.p[f][idx - (long long)f * g.total];
@@ -109,7 +110,7 @@ __global__ void __launch_bounds__(256) k_coarse_cg(Geom g, const OperatorTable<T
     if (r0 != 0.0) {
         FieldSet<T> pf = as_fields<T, F>(p, g);
         for (int iter = 1; iter <= max_its; ++iter) {
-            for (int e = threadIdx.x; e < it.total; e += 256) {
+            for (int e = krylov_tid(); e < it.total; e += 256) {
                 int f; long long idx;
                 it.decode(e, g, f, idx);
                 ap[idx] = apply_row<T, F>(op, pf, f, idx - (long long)f * g.total);
@@ -117,7 +118,7 @@ __global__ void __launch_bounds__(256) k_coarse_cg(Geom g, const OperatorTable<T
             __syncthreads();
             T pap = coarse_dot<T, D>(p, ap, g, it, s8);
             T alpha = t_div(rs, pap);
-            for (int e = threadIdx.x; e < it.total; e += 256) {
+            for (int e = krylov_tid(); e < it.total; e += 256) {
                 int f; long long idx;
                 it.decode(e, g, f, idx);
                 x[idx] = t_add(x[idx], t_mul(alpha, p[idx]));
@@ -127,7 +128,7 @@ __global__ void __launch_bounds__(256) k_coarse_cg(Geom g, const OperatorTable<T
             T rs_new = coarse_dot<T, D>(r, r, g, it, s8);
             if (t_abs(t_sqrt(rs_new)) <= reduction * r0) break;
             T beta = t_div(rs_new, rs);
-            for (int e = threadIdx.x; e < it.total; e += 256) {
+            for (int e = krylov_tid(); e < it.total; e += 256) {
                 int f; long long idx;
                 it.decode(e, g, f, idx);
                 p[idx] = t_add(r[idx], t_mul(beta, p[idx]));
@@ -139,18 +140,15 @@ __global__ void __launch_bounds__(256) k_coarse_cg(Geom g, const OperatorTable<T
     __syncthreads();
     // solution field: whole array (boundary = 0 for the error equation)
     for (int f = 0; f < F; ++f)
-        for (long long i = threadIdx.x; i < g.total; i += 256) sol.p[f][i] = x[(long long)f * g.total + i];
+        for (long long i = krylov_tid(); i < g.total; i += 256) sol.p[f][i] = x[(long long)f * g.total + i];
 }
 
 // ---- BiCGStab (Helmholtz/...exa3:396-433), dot without conjugation -----------------------------------
 // work: 7 vectors (x, res, res_hat, p, nu, s, t)
-template <typename T, int D, int F, bool SMEM>
-__global__ void __launch_bounds__(256) k_coarse_bicgstab(Geom g, const OperatorTable<T>* __restrict__ op,
-                                                         FieldSet<T> sol, FieldSet<T> rhs, T* gwork, int max_its,
-                                                         double reduction, int robin, cplx bc_factor) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ T s8[8];
-    T* work = SMEM ? reinterpret_cast<T*>(smem_raw) : gwork;
+template <typename T, int D, int F>
+__device__ void coarse_bicgstab_body(const Geom& g, const OperatorTable<T>* __restrict__ op, const FieldSet<T>& sol,
+                                     const FieldSet<T>& rhs, T* work, int max_its, double reduction, int robin,
+                                     cplx bc_factor, T* s8) {
     const long long vec = (long long)F * g.total;
     T* x = work;
     T* res = work + vec;
@@ -160,9 +158,9 @@ __global__ void __launch_bounds__(256) k_coarse_bicgstab(Geom g, const OperatorT
     T* s = work + 5 * vec;
     T* tt = work + 6 * vec;
     InteriorIter<D> it(g, F);
-    for (long long i = threadIdx.x; i < 7 * vec; i += 256) work[i] = t_zero(T());
+    for (long long i = krylov_tid(); i < 7 * vec; i += 256) work[i] = t_zero(T());
     __syncthreads();
-    for (int e = threadIdx.x; e < it.total; e += 256) {
+    for (int e = krylov_tid(); e < it.total; e += 256) {
         int f; long long idx;
         it.decode(e, g, f, idx);
         T v = rhs.p[f][idx - (long long)f * g.total];   // x = 0  =>  res = f
@@ -182,27 +180,27 @@ __global__ void __launch_bounds__(256) k_coarse_bicgstab(Geom g, const OperatorT
             T rho = rho_new;
             rho_new = coarse_dot<T, D>(rhat, res, g, it, s8);
             T beta = t_mul(t_div(rho_new, rho), t_div(alpha, omega));
-            for (int e = threadIdx.x; e < it.total; e += 256) {
+            for (int e = krylov_tid(); e < it.total; e += 256) {
                 int f; long long idx;
                 it.decode(e, g, f, idx);
                 p[idx] = t_add(res[idx], t_mul(beta, t_sub(p[idx], t_mul(omega, nu[idx]))));
             }
             if (robin) coarse_bc(p, g, bc_factor); else __syncthreads();
-            for (int e = threadIdx.x; e < it.total; e += 256) {
+            for (int e = krylov_tid(); e < it.total; e += 256) {
                 int f; long long idx;
                 it.decode(e, g, f, idx);
                 nu[idx] = apply_row<T, F>(op, pf, f, idx - (long long)f * g.total);
             }
             __syncthreads();
             alpha = t_div(rho_new, coarse_dot<T, D>(rhat, nu, g, it, s8));
-            for (int e = threadIdx.x; e < it.total; e += 256) {
+            for (int e = krylov_tid(); e < it.total; e += 256) {
                 int f; long long idx;
                 it.decode(e, g, f, idx);
                 x[idx] = t_add(x[idx], t_mul(alpha, p[idx]));          // h = x + alpha p
                 s[idx] = t_sub(res[idx], t_mul(alpha, nu[idx]));
             }
             if (robin) coarse_bc(s, g, bc_factor); else __syncthreads();
-            for (int e = threadIdx.x; e < it.total; e += 256) {
+            for (int e = krylov_tid(); e < it.total; e += 256) {
                 int f; long long idx;
                 it.decode(e, g, f, idx);
                 tt[idx] = apply_row<T, F>(op, sf, f, idx - (long long)f * g.total);
@@ -211,7 +209,7 @@ __global__ void __launch_bounds__(256) k_coarse_bicgstab(Geom g, const OperatorT
             T ts = coarse_dot<T, D>(tt, s, g, it, s8);
             T tdt = coarse_dot<T, D>(tt, tt, g, it, s8);
             omega = t_div(ts, tdt);
-            for (int e = threadIdx.x; e < it.total; e += 256) {
+            for (int e = krylov_tid(); e < it.total; e += 256) {
                 int f; long long idx;
                 it.decode(e, g, f, idx);
                 x[idx] = t_add(x[idx], t_mul(omega, s[idx]));          // x = h + omega s
@@ -225,7 +223,28 @@ __global__ void __launch_bounds__(256) k_coarse_bicgstab(Geom g, const OperatorT
     __syncthreads();
     if (robin) coarse_bc(x, g, bc_factor);
     for (int f = 0; f < F; ++f)
-        for (long long i = threadIdx.x; i < g.total; i += 256) sol.p[f][i] = x[(long long)f * g.total + i];
+        for (long long i = krylov_tid(); i < g.total; i += 256) sol.p[f][i] = x[(long long)f * g.total + i];
+}
+
+// ---- kernel wrappers: one CTA of 256 threads, Krylov vectors in dynamic shared memory when they fit ----
+template <typename T, int D, int F, bool SMEM>
+__global__ void __launch_bounds__(256) k_coarse_cg(Geom g, const OperatorTable<T>* __restrict__ op, FieldSet<T> sol,
+                                                   FieldSet<T> rhs, T* gwork, int max_its, double reduction) {
+    pdl_sync();
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ T s8[8];
+    coarse_cg_body<T, D, F>(g, op, sol, rhs, SMEM ? reinterpret_cast<T*>(smem_raw) : gwork, max_its, reduction, s8);
+}
+
+template <typename T, int D, int F, bool SMEM>
+__global__ void __launch_bounds__(256) k_coarse_bicgstab(Geom g, const OperatorTable<T>* __restrict__ op,
+                                                         FieldSet<T> sol, FieldSet<T> rhs, T* gwork, int max_its,
+                                                         double reduction, int robin, cplx bc_factor) {
+    pdl_sync();
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ T s8[8];
+    coarse_bicgstab_body<T, D, F>(g, op, sol, rhs, SMEM ? reinterpret_cast<T*>(smem_raw) : gwork, max_its, reduction,
+                                  robin, bc_factor, s8);
 }
 
 }  // namespace mg

@@ -67,6 +67,17 @@ struct SmootherTable {
     // w[k][s][t] follows in device memory (n_masks * n_slots * n_slots values of T)
 };
 
+// Programmatic dependent launch: every kernel lets its successor start launching at once
+// (launch_dependents) and then waits until its predecessor has completed and flushed (wait), before
+// it touches global memory.  Hides the launch latency between the ~70 small kernels of a cycle; a
+// no-op when the kernel was launched without the attribute.
+__device__ __forceinline__ void pdl_sync() {
+#if defined(__CUDA_ARCH__)
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+#endif
+}
+
 template <typename T>
 struct FieldSet {
     T* p[MG_MAX_FIELDS];

@@ -50,6 +50,8 @@ extern "C" int mg_create(mg_workspace** out, int dimension, int min_level, int m
     ws->dim = dimension; ws->min_level = min_level; ws->max_level = max_level;
     ws->n_fields = n_fields; ws->dtype = dtype; ws->device = device;
     ws->elem = dtype == MG_F64 ? 8 : 16;
+    if (const char* v = std::getenv("MG_TAIL_LEVEL")) ws->tail_max_level = std::atoi(v);
+    if (const char* v = std::getenv("MG_PDL")) ws->use_pdl = std::atoi(v) != 0;
     MG_CUDA(cudaStreamCreateWithFlags(&ws->stream, cudaStreamNonBlocking));
     MG_CUDA(cudaEventCreate(&ws->ev0));
     MG_CUDA(cudaEventCreate(&ws->ev1));
@@ -123,6 +125,7 @@ extern "C" int mg_destroy(mg_workspace* ws) {
         if (lv.partial) cudaFree(lv.partial);
     }
     if (ws->cgs_work) cudaFree(ws->cgs_work);
+    delete ws->tail;
     if (ws->d_norm) cudaFree(ws->d_norm);
     if (ws->h_norm) cudaFreeHost(ws->h_norm);
     if (ws->ev0) cudaEventDestroy(ws->ev0);

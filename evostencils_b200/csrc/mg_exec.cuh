@@ -3,6 +3,7 @@
 // serves direct execution (mg_exec_ops) and CUDA-graph capture (mg_build_cycle).
 #pragma once
 #include "mg_coarse.cuh"
+#include "mg_tail.cuh"
 #include "mg_kernels_fast.cuh"
 #include "mg_workspace.cuh"
 
@@ -30,7 +31,6 @@ inline dim3 node_grid(const Geom& g, int bx = 128) {
     return dim3((g.n + bx - 1) / bx, g.n, D == 3 ? g.n : 1);
 }
 
-inline void count(mg_workspace* ws, int k = 1) { ws->pending_count += k; }
 
 // ---- operator upload ------------------------------------------------------------------------------
 template <typename T>
@@ -102,8 +102,8 @@ inline int apply_bc<cplx>(mg_workspace* ws, Level& lv) {
     int blocks = (lv.g.n + 127) / 128;
     for (int f = 0; f < ws->n_fields; ++f) {
         cplx* u = static_cast<cplx*>(lv.sol[lv.cur[f]][f]);
-        k_bc_helmholtz<<<blocks, 128, 0, ws->stream>>>(lv.g, u, c);
-        k_bc_helmholtz_rows<<<blocks, 128, 0, ws->stream>>>(lv.g, u);
+        launch_k(ws, k_bc_helmholtz, blocks, 128, 0, lv.g, u, c);
+        launch_k(ws, k_bc_helmholtz_rows, blocks, 128, 0, lv.g, u);
         count(ws, 2);
     }
     return MG_OK;
@@ -132,7 +132,7 @@ int exec_smooth(mg_workspace* ws, const mg_op& op) {
                 int f = sm.slot_field[s];
                 dst.p[f] = static_cast<T*>(lv.sol[lv.cur[f] ^ 1][f]);
             }
-            k_smooth_point<T, D, F><<<node_grid<D>(lv.g), 128, 0, ws->stream>>>(lv.g, tab, st, w, src, rhs, dst,
+            launch_k(ws, k_smooth_point<T, D, F>, node_grid<D>(lv.g), 128, 0, lv.g, tab, st, w, src, rhs, dst,
                                                                                sm.colored ? c : -1);
             count(ws);
             for (int s = 0; s < sm.m; ++s) lv.cur[sm.slot_field[s]] ^= 1;
@@ -150,7 +150,7 @@ int exec_smooth(mg_workspace* ws, const mg_op& op) {
         int tiles[3] = {1, 1, 1};
         for (int d = 0; d < D; ++d) tiles[d] = (lv.g.n - 1) / sm.period[d] + 1;
         dim3 grid((tiles[0] + 63) / 64, tiles[1], tiles[2]);
-        k_smooth_tile<T, D, F><<<grid, 64, 0, ws->stream>>>(lv.g, tab, st, w, src, rhs, dst, tiles[0]);
+        launch_k(ws, k_smooth_tile<T, D, F>, grid, 64, 0, lv.g, tab, st, w, src, rhs, dst, tiles[0]);
         count(ws);
         for (int f = 0; f < F; ++f)
             if (flip[f]) lv.cur[f] ^= 1;
@@ -166,7 +166,7 @@ int exec_residual(mg_workspace* ws, int level) {
     int rc = upload_operator<T>(ws, lv);
     if (rc) return rc;
     if (ws->use_fast && fast_residual<T, D, F>(ws, lv)) return MG_OK;
-    k_residual<T, D, F><<<node_grid<D>(lv.g), 128, 0, ws->stream>>>(
+    launch_k(ws, k_residual<T, D, F>, node_grid<D>(lv.g), 128, 0, 
         lv.g, static_cast<const OperatorTable<T>*>(lv.d_op), cur_sol<T>(lv), fieldset<T>(lv.rhs), fieldset<T>(lv.res));
     count(ws);
     return MG_OK;
@@ -191,11 +191,11 @@ int exec_restrict(mg_workspace* ws, const mg_op& op, bool fused) {
         int rc = upload_operator<T>(ws, lf);
         if (rc) return rc;
         if (ws->use_fast && fast_residual_restrict<T, D, F>(ws, lf, lc)) return MG_OK;
-        k_residual_restrict<T, D, F><<<node_grid<D>(lc.g), 128, 0, ws->stream>>>(
+        launch_k(ws, k_residual_restrict<T, D, F>, node_grid<D>(lc.g), 128, 0, 
             lc.g, lf.g, static_cast<const OperatorTable<T>*>(lf.d_op), cur_sol<T>(lf), fieldset<T>(lf.rhs),
             fieldset<T>(lc.rhs));
     } else {
-        k_restrict<T, D, F><<<node_grid<D>(lc.g), 128, 0, ws->stream>>>(lc.g, lf.g, field_by_kind<T>(ws, lf, op.src),
+        launch_k(ws, k_restrict<T, D, F>, node_grid<D>(lc.g), 128, 0, lc.g, lf.g, field_by_kind<T>(ws, lf, op.src),
                                                                          fieldset<T>(lc.rhs));
     }
     count(ws);
@@ -210,7 +210,7 @@ int exec_prolong(mg_workspace* ws, const mg_op& op, bool add) {
     FieldSet<T> src = field_by_kind<T>(ws, lc, op.src);
     FieldSet<T> dst = add ? cur_sol<T>(lf) : field_by_kind<T>(ws, lf, MG_COR);
     if (!(add && ws->use_fast && fast_prolong_add<T, D, F>(ws, lf, lc, src, op.omega))) {
-        k_prolong<T, D, F><<<node_grid<D>(lf.g), 128, 0, ws->stream>>>(lf.g, lc.g, src, dst, op.omega, add ? 1 : 0);
+        launch_k(ws, k_prolong<T, D, F>, node_grid<D>(lf.g), 128, 0, lf.g, lc.g, src, dst, op.omega, add ? 1 : 0);
         count(ws);
     }
     if (add) return apply_bc<T>(ws, lf);
@@ -222,7 +222,11 @@ int exec_zero(mg_workspace* ws, int level) {
     Level& lv = ws->L(level);
     for (int f = 0; f < ws->n_fields; ++f) {
         lv.cur[f] = 0;
-        MG_CUDA(cudaMemsetAsync(lv.sol[0][f], 0, (size_t)lv.g.total * sizeof(T), ws->stream));
+        // a kernel, not a memset node: keeps the programmatic-dependent-launch chain of the cycle intact
+        const long long n16 = (long long)lv.g.total * sizeof(T) / 16;        // pitch is a multiple of 16 elements
+        const int blocks = (int)((n16 + 255) / 256 < 1184 ? (n16 + 255) / 256 : 1184);
+        launch_k(ws, k_zero, blocks, 256, 0, static_cast<double2*>(lv.sol[0][f]), n16);
+        count(ws);
     }
     return MG_OK;
 }
@@ -242,9 +246,13 @@ int prepare(mg_workspace* ws) {
     Level& lv = ws->L(ws->min_level);
     const int nvec = ws->cgs_kind == MG_CGS_CG ? 4 : 7;
     size_t bytes = (size_t)nvec * F * lv.g.total * sizeof(T);
+    ws->cgs_smem_bytes = bytes <= 200 * 1024 ? bytes : 0;
+    if (!ws->tail) ws->tail = new TailProgram();
+    ws->tail->n_cmds = 0;
     if (bytes <= 200 * 1024) {
         MG_CUDA(cudaFuncSetAttribute(k_coarse_cg<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
         MG_CUDA(cudaFuncSetAttribute(k_coarse_bicgstab<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     } else if (ws->cgs_work_bytes < bytes) {
         if (ws->cgs_work) cudaFree(ws->cgs_work);
         MG_CUDA(cudaMalloc(&ws->cgs_work, bytes));
@@ -270,15 +278,15 @@ int exec_cgs(mg_workspace* ws, int level) {
     int robin = ws->bc_kind == MG_BC_HELMHOLTZ_ROBIN ? 1 : 0;
     if (ws->cgs_kind == MG_CGS_CG) {
         if (smem) {
-            k_coarse_cg<T, D, F, true><<<1, 256, bytes, ws->stream>>>(lv.g, tab, sol, rhs, nullptr, ws->cgs_max_its, ws->cgs_reduction);
+            launch_k(ws, k_coarse_cg<T, D, F, true>, 1, 256, bytes, lv.g, tab, sol, rhs, nullptr, ws->cgs_max_its, ws->cgs_reduction);
         } else {
-            k_coarse_cg<T, D, F, false><<<1, 256, 0, ws->stream>>>(lv.g, tab, sol, rhs, gwork, ws->cgs_max_its, ws->cgs_reduction);
+            launch_k(ws, k_coarse_cg<T, D, F, false>, 1, 256, 0, lv.g, tab, sol, rhs, gwork, ws->cgs_max_its, ws->cgs_reduction);
         }
     } else {
         if (smem) {
-            k_coarse_bicgstab<T, D, F, true><<<1, 256, bytes, ws->stream>>>(lv.g, tab, sol, rhs, nullptr, ws->cgs_max_its, ws->cgs_reduction, robin, bcf);
+            launch_k(ws, k_coarse_bicgstab<T, D, F, true>, 1, 256, bytes, lv.g, tab, sol, rhs, nullptr, ws->cgs_max_its, ws->cgs_reduction, robin, bcf);
         } else {
-            k_coarse_bicgstab<T, D, F, false><<<1, 256, 0, ws->stream>>>(lv.g, tab, sol, rhs, gwork, ws->cgs_max_its, ws->cgs_reduction, robin, bcf);
+            launch_k(ws, k_coarse_bicgstab<T, D, F, false>, 1, 256, 0, lv.g, tab, sol, rhs, gwork, ws->cgs_max_its, ws->cgs_reduction, robin, bcf);
         }
     }
     count(ws);
@@ -291,20 +299,169 @@ int exec_norm(mg_workspace* ws, int level) {
     int rc = upload_operator<T>(ws, lv);
     if (rc) return rc;
     if (!(ws->use_fast && fast_norm<T, D, F>(ws, lv))) {
-        k_norm_partial<T, D, F><<<lv.norm_blocks, 256, 0, ws->stream>>>(
+        launch_k(ws, k_norm_partial<T, D, F>, lv.norm_blocks, 256, 0, 
             lv.g, static_cast<const OperatorTable<T>*>(lv.d_op), cur_sol<T>(lv), fieldset<T>(lv.rhs),
             static_cast<T*>(lv.partial));
         lv.norm_count = lv.norm_blocks;
         count(ws);
     }
-    k_norm_final<T><<<1, 256, 0, ws->stream>>>(static_cast<const T*>(lv.partial), lv.norm_count, ws->d_norm);
+    launch_k(ws, k_norm_final<T>, 1, 256, 0, static_cast<const T*>(lv.partial), lv.norm_count, ws->d_norm);
     count(ws);
     return MG_OK;
+}
+
+// ---- coarse tail: assemble commands instead of launching (mg_tail.cuh) ---------------------------------
+inline bool tail_level_ok(const mg_workspace* ws, int level) {
+    return ws->use_tail && ws->tail && ws->has_level(level) && level <= ws->tail_max_level &&
+           level - ws->min_level < TAIL_MAX_LEVELS;
+}
+
+template <typename T>
+inline void tail_set(void** dst, const FieldSet<T>& fs) {
+    for (int i = 0; i < MG_MAX_FIELDS; ++i) dst[i] = fs.p[i];
+}
+
+inline TailCmd& tail_new(mg_workspace* ws, int kind, int level) {
+    TailProgram& p = *ws->tail;
+    TailCmd& c = p.cmd[p.n_cmds++];
+    memset(&c, 0, sizeof(c));
+    c.kind = kind;
+    c.lv = level - ws->min_level;
+    c.colour = -1;
+    return c;
+}
+
+template <typename T, int D, int F>
+int tail_flush(mg_workspace* ws) {
+    if (!ws->tail || ws->tail->n_cmds == 0) return MG_OK;
+    TailProgram& p = *ws->tail;
+    p.cgs_kind = ws->cgs_kind;
+    p.cgs_max_its = ws->cgs_max_its;
+    p.cgs_reduction = ws->cgs_reduction;
+    p.robin = ws->bc_kind == MG_BC_HELMHOLTZ_ROBIN ? 1 : 0;
+    p.gwork = ws->cgs_work;
+    p.cgs_in_smem = ws->cgs_smem_bytes > 0 ? 1 : 0;
+    bool has_cgs = false;
+    for (int i = 0; i < p.n_cmds; ++i) has_cgs = has_cgs || p.cmd[i].kind == T_CGS;
+    for (int level = ws->min_level; level <= ws->max_level && level - ws->min_level < TAIL_MAX_LEVELS; ++level) {
+        Level& lv = ws->L(level);
+        TailLevel& tl = p.lv[level - ws->min_level];
+        tl.g = lv.g;
+        tl.op = lv.d_op;
+        double h = 1.0 / (double)(lv.g.n - 1);
+        tl.bc_factor = t_div(make_cplx(1.0, 0.0), make_cplx(1.0, -ws->bc_k * h));
+        tl.st.c = lv.star_c; tl.st.x = lv.star_x; tl.st.y = lv.star_y; tl.st.z = lv.star_z;
+    }
+    launch_k(ws, k_tail<T, D, F>, 1, TAIL_NT, has_cgs ? ws->cgs_smem_bytes : 0, p);
+    count(ws);
+    p.n_cmds = 0;
+    return MG_OK;
+}
+
+// -> 1: op appended to the tail program, 0: not eligible (caller flushes and launches), < 0: error
+template <typename T, int D, int F>
+int tail_append(mg_workspace* ws, const mg_op& op) {
+    if (!ws->use_tail || !ws->tail) return 0;
+    int top = op.level;                                        // highest level the op touches
+    if (op.kind == MG_OP_RESTRICT || op.kind == MG_OP_RESIDUAL_RESTRICT) top = op.level + 1;
+    int bottom = (op.kind == MG_OP_PROLONG_ADD || op.kind == MG_OP_PROLONG) ? op.level - 1 : op.level;
+    if (!tail_level_ok(ws, top) || !ws->has_level(bottom)) return 0;
+    if (ws->tail->n_cmds + 6 > TAIL_MAX_CMDS) {
+        int rc = tail_flush<T, D, F>(ws);
+        if (rc) return rc;
+    }
+    const bool robin = ws->bc_kind == MG_BC_HELMHOLTZ_ROBIN && sizeof(T) == sizeof(cplx);
+    Level& lv = ws->L(op.level);
+    switch (op.kind) {
+        case MG_OP_SMOOTH: {
+            if (op.smoother < 0 || op.smoother >= (int)ws->smoothers.size()) return fail(MG_ERR_INVALID, "bad smoother handle");
+            Smoother& sm = ws->smoothers[op.smoother];
+            if (sm.level != op.level) return fail(MG_ERR_INVALID, "smoother registered for another level");
+            if (lv.op_dirty) return fail(MG_ERR_STATE, "operator not uploaded (prepare not run)");
+            const int passes = (sm.point && sm.colored) ? 2 : 1;
+            for (int c = 0; c < passes; ++c) {
+                FieldSet<T> src = cur_sol<T>(lv);
+                FieldSet<T> dst = src;
+                bool flip[MG_MAX_FIELDS] = {};
+                for (int s = 0; s < sm.m; ++s) flip[sm.slot_field[s]] = true;
+                for (int f = 0; f < F; ++f)
+                    if (flip[f]) dst.p[f] = static_cast<T*>(lv.sol[lv.cur[f] ^ 1][f]);
+                TailCmd& cmd = tail_new(ws, sm.point ? T_SMOOTH_POINT : T_SMOOTH_TILE, op.level);
+                cmd.colour = (sm.point && sm.colored) ? c : -1;
+                cmd.star = (ws->use_fast && lv.star && sm.point && sm.m == 1) ? 1 : 0;
+                cmd.omega = sm.w00;
+                cmd.sm = sm.d_table;
+                cmd.w = sm.d_w;
+                tail_set<T>(cmd.a, src);
+                tail_set<T>(cmd.b, fieldset<T>(lv.rhs));
+                tail_set<T>(cmd.c, dst);
+                for (int f = 0; f < F; ++f)
+                    if (flip[f]) lv.cur[f] ^= 1;
+                if (robin) tail_set<T>(tail_new(ws, T_BC, op.level).c, cur_sol<T>(lv));
+            }
+            return 1;
+        }
+        case MG_OP_RESIDUAL: {
+            if (lv.op_dirty) return fail(MG_ERR_STATE, "operator not uploaded (prepare not run)");
+            TailCmd& cmd = tail_new(ws, T_RESIDUAL, op.level);
+            cmd.star = (ws->use_fast && lv.star) ? 1 : 0;
+            tail_set<T>(cmd.a, cur_sol<T>(lv));
+            tail_set<T>(cmd.b, fieldset<T>(lv.rhs));
+            tail_set<T>(cmd.c, fieldset<T>(lv.res));
+            return 1;
+        }
+        case MG_OP_RESTRICT:
+        case MG_OP_RESIDUAL_RESTRICT: {
+            Level& lf = ws->L(op.level + 1);
+            if (lf.op_dirty && op.kind == MG_OP_RESIDUAL_RESTRICT) return fail(MG_ERR_STATE, "operator not uploaded");
+            TailCmd& cmd = tail_new(ws, op.kind == MG_OP_RESTRICT ? T_RESTRICT : T_RESIDUAL_RESTRICT, op.level);
+            cmd.star = (ws->use_fast && lf.star) ? 1 : 0;
+            if (op.kind == MG_OP_RESTRICT) {
+                tail_set<T>(cmd.a, field_by_kind<T>(ws, lf, op.src));
+            } else {
+                tail_set<T>(cmd.a, cur_sol<T>(lf));
+                tail_set<T>(cmd.b, fieldset<T>(lf.rhs));
+            }
+            tail_set<T>(cmd.c, fieldset<T>(lv.rhs));
+            return 1;
+        }
+        case MG_OP_ZERO: {
+            for (int f = 0; f < F; ++f) lv.cur[f] = 0;
+            tail_set<T>(tail_new(ws, T_ZERO, op.level).c, cur_sol<T>(lv));
+            return 1;
+        }
+        case MG_OP_PROLONG_ADD:
+        case MG_OP_PROLONG: {
+            Level& lc = ws->L(op.level - 1);
+            const bool add = op.kind == MG_OP_PROLONG_ADD;
+            TailCmd& cmd = tail_new(ws, T_PROLONG, op.level);
+            cmd.omega = op.omega;
+            cmd.add = add ? 1 : 0;
+            tail_set<T>(cmd.a, field_by_kind<T>(ws, lc, op.src));
+            tail_set<T>(cmd.c, add ? cur_sol<T>(lv) : field_by_kind<T>(ws, lv, MG_COR));
+            if (add && robin) tail_set<T>(tail_new(ws, T_BC, op.level).c, cur_sol<T>(lv));
+            return 1;
+        }
+        case MG_OP_CGS: {
+            if (op.level != ws->min_level) return fail(MG_ERR_INVALID, "coarse-grid solver op must be on the workspace's min level");
+            if (lv.op_dirty) return fail(MG_ERR_STATE, "operator not uploaded (prepare not run)");
+            for (int f = 0; f < F; ++f) lv.cur[f] = 0;
+            TailCmd& cmd = tail_new(ws, T_CGS, op.level);
+            tail_set<T>(cmd.b, fieldset<T>(lv.rhs));
+            tail_set<T>(cmd.c, cur_sol<T>(lv));
+            return 1;
+        }
+        default: return 0;
+    }
 }
 
 template <typename T, int D, int F>
 int exec_op(mg_workspace* ws, const mg_op& op) {
     if (!ws->has_level(op.level)) return fail(MG_ERR_INVALID, "op level out of range");
+    int rc = tail_append<T, D, F>(ws, op);
+    if (rc != 0) return rc < 0 ? rc : MG_OK;
+    rc = tail_flush<T, D, F>(ws);
+    if (rc) return rc;
     switch (op.kind) {
         case MG_OP_SMOOTH: return exec_smooth<T, D, F>(ws, op);
         case MG_OP_RESIDUAL: return exec_residual<T, D, F>(ws, op.level);

@@ -81,6 +81,7 @@ template <int MODE, int NT, int R>
 __global__ void __launch_bounds__(NT) k_star2d(Geom g, Star2D s, const double* __restrict__ u,
                                                 const double* __restrict__ f, double* __restrict__ out, double w,
                                                 double* __restrict__ partial) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int x0 = (blockIdx.x * NT + threadIdx.x) * 2;       // 0 <= x0 <= n-3
     const int n = g.n;
@@ -173,6 +174,7 @@ __device__ __forceinline__ double red_value(const Star2D& s, double w, double S,
 template <int NT, int R>
 __global__ void __launch_bounds__(NT) k_rbgs2d(Geom g, Star2D s, const double* __restrict__ u,
                                                 const double* __restrict__ f, double* __restrict__ out, double w) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int x0 = (blockIdx.x * NT + threadIdx.x) * 2;       // even column; x0+1 odd
     const int n = g.n;
@@ -272,6 +274,7 @@ template <int NT, int RMAX>
 __global__ void __launch_bounds__(NT) k_tile2d(Geom g, Star2D s, Tile2D t, const SmootherTable<double>* __restrict__ st,
                                                 const double* __restrict__ wtab, const double* __restrict__ u,
                                                 const double* __restrict__ f, double* __restrict__ out) {
+    pdl_sync();
     __shared__ double r_s[RMAX][2 * NT];
     __shared__ double w_s[16];
     const int lane = threadIdx.x & 31;
@@ -371,6 +374,7 @@ template <int NT>
 __global__ void __launch_bounds__(NT) k_resrestrict2d(Geom gc, Geom gf, Star2D s, const double* __restrict__ u,
                                                        const double* __restrict__ f, double* __restrict__ coarse,
                                                        int rows) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int X0 = (blockIdx.x * NT + threadIdx.x) * 2;        // coarse columns X0, X0+1 ; X0 <= nc-3
     const int x0 = 2 * X0;                                      // fine columns x0 .. x0+3
@@ -463,6 +467,7 @@ __global__ void __launch_bounds__(NT) k_resrestrict2d(Geom gc, Geom gf, Star2D s
 template <int NT>
 __global__ void __launch_bounds__(NT) k_prolong2d(Geom gf, Geom gc, const double* __restrict__ e,
                                                    double* __restrict__ u, double omega, int rows) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int x0 = (blockIdx.x * NT + threadIdx.x) * 4;        // fine columns x0..x0+3 ; x0 <= nf-5
     const int X0 = x0 >> 1;

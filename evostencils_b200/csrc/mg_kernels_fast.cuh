@@ -60,9 +60,9 @@ template <int MODE>
 inline void launch_star2d(mg_workspace* ws, Level& lv, int r, const double* u, const double* f, double* out, double w,
                           double* partial) {
     dim3 grid = strip_grid(lv, 2, r, lv.g.n - 2);
-    if (r == 8) k_star2d<MODE, FAST_NT, 8><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), u, f, out, w, partial);
-    else if (r == 4) k_star2d<MODE, FAST_NT, 4><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), u, f, out, w, partial);
-    else k_star2d<MODE, FAST_NT, 2><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), u, f, out, w, partial);
+    if (r == 8) launch_k(ws, k_star2d<MODE, FAST_NT, 8>, grid, FAST_NT, 0, lv.g, star2d(lv), u, f, out, w, partial);
+    else if (r == 4) launch_k(ws, k_star2d<MODE, FAST_NT, 4>, grid, FAST_NT, 0, lv.g, star2d(lv), u, f, out, w, partial);
+    else launch_k(ws, k_star2d<MODE, FAST_NT, 2>, grid, FAST_NT, 0, lv.g, star2d(lv), u, f, out, w, partial);
 }
 
 inline int valid_rows(int r, int dflt) { return (r == 2 || r == 4 || r == 8) ? r : dflt; }
@@ -82,7 +82,7 @@ inline bool fast_tile_smooth(mg_workspace* ws, Level& lv, Smoother& sm) {
         t.rb = py == 3 ? 3 : 4;
         t.full_index = sm.full_index;
         dim3 grid((lv.g.n - 1 + t.cw - 1) / t.cw, (lv.g.n + t.rb - 1) / t.rb, 1);
-        k_tile2d<FAST_NT, 4><<<grid, FAST_NT, 0, ws->stream>>>(
+        launch_k(ws, k_tile2d<FAST_NT, 4>, grid, FAST_NT, 0, 
             lv.g, star2d(lv), t, static_cast<const SmootherTable<double>*>(sm.d_table),
             static_cast<const double*>(sm.d_w), static_cast<const double*>(lv.sol[lv.cur[0]][0]),
             static_cast<const double*>(lv.rhs[0]), static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]));
@@ -104,9 +104,9 @@ inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm) {
         if (sm.colored) {
             const int r = valid_rows(rows_rb, pick_rows(lv, 2));
             dim3 grid = strip_grid(lv, 2, r, lv.g.n - 2);
-            if (r == 8) k_rbgs2d<FAST_NT, 8><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), src, rhs, dst, sm.w00);
-            else if (r == 4) k_rbgs2d<FAST_NT, 4><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), src, rhs, dst, sm.w00);
-            else k_rbgs2d<FAST_NT, 2><<<grid, FAST_NT, 0, ws->stream>>>(lv.g, star2d(lv), src, rhs, dst, sm.w00);
+            if (r == 8) launch_k(ws, k_rbgs2d<FAST_NT, 8>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00);
+            else if (r == 4) launch_k(ws, k_rbgs2d<FAST_NT, 4>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00);
+            else launch_k(ws, k_rbgs2d<FAST_NT, 2>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00);
         } else {
             launch_star2d<STAR_JACOBI>(ws, lv, valid_rows(rows_j, pick_rows(lv, 2)), src, rhs, dst, sm.w00, nullptr);
         }
@@ -154,7 +154,7 @@ inline bool fast_residual_restrict(mg_workspace* ws, Level& lf, Level& lc) {
         if (!star_level_ok<D>(ws, lf, 4) || (lc.g.n - 1) % (2 * FAST_NT) != 0) return false;
         static const int rows_env = tunable("MG_RESTRICT_ROWS", 0);
         const int rows = rows_env > 0 ? rows_env : march_rows(lc.g.n - 2, (lc.g.n - 1) / (2 * FAST_NT));
-        k_resrestrict2d<FAST_NT><<<strip_grid(lc, 2, rows, lc.g.n - 2), FAST_NT, 0, ws->stream>>>(
+        launch_k(ws, k_resrestrict2d<FAST_NT>, strip_grid(lc, 2, rows, lc.g.n - 2), FAST_NT, 0, 
             lc.g, lf.g, star2d(lf), static_cast<const double*>(lf.sol[lf.cur[0]][0]),
             static_cast<const double*>(lf.rhs[0]), static_cast<double*>(lc.rhs[0]), rows);
         fast_count(ws);
@@ -169,7 +169,7 @@ inline bool fast_prolong_add(mg_workspace* ws, Level& lf, Level& lc, const Field
         if (ws->dtype != MG_F64 || (lf.g.n - 1) % (4 * FAST_NT) != 0) return false;
         static const int rows_env = tunable("MG_PROLONG_ROWS", 0);
         const int rows = rows_env > 0 ? rows_env : march_rows(lc.g.n - 1, (lf.g.n - 1) / (4 * FAST_NT));
-        k_prolong2d<FAST_NT><<<strip_grid(lf, 4, rows, lc.g.n - 1), FAST_NT, 0, ws->stream>>>(
+        launch_k(ws, k_prolong2d<FAST_NT>, strip_grid(lf, 4, rows, lc.g.n - 1), FAST_NT, 0, 
             lf.g, lc.g, reinterpret_cast<const double*>(src.p[0]), static_cast<double*>(lf.sol[lf.cur[0]][0]), omega,
             rows);
         fast_count(ws);

@@ -47,23 +47,31 @@ __device__ __forceinline__ T apply_row(const OperatorTable<T>* __restrict__ op, 
 
 // res = rhs - A sol
 template <typename T, int D, int F>
-__global__ void k_residual(Geom g, const OperatorTable<T>* __restrict__ op, FieldSet<T> sol, FieldSet<T> rhs,
-                           FieldSet<T> res) {
-    int x, y, z;
-    if (!node_coords<D>(g, x, y, z) || !is_interior<D>(g, x, y, z)) return;
+__device__ __forceinline__ void residual_node(const Geom& g, const OperatorTable<T>* __restrict__ op,
+                                              const FieldSet<T>& sol, const FieldSet<T>& rhs, const FieldSet<T>& res,
+                                              int x, int y, int z) {
+    if (!is_interior<D>(g, x, y, z)) return;
     long long idx = node_index<D>(g, x, y, z);
 #pragma unroll
     for (int i = 0; i < F; ++i) res.p[i][idx] = t_sub(rhs.p[i][idx], apply_row<T, F>(op, sol, i, idx));
 }
 
+template <typename T, int D, int F>
+__global__ void k_residual(Geom g, const OperatorTable<T>* __restrict__ op, FieldSet<T> sol, FieldSet<T> rhs,
+                           FieldSet<T> res) {
+    pdl_sync();
+    int x, y, z;
+    if (!node_coords<D>(g, x, y, z)) return;
+    residual_node<T, D, F>(g, op, sol, rhs, res, x, y, z);
+}
+
 // Point smoother, out of place: dst_s = src_s + sum_t W[s][t] r_t on the selected colour
 // (colour < 0: all interior nodes), dst_s = src_s elsewhere (including the boundary).
 template <typename T, int D, int F>
-__global__ void k_smooth_point(Geom g, const OperatorTable<T>* __restrict__ op,
-                               const SmootherTable<T>* __restrict__ sm, const T* __restrict__ w, FieldSet<T> src,
-                               FieldSet<T> rhs, FieldSet<T> dst, int colour) {
-    int x, y, z;
-    if (!node_coords<D>(g, x, y, z)) return;
+__device__ __forceinline__ void smooth_point_node(const Geom& g, const OperatorTable<T>* __restrict__ op,
+                                                  const SmootherTable<T>* __restrict__ sm, const T* __restrict__ w,
+                                                  const FieldSet<T>& src, const FieldSet<T>& rhs, const FieldSet<T>& dst,
+                                                  int colour, int x, int y, int z) {
     long long idx = node_index<D>(g, x, y, z);
     const int m = sm->n_slots;
     bool active = is_interior<D>(g, x, y, z) && (colour < 0 || ((x + y + z) & 1) == colour);
@@ -88,15 +96,22 @@ __global__ void k_smooth_point(Geom g, const OperatorTable<T>* __restrict__ op,
     }
 }
 
+template <typename T, int D, int F>
+__global__ void k_smooth_point(Geom g, const OperatorTable<T>* __restrict__ op,
+                               const SmootherTable<T>* __restrict__ sm, const T* __restrict__ w, FieldSet<T> src,
+                               FieldSet<T> rhs, FieldSet<T> dst, int colour) {
+    pdl_sync();
+    int x, y, z;
+    if (!node_coords<D>(g, x, y, z)) return;
+    smooth_point_node<T, D, F>(g, op, sm, w, src, rhs, dst, colour, x, y, z);
+}
+
 // Tile smoother (Jacobi), one thread per tile, out of place.
 template <typename T, int D, int F>
-__global__ void k_smooth_tile(Geom g, const OperatorTable<T>* __restrict__ op,
-                              const SmootherTable<T>* __restrict__ sm, const T* __restrict__ w, FieldSet<T> src,
-                              FieldSet<T> rhs, FieldSet<T> dst, int tiles_x) {
-    int tx = blockIdx.x * blockDim.x + threadIdx.x;
-    int ty = blockIdx.y;
-    int tz = (D == 3) ? blockIdx.z : 0;
-    if (tx >= tiles_x) return;
+__device__ __forceinline__ void smooth_tile_node(const Geom& g, const OperatorTable<T>* __restrict__ op,
+                                                 const SmootherTable<T>* __restrict__ sm, const T* __restrict__ w,
+                                                 const FieldSet<T>& src, const FieldSet<T>& rhs, const FieldSet<T>& dst,
+                                                 int tx, int ty, int tz) {
     const int m = sm->n_slots;
     T r[MG_MAX_SLOTS];
     long long idx[MG_MAX_SLOTS];
@@ -136,9 +151,21 @@ __global__ void k_smooth_tile(Geom g, const OperatorTable<T>* __restrict__ op,
     }
 }
 
+template <typename T, int D, int F>
+__global__ void k_smooth_tile(Geom g, const OperatorTable<T>* __restrict__ op,
+                              const SmootherTable<T>* __restrict__ sm, const T* __restrict__ w, FieldSet<T> src,
+                              FieldSet<T> rhs, FieldSet<T> dst, int tiles_x) {
+    pdl_sync();
+    int tx = blockIdx.x * blockDim.x + threadIdx.x;
+    int ty = blockIdx.y;
+    int tz = (D == 3) ? blockIdx.z : 0;
+    if (tx >= tiles_x) return;
+    smooth_tile_node<T, D, F>(g, op, sm, w, src, rhs, dst, tx, ty, tz);
+}
+
 // full weighting: coarse(I) = sum_o w_o fine(2I + o), offsets in memory order
 template <typename T, int D>
-__device__ __forceinline__ T restrict_at(const T* __restrict__ fine, const Geom& gf, int X, int Y, int Z) {
+__device__ __forceinline__ T restrict_at(const T* fine, const Geom& gf, int X, int Y, int Z) {
     T acc = t_zero(T());
     bool first = true;
     const double w1[3] = {0.25, 0.5, 0.25};
@@ -155,20 +182,29 @@ __device__ __forceinline__ T restrict_at(const T* __restrict__ fine, const Geom&
 }
 
 template <typename T, int D, int F>
-__global__ void k_restrict(Geom gc, Geom gf, FieldSet<T> fine, FieldSet<T> coarse_rhs) {
-    int x, y, z;
-    if (!node_coords<D>(gc, x, y, z) || !is_interior<D>(gc, x, y, z)) return;
+__device__ __forceinline__ void restrict_node(const Geom& gc, const Geom& gf, const FieldSet<T>& fine,
+                                              const FieldSet<T>& coarse_rhs, int x, int y, int z) {
+    if (!is_interior<D>(gc, x, y, z)) return;
     long long idx = node_index<D>(gc, x, y, z);
 #pragma unroll
     for (int i = 0; i < F; ++i) coarse_rhs.p[i][idx] = restrict_at<T, D>(fine.p[i], gf, x, y, z);
 }
 
+template <typename T, int D, int F>
+__global__ void k_restrict(Geom gc, Geom gf, FieldSet<T> fine, FieldSet<T> coarse_rhs) {
+    pdl_sync();
+    int x, y, z;
+    if (!node_coords<D>(gc, x, y, z)) return;
+    restrict_node<T, D, F>(gc, gf, fine, coarse_rhs, x, y, z);
+}
+
 // fused residual + restriction (generic: each coarse thread recomputes its 3^D fine residuals)
 template <typename T, int D, int F>
-__global__ void k_residual_restrict(Geom gc, Geom gf, const OperatorTable<T>* __restrict__ op, FieldSet<T> sol,
-                                    FieldSet<T> rhs, FieldSet<T> coarse_rhs) {
-    int X, Y, Z;
-    if (!node_coords<D>(gc, X, Y, Z) || !is_interior<D>(gc, X, Y, Z)) return;
+__device__ __forceinline__ void residual_restrict_node(const Geom& gc, const Geom& gf,
+                                                       const OperatorTable<T>* __restrict__ op, const FieldSet<T>& sol,
+                                                       const FieldSet<T>& rhs, const FieldSet<T>& coarse_rhs, int X,
+                                                       int Y, int Z) {
+    if (!is_interior<D>(gc, X, Y, Z)) return;
     long long cidx = node_index<D>(gc, X, Y, Z);
     const double w1[3] = {0.25, 0.5, 0.25};
 #pragma unroll
@@ -190,9 +226,18 @@ __global__ void k_residual_restrict(Geom gc, Geom gf, const OperatorTable<T>* __
     }
 }
 
+template <typename T, int D, int F>
+__global__ void k_residual_restrict(Geom gc, Geom gf, const OperatorTable<T>* __restrict__ op, FieldSet<T> sol,
+                                    FieldSet<T> rhs, FieldSet<T> coarse_rhs) {
+    pdl_sync();
+    int X, Y, Z;
+    if (!node_coords<D>(gc, X, Y, Z)) return;
+    residual_restrict_node<T, D, F>(gc, gf, op, sol, rhs, coarse_rhs, X, Y, Z);
+}
+
 // (P e)(x): 2^-k * (sum of the 2^k enclosing coarse nodes in memory order), k = #odd coordinates
 template <typename T, int D>
-__device__ __forceinline__ T prolong_at(const T* __restrict__ coarse, const Geom& gc, int x, int y, int z) {
+__device__ __forceinline__ T prolong_at(const T* coarse, const Geom& gc, int x, int y, int z) {
     int px = x & 1, py = y & 1, pz = (D == 3) ? (z & 1) : 0;
     int X = x >> 1, Y = y >> 1, Z = z >> 1;
     T acc = t_zero(T());
@@ -212,9 +257,9 @@ __device__ __forceinline__ T prolong_at(const T* __restrict__ coarse, const Geom
 
 // sol += omega * P coarse   (add != 0)   |   dst = P coarse   (add == 0)
 template <typename T, int D, int F>
-__global__ void k_prolong(Geom gf, Geom gc, FieldSet<T> coarse, FieldSet<T> dst, double omega, int add) {
-    int x, y, z;
-    if (!node_coords<D>(gf, x, y, z) || !is_interior<D>(gf, x, y, z)) return;
+__device__ __forceinline__ void prolong_node(const Geom& gf, const Geom& gc, const FieldSet<T>& coarse,
+                                             const FieldSet<T>& dst, double omega, int add, int x, int y, int z) {
+    if (!is_interior<D>(gf, x, y, z)) return;
     long long idx = node_index<D>(gf, x, y, z);
 #pragma unroll
     for (int i = 0; i < F; ++i) {
@@ -223,8 +268,24 @@ __global__ void k_prolong(Geom gf, Geom gc, FieldSet<T> coarse, FieldSet<T> dst,
     }
 }
 
+template <typename T, int D, int F>
+__global__ void k_prolong(Geom gf, Geom gc, FieldSet<T> coarse, FieldSet<T> dst, double omega, int add) {
+    pdl_sync();
+    int x, y, z;
+    if (!node_coords<D>(gf, x, y, z)) return;
+    prolong_node<T, D, F>(gf, gc, coarse, dst, omega, add, x, y, z);
+}
+
+// zero-fill (16 bytes per thread and step)
+__global__ void k_zero(double2* __restrict__ p, long long n16) {
+    pdl_sync();
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += (long long)gridDim.x * blockDim.x)
+        p[i] = make_double2(0.0, 0.0);
+}
+
 // Robin columns of the Helmholtz problem (2D): u(0,y) = c u(1,y), u(n-1,y) = c u(n-2,y); rows y=0,n-1 -> 0
 __global__ void k_bc_helmholtz(Geom g, cplx* u, cplx c) {
+    pdl_sync();
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= g.n) return;
     long long row = (long long)t * g.pitch;
@@ -232,6 +293,7 @@ __global__ void k_bc_helmholtz(Geom g, cplx* u, cplx c) {
     u[row + g.n - 1] = t_mul(u[row + g.n - 2], c);
 }
 __global__ void k_bc_helmholtz_rows(Geom g, cplx* u) {
+    pdl_sync();
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= g.n) return;
     u[t] = make_cplx(0.0, 0.0);
@@ -266,7 +328,7 @@ __device__ __forceinline__ T block_sum_256(T v, T* smem8) {
     v = warp_sum<T>(v);
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __syncthreads();
-    if (lane == 0) smem8[warp] = v;
+    if (lane == 0 && warp < 8) smem8[warp] = v;      // CTAs with more than 256 threads: only the first 8 warps contribute
     __syncthreads();
     T a0 = t_add(smem8[0], smem8[4]), a1 = t_add(smem8[1], smem8[5]);
     T a2 = t_add(smem8[2], smem8[6]), a3 = t_add(smem8[3], smem8[7]);
@@ -277,6 +339,7 @@ __device__ __forceinline__ T block_sum_256(T v, T* smem8) {
 template <typename T, int D, int F>
 __global__ void __launch_bounds__(256) k_norm_partial(Geom g, const OperatorTable<T>* __restrict__ op,
                                                       FieldSet<T> sol, FieldSet<T> rhs, T* __restrict__ partial) {
+    pdl_sync();
     __shared__ T s8[8];
     const int rows_per_field = (D == 3) ? g.n * g.n : g.n;
     const int rows = F * rows_per_field;
@@ -300,6 +363,7 @@ __global__ void __launch_bounds__(256) k_norm_partial(Geom g, const OperatorTabl
 // out[0] = |sqrt(sum partial)|  (real: sqrt; complex: modulus of the complex square root)
 template <typename T>
 __global__ void __launch_bounds__(256) k_norm_final(const T* __restrict__ partial, int n, double* __restrict__ out) {
+    pdl_sync();
     __shared__ T s8[8];
     T acc = t_zero(T());
     for (int i = threadIdx.x; i < n; i += 256) acc = t_add(acc, partial[i]);

@@ -1,0 +1,256 @@
+// mg_tail.cuh -- "coarse tail": every op of a cycle that touches only small levels (<= tail_max_level,
+// default 6: at most 65^D nodes) is executed by ONE persistent CTA of 256 threads that interprets a
+// command list passed by value in the kernel parameters, with __syncthreads() between commands.
+// A V-cycle spends ~10 launches per level on those levels; each is a few microseconds of launch and
+// drain latency for nanoseconds of work, so the tail removes ~50 kernel nodes per cycle from the
+// captured graph.  The commands call the same per-node device functions as the grid kernels
+// (mg_kernels_generic.cuh) and the same Krylov bodies (mg_coarse.cuh): results are bit-identical.
+// Fields of these levels are L1/L2 resident (65^2 doubles = 34 KB per array).
+#pragma once
+#include "../../include/mgengine.h"
+#include "mg_coarse.cuh"
+
+namespace mg {
+
+constexpr int TAIL_MAX_CMDS = 224;
+constexpr int TAIL_MAX_LEVELS = 10;
+constexpr int TAIL_NT = 512;            // threads of the tail CTA (the Krylov bodies use the first 256)
+
+enum TailKind {
+    T_SMOOTH_POINT = 0, T_SMOOTH_TILE, T_RESIDUAL, T_RESTRICT, T_RESIDUAL_RESTRICT, T_ZERO, T_PROLONG, T_CGS, T_BC
+};
+
+struct TailCmd {
+    int kind;
+    int lv;                        // index (level - min_level) of the level that is written
+    int colour;                    // SMOOTH_POINT: -1 all, 0/1 colour
+    int add;                       // PROLONG: 1 = sol += omega P e, 0 = dst = P e
+    int star;                      // scalar real star stencil: coefficients from TailLevel::st, weight = omega
+    int pad_;
+    double omega;
+    const void* sm;                // SmootherTable<T>
+    const void* w;                 // W tables
+    void* a[MG_MAX_FIELDS];        // source solution (smooth, residual*) / fine source (restrict) / coarse source (prolong)
+    void* b[MG_MAX_FIELDS];        // right-hand side of the level the residual is formed on
+    void* c[MG_MAX_FIELDS];        // destination
+};
+
+struct StarCoef {                   // (2d+1)-point star, canonical order z-, y-, x-, c, x+, y+, z+
+    double c, x, y, z;
+};
+
+struct TailLevel {
+    Geom g;
+    const void* op;                // OperatorTable<T>
+    cplx bc_factor;                // Helmholtz Robin factor 1 / (1 - i k h)
+    StarCoef st;
+};
+
+template <int D>
+__device__ __forceinline__ double star_apply(const StarCoef& s, const double* u, long long idx, const Geom& g) {
+    double a;
+    if (D == 3) {
+        a = s.z * u[idx - g.plane];
+        a = a + s.y * u[idx - g.pitch];
+    } else {
+        a = s.y * u[idx - g.pitch];
+    }
+    a = a + s.x * u[idx - 1];
+    a = a + s.c * u[idx];
+    a = a + s.x * u[idx + 1];
+    a = a + s.y * u[idx + g.pitch];
+    if (D == 3) a = a + s.z * u[idx + g.plane];
+    return a;
+}
+
+struct TailProgram {
+    int n_cmds;
+    int cgs_kind, cgs_max_its, robin;
+    double cgs_reduction;
+    void* gwork;                   // global Krylov scratch when the vectors do not fit into shared memory
+    int cgs_in_smem;
+    TailLevel lv[TAIL_MAX_LEVELS];
+    TailCmd cmd[TAIL_MAX_CMDS];
+};
+
+template <typename T>
+__device__ __forceinline__ FieldSet<T> tail_fields(void* const* p) {
+    FieldSet<T> fs;
+#pragma unroll
+    for (int i = 0; i < MG_MAX_FIELDS; ++i) fs.p[i] = static_cast<T*>(p[i]);
+    return fs;
+}
+
+template <int D>
+__device__ __forceinline__ void tail_decode(int i, int n, int& x, int& y, int& z) {
+    x = i % n;
+    int t = i / n;
+    if (D == 3) {
+        y = t % n;
+        z = t / n;
+    } else {
+        y = t;
+        z = 0;
+    }
+}
+
+__device__ inline void tail_bc(const Geom&, double*, cplx) {}
+__device__ inline void tail_bc(const Geom& g, cplx* u, cplx c) {
+    for (int t = threadIdx.x; t < g.n; t += TAIL_NT) {
+        long long row = (long long)t * g.pitch;
+        u[row] = t_mul(u[row + 1], c);
+        u[row + g.n - 1] = t_mul(u[row + g.n - 2], c);
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < g.n; t += TAIL_NT) {
+        u[t] = make_cplx(0.0, 0.0);
+        u[(long long)(g.n - 1) * g.pitch + t] = make_cplx(0.0, 0.0);
+    }
+}
+
+template <typename T, int D, int F>
+__global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailProgram prog) {
+    pdl_sync();
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ T s8[8];
+    for (int ci = 0; ci < prog.n_cmds; ++ci) {
+        const TailCmd& cmd = prog.cmd[ci];
+        const Geom g = prog.lv[cmd.lv].g;
+        const OperatorTable<T>* op = static_cast<const OperatorTable<T>*>(prog.lv[cmd.lv].op);
+        const int nodes = (D == 3) ? g.n * g.n * g.n : g.n * g.n;
+        const FieldSet<T> A = tail_fields<T>(cmd.a), B = tail_fields<T>(cmd.b), C = tail_fields<T>(cmd.c);
+        int x, y, z;
+        switch (cmd.kind) {
+            case T_SMOOTH_POINT: {
+                if constexpr (F == 1 && sizeof(T) == sizeof(double)) {
+                    if (cmd.star) {                                 // dst = src + w (f - A src) on the colour
+                        const StarCoef st = prog.lv[cmd.lv].st;
+                        const double* src = static_cast<const double*>(cmd.a[0]);
+                        const double* rhs = static_cast<const double*>(cmd.b[0]);
+                        double* dst = static_cast<double*>(cmd.c[0]);
+#pragma unroll 4
+                        for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                            tail_decode<D>(i, g.n, x, y, z);
+                            const long long idx = node_index<D>(g, x, y, z);
+                            double v = src[idx];
+                            if (is_interior<D>(g, x, y, z) && (cmd.colour < 0 || ((x + y + z) & 1) == cmd.colour))
+                                v = v + cmd.omega * (rhs[idx] - star_apply<D>(st, src, idx, g));
+                            dst[idx] = v;
+                        }
+                        break;
+                    }
+                }
+                const SmootherTable<T>* sm = static_cast<const SmootherTable<T>*>(cmd.sm);
+                const T* w = static_cast<const T*>(cmd.w);
+                for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                    tail_decode<D>(i, g.n, x, y, z);
+                    smooth_point_node<T, D, F>(g, op, sm, w, A, B, C, cmd.colour, x, y, z);
+                }
+                break;
+            }
+            case T_SMOOTH_TILE: {
+                const SmootherTable<T>* sm = static_cast<const SmootherTable<T>*>(cmd.sm);
+                const T* w = static_cast<const T*>(cmd.w);
+                const int t0 = (g.n - 1) / sm->period[0] + 1, t1 = (g.n - 1) / sm->period[1] + 1;
+                const int t2 = (D == 3) ? (g.n - 1) / sm->period[2] + 1 : 1;
+                for (int i = threadIdx.x; i < t0 * t1 * t2; i += TAIL_NT) {
+                    int tx = i % t0, r = i / t0;
+                    smooth_tile_node<T, D, F>(g, op, sm, w, A, B, C, tx, r % t1, r / t1);
+                }
+                break;
+            }
+            case T_RESIDUAL:
+                if constexpr (F == 1 && sizeof(T) == sizeof(double)) {
+                    if (cmd.star) {
+                        const StarCoef st = prog.lv[cmd.lv].st;
+                        const double* src = static_cast<const double*>(cmd.a[0]);
+                        const double* rhs = static_cast<const double*>(cmd.b[0]);
+                        double* dst = static_cast<double*>(cmd.c[0]);
+#pragma unroll 4
+                        for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                            tail_decode<D>(i, g.n, x, y, z);
+                            if (!is_interior<D>(g, x, y, z)) continue;
+                            const long long idx = node_index<D>(g, x, y, z);
+                            dst[idx] = rhs[idx] - star_apply<D>(st, src, idx, g);
+                        }
+                        break;
+                    }
+                }
+                for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                    tail_decode<D>(i, g.n, x, y, z);
+                    residual_node<T, D, F>(g, op, A, B, C, x, y, z);
+                }
+                break;
+            case T_RESTRICT:
+            case T_RESIDUAL_RESTRICT: {
+                const Geom gf = prog.lv[cmd.lv + 1].g;
+                const OperatorTable<T>* opf = static_cast<const OperatorTable<T>*>(prog.lv[cmd.lv + 1].op);
+                if constexpr (F == 1 && sizeof(T) == sizeof(double)) {
+                    if (cmd.star && cmd.kind == T_RESIDUAL_RESTRICT) {      // same loop order as residual_restrict_node
+                        const StarCoef st = prog.lv[cmd.lv + 1].st;
+                        const double* src = static_cast<const double*>(cmd.a[0]);
+                        const double* rhs = static_cast<const double*>(cmd.b[0]);
+                        double* dst = static_cast<double*>(cmd.c[0]);
+                        const double w1[3] = {0.25, 0.5, 0.25};
+#pragma unroll 2
+                        for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                            tail_decode<D>(i, g.n, x, y, z);
+                            if (!is_interior<D>(g, x, y, z)) continue;
+                            double acc = 0.0;
+                            bool first = true;
+#pragma unroll
+                            for (int oz = (D == 3 ? -1 : 0); oz <= (D == 3 ? 1 : 0); ++oz)
+#pragma unroll
+                                for (int oy = -1; oy <= 1; ++oy)
+#pragma unroll
+                                    for (int ox = -1; ox <= 1; ++ox) {
+                                        double wgt = w1[ox + 1] * w1[oy + 1];
+                                        if (D == 3) wgt = w1[oz + 1] * wgt;
+                                        const long long fidx = node_index<D>(gf, 2 * x + ox, 2 * y + oy, 2 * z + oz);
+                                        const double term = wgt * (rhs[fidx] - star_apply<D>(st, src, fidx, gf));
+                                        acc = first ? term : acc + term;
+                                        first = false;
+                                    }
+                            dst[node_index<D>(g, x, y, z)] = acc;
+                        }
+                        break;
+                    }
+                }
+                for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                    tail_decode<D>(i, g.n, x, y, z);
+                    if (cmd.kind == T_RESTRICT) restrict_node<T, D, F>(g, gf, A, C, x, y, z);
+                    else residual_restrict_node<T, D, F>(g, gf, opf, A, B, C, x, y, z);
+                }
+                break;
+            }
+            case T_ZERO:
+                for (int f = 0; f < F; ++f)
+                    for (long long i = threadIdx.x; i < g.total; i += TAIL_NT) C.p[f][i] = t_zero(T());
+                break;
+            case T_PROLONG: {
+                const Geom gc = prog.lv[cmd.lv - 1].g;
+                for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                    tail_decode<D>(i, g.n, x, y, z);
+                    prolong_node<T, D, F>(g, gc, A, C, cmd.omega, cmd.add, x, y, z);
+                }
+                break;
+            }
+            case T_CGS: {
+                T* work = prog.cgs_in_smem ? reinterpret_cast<T*>(smem_raw) : static_cast<T*>(prog.gwork);
+                if (prog.cgs_kind == MG_CGS_CG)
+                    coarse_cg_body<T, D, F>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, s8);
+                else
+                    coarse_bicgstab_body<T, D, F>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, prog.robin,
+                                                  prog.lv[cmd.lv].bc_factor, s8);
+                break;
+            }
+            case T_BC:
+                for (int f = 0; f < F; ++f) tail_bc(g, C.p[f], prog.lv[cmd.lv].bc_factor);
+                break;
+            default: break;
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace mg

@@ -11,6 +11,7 @@
 
 #include "../../include/mgengine.h"
 #include "mg_common.cuh"
+#include "mg_tail.cuh"
 
 namespace mg {
 
@@ -106,6 +107,12 @@ struct mg_workspace {
     long long launches = 0;                     // kernels launched (incl. graph replays)
     long long pending_count = 0;                // kernels issued since the counter was last sampled
     bool use_fast = true;                       // specialised kernels where applicable
+    bool use_pdl = false;                       // programmatic dependent launch between consecutive kernels (MG_PDL=1):
+                                                // measured neutral inside captured graphs, so off by default
+    bool use_tail = true;                       // small levels run inside the single-CTA tail kernel
+    int tail_max_level = 6;                     // levels <= this are "small" (MG_TAIL_LEVEL overrides)
+    mg::TailProgram* tail = nullptr;            // command list being assembled (host copy, passed by value)
+    size_t cgs_smem_bytes = 0;                  // dynamic shared memory of the coarse solver (0: global scratch)
 
     mg::Level& L(int level) { return levels[level - min_level]; }
     bool has_level(int level) const { return level >= min_level && level <= max_level; }
@@ -118,3 +125,26 @@ struct mg_workspace {
         for (int f = 0; f < n_fields; ++f) L(max_level).cur[f] = (s >> f) & 1;
     }
 };
+
+namespace mg {
+
+inline void count(mg_workspace* ws, int k = 1) { ws->pending_count += k; }
+
+// every kernel goes through here: launch on the workspace stream, with the programmatic-dependent-
+// launch attribute (mg_common.cuh pdl_sync) unless disabled (MG_PDL=0)
+template <typename... KArgs, typename... Args>
+inline void launch_k(mg_workspace* ws, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ws->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = ws->use_pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
+}  // namespace mg

@@ -85,7 +85,8 @@ def load_library(path: Optional[str] = None):
                              C.POINTER(C.c_float)]
     lib.mg_synchronize.argtypes = [vp]
     lib.mg_time_ops.argtypes = [vp, C.POINTER(MgOp), i32, i32, C.POINTER(C.c_float)]
-    lib.mg_profile_ops.argtypes = [vp, C.POINTER(MgOp), i32, C.POINTER(C.c_float)]
+    if path == LIB_PATH or hasattr(lib, "mg_profile_ops"):      # the CPU oracle port has no per-op profiler
+        lib.mg_profile_ops.argtypes = [vp, C.POINTER(MgOp), i32, C.POINTER(C.c_float)]
     lib.mg_mark.argtypes = [vp, i32]
     lib.mg_elapsed.argtypes = [vp, C.POINTER(C.c_float)]
     lib.mg_flush_l2.argtypes = [vp, C.c_size_t]
@@ -354,5 +355,8 @@ class Workspace:
     def flush_l2(self, nbytes=256 << 20):
         self._check(self.lib.mg_flush_l2(self._h, nbytes))
 
-    def set_fast_kernels(self, enabled: bool):
-        self._check(self.lib.mg_set_fast_kernels(self._h, int(bool(enabled))))
+    def set_fast_kernels(self, enabled: bool, tail=None):
+        """Specialised kernels on/off; `tail` (default: same as `enabled`) selects the single-CTA
+        interpreter for the small levels."""
+        tail = enabled if tail is None else tail
+        self._check(self.lib.mg_set_fast_kernels(self._h, (1 if enabled else 0) | (2 if tail else 0)))

@@ -141,7 +141,8 @@ int mg_mark(mg_workspace* ws, int which);
 int mg_elapsed(mg_workspace* ws, float* ms);
 /* write `bytes` bytes of scratch (allocated on first use) to evict the L2 between timed runs */
 int mg_flush_l2(mg_workspace* ws, size_t bytes);
-/* 0: generic kernels only, 1: specialised kernels where applicable (default) */
+/* bit 0: specialised kernels where applicable, bit 1: single-CTA tail kernel for the small levels
+ * (default 3 = both; 0 = generic grid kernels only) */
 int mg_set_fast_kernels(mg_workspace* ws, int enabled);
 
 #ifdef __cplusplus
