@@ -107,6 +107,11 @@ static void free_smoothers(mg_workspace* ws) {
 }
 
 static void free_cycles(mg_workspace* ws) {
+    if (ws->outer_graph) {
+        cudaGraphExecDestroy(ws->outer_graph);
+        ws->outer_graph = nullptr;
+        ws->outer_graph_cycle = -1;
+    }
     for (auto& c : ws->cycles)
         for (auto& kv : c.variants)
             if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
@@ -126,6 +131,10 @@ extern "C" int mg_destroy(mg_workspace* ws) {
     }
     if (ws->cgs_work) cudaFree(ws->cgs_work);
     delete ws->tail;
+    if (ws->outer_graph) cudaGraphExecDestroy(ws->outer_graph);
+    if (ws->outer_slab) cudaFree(ws->outer_slab);
+    if (ws->d_outer_scalars) cudaFree(ws->d_outer_scalars);
+    if (ws->d_op_outer) cudaFree(ws->d_op_outer);
     if (ws->d_norm) cudaFree(ws->d_norm);
     if (ws->h_norm) cudaFreeHost(ws->h_norm);
     if (ws->ev0) cudaEventDestroy(ws->ev0);

@@ -5,6 +5,7 @@
 #include "mg_coarse.cuh"
 #include "mg_tail.cuh"
 #include "mg_kernels_fast.cuh"
+#include "mg_outer.cuh"
 #include "mg_workspace.cuh"
 
 namespace mg {

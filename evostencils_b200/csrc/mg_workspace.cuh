@@ -112,6 +112,16 @@ struct mg_workspace {
     bool use_tail = true;                       // small levels run inside the single-CTA tail kernel
     int tail_max_level = 6;                     // levels <= this are "small" (MG_TAIL_LEVEL overrides)
     mg::TailProgram* tail = nullptr;            // command list being assembled (host copy, passed by value)
+    // preconditioned BiCGStab outer solver (mg_outer.cuh)
+    mg::HostOperator hop_outer;                 // unshifted operator A of the finest level
+    bool outer_set = false, outer_dirty = true;
+    void* d_op_outer = nullptr;
+    void* outer_slab = nullptr;
+    void* outer_vec[16] = {};
+    void* d_outer_scalars = nullptr;
+    cudaGraphExec_t outer_graph = nullptr;
+    int outer_graph_cycle = -1;
+    long long outer_graph_kernels = 0;
     size_t cgs_smem_bytes = 0;                  // dynamic shared memory of the coarse solver (0: global scratch)
 
     mg::Level& L(int level) { return levels[level - min_level]; }

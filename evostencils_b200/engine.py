@@ -32,7 +32,8 @@ EXPORTED_SYMBOLS = [
     "mg_create", "mg_destroy", "mg_last_error", "mg_launch_count", "mg_set_operator", "mg_set_boundary",
     "mg_set_coarse_solver", "mg_add_smoother", "mg_clear_smoothers", "mg_upload", "mg_download",
     "mg_upload_device", "mg_save_initial_guess", "mg_restore_initial_guess", "mg_exec_ops", "mg_build_cycle",
-    "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_synchronize",
+    "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_set_outer_operator",
+    "mg_solve_bicgstab", "mg_synchronize",
     "mg_time_ops", "mg_profile_ops", "mg_mark", "mg_elapsed", "mg_flush_l2", "mg_set_fast_kernels",
 ]
 
@@ -83,6 +84,10 @@ def load_library(path: Optional[str] = None):
     lib.mg_residual_norm.argtypes = [vp, i32, C.POINTER(dbl)]
     lib.mg_solve.argtypes = [vp, i32, dbl, i32, C.POINTER(dbl), C.POINTER(C.c_int), C.POINTER(C.c_int),
                              C.POINTER(C.c_float)]
+    if path == LIB_PATH or hasattr(lib, "mg_solve_bicgstab"):   # the CPU oracle port has no outer Krylov solver
+        lib.mg_set_outer_operator.argtypes = [vp, i32, C.POINTER(C.c_int32), C.POINTER(dbl)]
+        lib.mg_solve_bicgstab.argtypes = [vp, i32, dbl, i32, C.POINTER(dbl), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                          C.POINTER(C.c_float)]
     lib.mg_synchronize.argtypes = [vp]
     lib.mg_time_ops.argtypes = [vp, C.POINTER(MgOp), i32, i32, C.POINTER(C.c_float)]
     if path == LIB_PATH or hasattr(lib, "mg_profile_ops"):      # the CPU oracle port has no per-op profiler
@@ -194,6 +199,21 @@ class Workspace:
                         vals[k] = float(val)
                 self._check(self.lib.mg_set_operator(self._h, level, i, j, n, offs, vals))
         self._operators[level] = table
+
+    def set_outer_operator(self, entries):
+        """Unshifted operator A of the finest level for the outer BiCGStab: [(offset, value), ...]."""
+        n = len(entries)
+        offs = (C.c_int32 * (n * self.dimension))()
+        vals = (C.c_double * (n * (2 if self.dtype == "c128" else 1)))()
+        for k, (off, val) in enumerate(entries):
+            for c in range(self.dimension):
+                offs[k * self.dimension + c] = off[c]
+            if self.dtype == "c128":
+                v = complex(val)
+                vals[2 * k], vals[2 * k + 1] = v.real, v.imag
+            else:
+                vals[k] = float(val)
+        self._check(self.lib.mg_set_outer_operator(self._h, n, offs, vals))
 
     def set_boundary(self, kind: str, k: float = 0.0):
         self._check(self.lib.mg_set_boundary(
@@ -319,6 +339,14 @@ class Workspace:
         hist = (C.c_double * (max_its + 1))()
         n_its, conv, ms = C.c_int(), C.c_int(), C.c_float()
         self._check(self.lib.mg_solve(self._h, cycle, tol, max_its, hist, C.byref(n_its), C.byref(conv), C.byref(ms)))
+        return list(hist[: n_its.value + 1]), bool(conv.value), ms.value
+
+    def solve_bicgstab(self, cycle: int, tol: float, max_its: int):
+        """Preconditioned BiCGStab with the cycle as preconditioner -> (history, converged, ms)."""
+        hist = (C.c_double * (max_its + 1))()
+        n_its, conv, ms = C.c_int(), C.c_int(), C.c_float()
+        self._check(self.lib.mg_solve_bicgstab(self._h, cycle, tol, max_its, hist, C.byref(n_its), C.byref(conv),
+                                               C.byref(ms)))
         return list(hist[: n_its.value + 1]), bool(conv.value), ms.value
 
     def synchronize(self):

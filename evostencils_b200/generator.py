@@ -22,7 +22,7 @@ from typing import Dict, List, Optional
 
 import numpy as np
 
-from . import ir, lowering, problems
+from . import ir, lowering, problems, stencils
 from .engine import EngineError, Workspace
 
 
@@ -86,6 +86,22 @@ def summarise_history(history, n, converged, infinity=1e100, solver_iteration_li
     iterations = float(n)
     if not converged or n == 0:
         iterations = infinity
+    if solver_iteration_limit is not None and iterations >= solver_iteration_limit:
+        iterations = infinity
+    return factor, iterations
+
+
+def summarise_bicgstab(history, converged, infinity=1e100, solver_iteration_limit=None):
+    """Output contract of the hand-written outer solver (Helmholtz/...exa3:192-199): one
+    "convergence factor" line = |curRes| / |initRes|; the printed iteration number is the 0-based
+    loop counter `curStep`, and `parse_output` maps 0 and the limit message to infinity."""
+    factor = history[-1] / history[0] if history[0] != 0 else float("nan")
+    if math.isinf(factor) or math.isnan(factor):
+        factor = math.sqrt(infinity)
+    steps = len(history) - 2                       # curStep of the iteration that met the tolerance
+    iterations = float(steps) if converged and steps > 0 else infinity
+    if len(history) == 1:
+        return infinity, infinity
     if solver_iteration_limit is not None and iterations >= solver_iteration_limit:
         iterations = infinity
     return factor, iterations
@@ -311,8 +327,8 @@ class B200ProgramGenerator:
                          max_iterations=None):
         """Solve `evaluation_samples` times; average like `evaluate` (exastencils.py:417-443)."""
         p = self._problem
-        if p.outer != "mg":
-            raise EngineError("outer solver '%s' is not executable by the engine yet" % p.outer)
+        if p.outer not in ("mg", "bicgstab"):
+            raise EngineError("outer solver '%s' is not executable by the engine" % p.outer)
         ws = self._ensure_workspace(program.min_level, program.max_level)
         if ws.max_level != program.max_level:
             raise EngineError("program finest level differs from the workspace")
@@ -328,15 +344,30 @@ class B200ProgramGenerator:
         tol = p.solver.target_reduction
         max_its = p.solver.max_iterations if max_iterations is None else max_iterations
         total_time = total_rho = total_n = 0.0
+        if p.outer == "bicgstab":
+            # unshifted operator of the finest level (Helmholtz/2D_FD_Helmholtz_fromL3.exa3:55-62)
+            merged = dict(p.parameters)
+            merged.update(params)
+            ws.set_outer_operator(lowering._canon(stencils.helmholtz_2d(p.spacing(program.max_level), merged["k"], 1.0)))
         for sample in range(evaluation_samples):
-            if sample == 0:
+            if sample == 0 and p.outer == "mg":
                 self._load_inputs(ws, params, self._custom_rhs, self._custom_u0)
-            else:
+            elif p.outer == "mg":
                 ws.restore_initial_guess()
-            history, converged, ms = ws.solve(cycle, tol, max_its)
-            self.d2h_bytes += 8 * len(history)
-            self.last_residual_history = history
-            rho, n = summarise_history(history, len(history) - 1, converged, infinity, self._solver_iteration_limit)
+            else:
+                self._inputs_key = None          # the preconditioner calls overwrite the right-hand side field
+                self._load_inputs(ws, params, self._custom_rhs, self._custom_u0)
+            if p.outer == "bicgstab":
+                history, converged, ms = ws.solve_bicgstab(cycle, tol, max_its)
+                self.d2h_bytes += 8 * len(history)
+                self.last_residual_history = history
+                rho, n = summarise_bicgstab(history, converged, infinity, self._solver_iteration_limit)
+            else:
+                history, converged, ms = ws.solve(cycle, tol, max_its)
+                self.d2h_bytes += 8 * len(history)
+                self.last_residual_history = history
+                rho, n = summarise_history(history, len(history) - 1, converged, infinity,
+                                           self._solver_iteration_limit)
             if n >= infinity or rho > 1:
                 return ms, rho, n
             if math.isinf(rho) or math.isnan(rho):

@@ -128,6 +128,13 @@ int mg_residual_norm(mg_workspace* ws, int level, double* out);
  * res_hist must hold max_its + 1 doubles.  *ms = device time of the solve phase. */
 int mg_solve(mg_workspace* ws, int cycle, double tol, int max_its, double* res_hist,
              int* n_its, int* converged, float* ms);
+/* Preconditioned BiCGStab outer solver of the Helmholtz configuration
+ * (example_problems/Helmholtz/2D_FD_Helmholtz_fromL3.exa3:144-200): the cycle is the preconditioner
+ * (u = 0; f = p; cycle), `A` the unshifted operator of the finest level set by mg_set_outer_operator.
+ * Same history / stopping conventions as mg_solve; one CUDA graph per BiCGStab iteration. */
+int mg_set_outer_operator(mg_workspace* ws, int n_entries, const int32_t* offsets, const double* values);
+int mg_solve_bicgstab(mg_workspace* ws, int cycle, double tol, int max_its, double* res_hist, int* n_its,
+                      int* converged, float* ms);
 int mg_synchronize(mg_workspace* ws);
 
 /* ---- measurement (CUDA events on the workspace stream) ---------------------------------- */
