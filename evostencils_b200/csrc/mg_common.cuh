@@ -44,8 +44,13 @@ struct Geom {
     int dim;
     int n;                 // nodes per dimension = 2^level + 1
     int pitch;             // elements per x-row (n rounded up to 16)
-    long long plane;       // pitch * n (3D) ; total elements = plane * n (3D) or pitch * n (2D)
+    long long plane;       // pitch * n (3D) ; total elements = plane * nz (3D) or pitch * n (2D)
     long long total;       // allocated elements of one field array
+    // 3D slab (domain decomposition along z): the array holds planes z0 .. z0+nz-1 of the global grid;
+    // local planes 0 and nz-1 are ghost planes (a neighbour's data) or the global Dirichlet planes.
+    // A whole grid is the slab nz = n, z0 = 0.  2D: nz = 1, z0 = 0.
+    int nz;
+    int z0;
 };
 
 // Block operator of one level: F x F constant stencils, linear element offsets precomputed.

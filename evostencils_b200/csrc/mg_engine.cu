@@ -33,8 +33,26 @@ static int check_ws(mg_workspace* ws) {
 
 extern "C" const char* mg_last_error(void) { return g_last_error.c_str(); }
 
+static int create_impl(mg_workspace** out, int dimension, int min_level, int max_level, int n_fields, int dtype,
+                       int device, const int32_t* z_begin, const int32_t* z_end);
+
 extern "C" int mg_create(mg_workspace** out, int dimension, int min_level, int max_level, int n_fields, int dtype,
                          int device) {
+    return create_impl(out, dimension, min_level, max_level, n_fields, dtype, device, nullptr, nullptr);
+}
+
+extern "C" int mg_create_slab(mg_workspace** out, int min_level, int max_level, int n_fields, int dtype, int device,
+                              const int32_t* z_begin, const int32_t* z_end) {
+    if (!z_begin || !z_end) return fail(MG_ERR_INVALID, "slab plane ranges are null");
+    for (int level = min_level; level <= max_level; ++level) {
+        const int n = (1 << level) + 1, zb = z_begin[level - min_level], ze = z_end[level - min_level];
+        if (zb < 1 || ze > n - 2 || ze < zb) return fail(MG_ERR_INVALID, "slab must own a non-empty range of interior planes");
+    }
+    return create_impl(out, 3, min_level, max_level, n_fields, dtype, device, z_begin, z_end);
+}
+
+static int create_impl(mg_workspace** out, int dimension, int min_level, int max_level, int n_fields, int dtype,
+                       int device, const int32_t* z_begin, const int32_t* z_end) {
     if (!out) return fail(MG_ERR_INVALID, "out is null");
     if (dimension < 2 || dimension > 3) return fail(MG_ERR_INVALID, "dimension must be 2 or 3");
     if (min_level < 1 || max_level < min_level || max_level > 14) return fail(MG_ERR_INVALID, "bad level range");
@@ -68,7 +86,14 @@ extern "C" int mg_create(mg_workspace** out, int dimension, int min_level, int m
         g.n = (1 << level) + 1;
         g.pitch = (g.n + 15) / 16 * 16;
         g.plane = (long long)g.pitch * g.n;
-        g.total = dimension == 3 ? g.plane * g.n : g.plane;
+        g.nz = dimension == 3 ? g.n : 1;
+        g.z0 = 0;
+        if (z_begin) {                         // owned planes [zb, ze] + one ghost / boundary plane on either side
+            g.z0 = z_begin[level - min_level] - 1;
+            g.nz = z_end[level - min_level] - z_begin[level - min_level] + 3;
+            ws->slab = true;
+        }
+        g.total = dimension == 3 ? g.plane * g.nz : g.plane;
         const bool finest = level == max_level;
         const int arrays_per_field = 4 + (finest ? 2 : 0);
         // one guard row before and after every array so that halo reads of the specialised
@@ -89,7 +114,7 @@ extern "C" int mg_create(mg_workspace** out, int dimension, int min_level, int m
             lv.sol[0][f] = next(); lv.sol[1][f] = next(); lv.rhs[f] = next(); lv.res[f] = next();
             if (finest) { lv.cor[f] = next(); lv.init[f] = next(); }
         }
-        const int rows = n_fields * (dimension == 3 ? g.n * g.n : g.n);
+        const int rows = n_fields * (dimension == 3 ? g.n * g.nz : g.n);
         lv.norm_blocks = rows < 1184 ? rows : 1184;          // 8 CTAs of 256 threads per SM x 148 SMs
         MG_CUDA(cudaMalloc(&lv.partial, (size_t)MAX_PARTIALS * ws->elem));
     }
@@ -254,6 +279,7 @@ extern "C" int mg_add_smoother(mg_workspace* ws, int level, int jacobi, int colo
     }
     if (sm.point && n_slots > ws->n_fields) return fail(MG_ERR_INVALID, "point smoother with more slots than fields");
     if (!sm.point && (sm.colored || !sm.jacobi)) return fail(MG_ERR_INVALID, "tile smoothers are Jacobi only");
+    if (!sm.point && ws->slab) return fail(MG_ERR_INVALID, "tile smoothers are not available on a z-slab workspace");
     rc = ws->dtype == MG_F64 ? add_smoother_t<double>(ws, sm, slot_pos, n_masks, masks, w_table)
                              : add_smoother_t<cplx>(ws, sm, slot_pos, n_masks, masks, w_table);
     if (rc) {

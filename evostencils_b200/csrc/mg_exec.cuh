@@ -29,7 +29,7 @@ inline FieldSet<T> cur_sol(Level& lv) {
 
 template <int D>
 inline dim3 node_grid(const Geom& g, int bx = 128) {
-    return dim3((g.n + bx - 1) / bx, g.n, D == 3 ? g.n : 1);
+    return dim3((g.n + bx - 1) / bx, g.n, D == 3 ? g.nz : 1);
 }
 
 
@@ -265,6 +265,7 @@ int prepare(mg_workspace* ws) {
 template <typename T, int D, int F>
 int exec_cgs(mg_workspace* ws, int level) {
     if (level != ws->min_level) return fail(MG_ERR_INVALID, "coarse-grid solver op must be on the workspace's min level");
+    if (ws->slab) return fail(MG_ERR_INVALID, "the coarse-grid solver runs on whole grids, not on a z-slab");
     Level& lv = ws->L(level);
     if (lv.op_dirty) return fail(MG_ERR_STATE, "operator not uploaded (prepare not run)");
     for (int f = 0; f < F; ++f) lv.cur[f] = 0;
@@ -444,6 +445,7 @@ int tail_append(mg_workspace* ws, const mg_op& op) {
             return 1;
         }
         case MG_OP_CGS: {
+            if (ws->slab) return fail(MG_ERR_INVALID, "the coarse-grid solver runs on whole grids, not on a z-slab");
             if (op.level != ws->min_level) return fail(MG_ERR_INVALID, "coarse-grid solver op must be on the workspace's min level");
             if (lv.op_dirty) return fail(MG_ERR_STATE, "operator not uploaded (prepare not run)");
             for (int f = 0; f < F; ++f) lv.cur[f] = 0;

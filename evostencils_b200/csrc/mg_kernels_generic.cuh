@@ -18,7 +18,7 @@ __device__ __forceinline__ bool node_coords(const Geom& g, int& x, int& y, int& 
 template <int D>
 __device__ __forceinline__ bool is_interior(const Geom& g, int x, int y, int z) {
     bool in = x >= 1 && x <= g.n - 2 && y >= 1 && y <= g.n - 2;
-    if (D == 3) in = in && z >= 1 && z <= g.n - 2;
+    if (D == 3) in = in && z >= 1 && z <= g.nz - 2 && z + g.z0 >= 1 && z + g.z0 <= g.n - 2;
     return in;
 }
 
@@ -74,7 +74,7 @@ __device__ __forceinline__ void smooth_point_node(const Geom& g, const OperatorT
                                                   int colour, int x, int y, int z) {
     long long idx = node_index<D>(g, x, y, z);
     const int m = sm->n_slots;
-    bool active = is_interior<D>(g, x, y, z) && (colour < 0 || ((x + y + z) & 1) == colour);
+    bool active = is_interior<D>(g, x, y, z) && (colour < 0 || ((x + y + z + g.z0) & 1) == colour);
     if (!active) {
         for (int s = 0; s < m; ++s) {
             int f = sm->slot_field[s];
@@ -120,7 +120,7 @@ __device__ __forceinline__ void smooth_tile_node(const Geom& g, const OperatorTa
         int x = tx * sm->period[0] + sm->slot_pos[s][0];
         int y = ty * sm->period[1] + sm->slot_pos[s][1];
         int z = (D == 3) ? tz * sm->period[2] + sm->slot_pos[s][2] : 0;
-        bool exists = x < g.n && y < g.n && (D < 3 || z < g.n);
+        bool exists = x < g.n && y < g.n && (D < 3 || z < g.nz);
         idx[s] = exists ? node_index<D>(g, x, y, z) : -1;
         r[s] = t_zero(T());
         if (exists && is_interior<D>(g, x, y, z)) {
@@ -165,7 +165,7 @@ __global__ void k_smooth_tile(Geom g, const OperatorTable<T>* __restrict__ op,
 
 // full weighting: coarse(I) = sum_o w_o fine(2I + o), offsets in memory order
 template <typename T, int D>
-__device__ __forceinline__ T restrict_at(const T* fine, const Geom& gf, int X, int Y, int Z) {
+__device__ __forceinline__ T restrict_at(const T* fine, const Geom& gf, int X, int Y, int Z /* fine-local 2Z */) {
     T acc = t_zero(T());
     bool first = true;
     const double w1[3] = {0.25, 0.5, 0.25};
@@ -174,7 +174,7 @@ __device__ __forceinline__ T restrict_at(const T* fine, const Geom& gf, int X, i
             for (int ox = -1; ox <= 1; ++ox) {
                 double wgt = w1[ox + 1] * w1[oy + 1];   // products of powers of two: exact
                 if (D == 3) wgt = w1[oz + 1] * wgt;
-                T term = t_scale(wgt, fine[node_index<D>(gf, 2 * X + ox, 2 * Y + oy, 2 * Z + oz)]);
+                T term = t_scale(wgt, fine[node_index<D>(gf, 2 * X + ox, 2 * Y + oy, Z + oz)]);
                 acc = first ? term : t_add(acc, term);
                 first = false;
             }
@@ -186,8 +186,9 @@ __device__ __forceinline__ void restrict_node(const Geom& gc, const Geom& gf, co
                                               const FieldSet<T>& coarse_rhs, int x, int y, int z) {
     if (!is_interior<D>(gc, x, y, z)) return;
     long long idx = node_index<D>(gc, x, y, z);
+    const int zf = (D == 3) ? 2 * (z + gc.z0) - gf.z0 : 0;      // fine-local plane of the coarse node
 #pragma unroll
-    for (int i = 0; i < F; ++i) coarse_rhs.p[i][idx] = restrict_at<T, D>(fine.p[i], gf, x, y, z);
+    for (int i = 0; i < F; ++i) coarse_rhs.p[i][idx] = restrict_at<T, D>(fine.p[i], gf, x, y, zf);
 }
 
 template <typename T, int D, int F>
@@ -206,6 +207,7 @@ __device__ __forceinline__ void residual_restrict_node(const Geom& gc, const Geo
                                                        int Y, int Z) {
     if (!is_interior<D>(gc, X, Y, Z)) return;
     long long cidx = node_index<D>(gc, X, Y, Z);
+    const int zf = (D == 3) ? 2 * (Z + gc.z0) - gf.z0 : 0;
     const double w1[3] = {0.25, 0.5, 0.25};
 #pragma unroll
     for (int i = 0; i < F; ++i) {
@@ -216,7 +218,7 @@ __device__ __forceinline__ void residual_restrict_node(const Geom& gc, const Geo
                 for (int ox = -1; ox <= 1; ++ox) {
                     double wgt = w1[ox + 1] * w1[oy + 1];
                     if (D == 3) wgt = w1[oz + 1] * wgt;
-                    long long fidx = node_index<D>(gf, 2 * X + ox, 2 * Y + oy, 2 * Z + oz);
+                    long long fidx = node_index<D>(gf, 2 * X + ox, 2 * Y + oy, zf + oz);
                     T r = t_sub(rhs.p[i][fidx], apply_row<T, F>(op, sol, i, fidx));
                     T term = t_scale(wgt, r);
                     acc = first ? term : t_add(acc, term);
@@ -238,8 +240,9 @@ __global__ void k_residual_restrict(Geom gc, Geom gf, const OperatorTable<T>* __
 // (P e)(x): 2^-k * (sum of the 2^k enclosing coarse nodes in memory order), k = #odd coordinates
 template <typename T, int D>
 __device__ __forceinline__ T prolong_at(const T* coarse, const Geom& gc, int x, int y, int z) {
+    // z is the GLOBAL fine plane index; the coarse array is addressed slab-locally
     int px = x & 1, py = y & 1, pz = (D == 3) ? (z & 1) : 0;
-    int X = x >> 1, Y = y >> 1, Z = z >> 1;
+    int X = x >> 1, Y = y >> 1, Z = (z >> 1) - gc.z0;
     T acc = t_zero(T());
     bool first = true;
     for (int cz = 0; cz <= pz; ++cz)
@@ -263,7 +266,7 @@ __device__ __forceinline__ void prolong_node(const Geom& gf, const Geom& gc, con
     long long idx = node_index<D>(gf, x, y, z);
 #pragma unroll
     for (int i = 0; i < F; ++i) {
-        T pe = prolong_at<T, D>(coarse.p[i], gc, x, y, z);
+        T pe = prolong_at<T, D>(coarse.p[i], gc, x, y, z + gf.z0);
         dst.p[i][idx] = add ? t_add(dst.p[i][idx], t_scale(omega, pe)) : pe;
     }
 }
@@ -341,7 +344,7 @@ __global__ void __launch_bounds__(256) k_norm_partial(Geom g, const OperatorTabl
                                                       FieldSet<T> sol, FieldSet<T> rhs, T* __restrict__ partial) {
     pdl_sync();
     __shared__ T s8[8];
-    const int rows_per_field = (D == 3) ? g.n * g.n : g.n;
+    const int rows_per_field = (D == 3) ? g.n * g.nz : g.n;
     const int rows = F * rows_per_field;
     T acc = t_zero(T());
     for (int row = blockIdx.x; row < rows; row += gridDim.x) {
@@ -349,7 +352,7 @@ __global__ void __launch_bounds__(256) k_norm_partial(Geom g, const OperatorTabl
         int rr = row - f * rows_per_field;
         int z = (D == 3) ? rr / g.n : 0;
         int y = (D == 3) ? rr - z * g.n : rr;
-        if (y < 1 || y > g.n - 2 || (D == 3 && (z < 1 || z > g.n - 2))) continue;
+        if (!is_interior<D>(g, 1, y, z)) continue;
         for (int x = 1 + threadIdx.x; x <= g.n - 2; x += 256) {
             long long idx = node_index<D>(g, x, y, z);
             T r = t_sub(rhs.p[f][idx], apply_row<T, F>(op, sol, f, idx));

@@ -46,12 +46,12 @@ template <typename T, int D>
 __global__ void __launch_bounds__(256) k_outer_dot(Geom g, const T* a, const T* b, T* __restrict__ partial) {
     pdl_sync();
     __shared__ T s8[8];
-    const int rows = (D == 3) ? g.n * g.n : g.n;
+    const int rows = (D == 3) ? g.n * g.nz : g.n;
     T acc = t_zero(T());
     for (int row = blockIdx.x; row < rows; row += gridDim.x) {
         int z = (D == 3) ? row / g.n : 0;
         int y = (D == 3) ? row - z * g.n : row;
-        if (y < 1 || y > g.n - 2 || (D == 3 && (z < 1 || z > g.n - 2))) continue;
+        if (!is_interior<D>(g, 1, y, z)) continue;
         for (int x = 1 + threadIdx.x; x <= g.n - 2; x += 256) {
             long long idx = node_index<D>(g, x, y, z);
             acc = t_add(acc, t_mul(a[idx], b[idx]));

@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
         const TailCmd& cmd = prog.cmd[ci];
         const Geom g = prog.lv[cmd.lv].g;
         const OperatorTable<T>* op = static_cast<const OperatorTable<T>*>(prog.lv[cmd.lv].op);
-        const int nodes = (D == 3) ? g.n * g.n * g.n : g.n * g.n;
+        const int nodes = (D == 3) ? g.n * g.n * g.nz : g.n * g.n;
         const FieldSet<T> A = tail_fields<T>(cmd.a), B = tail_fields<T>(cmd.b), C = tail_fields<T>(cmd.c);
         int x, y, z;
         switch (cmd.kind) {
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
                             tail_decode<D>(i, g.n, x, y, z);
                             const long long idx = node_index<D>(g, x, y, z);
                             double v = src[idx];
-                            if (is_interior<D>(g, x, y, z) && (cmd.colour < 0 || ((x + y + z) & 1) == cmd.colour))
+                            if (is_interior<D>(g, x, y, z) && (cmd.colour < 0 || ((x + y + z + g.z0) & 1) == cmd.colour))
                                 v = v + cmd.omega * (rhs[idx] - star_apply<D>(st, src, idx, g));
                             dst[idx] = v;
                         }
@@ -196,6 +196,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
                         for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
                             tail_decode<D>(i, g.n, x, y, z);
                             if (!is_interior<D>(g, x, y, z)) continue;
+                            const int zf = (D == 3) ? 2 * (z + g.z0) - gf.z0 : 0;
                             double acc = 0.0;
                             bool first = true;
 #pragma unroll
@@ -206,7 +207,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
                                     for (int ox = -1; ox <= 1; ++ox) {
                                         double wgt = w1[ox + 1] * w1[oy + 1];
                                         if (D == 3) wgt = w1[oz + 1] * wgt;
-                                        const long long fidx = node_index<D>(gf, 2 * x + ox, 2 * y + oy, 2 * z + oz);
+                                        const long long fidx = node_index<D>(gf, 2 * x + ox, 2 * y + oy, zf + oz);
                                         const double term = wgt * (rhs[fidx] - star_apply<D>(st, src, fidx, gf));
                                         acc = first ? term : acc + term;
                                         first = false;

@@ -89,6 +89,7 @@ struct Cycle {
 struct mg_workspace {
     int dim = 2, min_level = 0, max_level = 0, n_fields = 1, dtype = MG_F64, device = 0;
     size_t elem = 8;
+    bool slab = false;                          // 3D z-slab of a domain-decomposed grid (mg_create_slab)
     cudaStream_t stream = nullptr;
     std::vector<mg::Level> levels;              // index = level - min_level
     std::vector<mg::Smoother> smoothers;

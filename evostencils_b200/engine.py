@@ -29,7 +29,7 @@ MG_CGS_CG, MG_CGS_BICGSTAB = 0, 1
 _FIELD = {"sol": MG_SOL, "rhs": MG_RHS, "res": MG_RES, "cor": MG_COR, "": MG_SOL}
 
 EXPORTED_SYMBOLS = [
-    "mg_create", "mg_destroy", "mg_last_error", "mg_launch_count", "mg_set_operator", "mg_set_boundary",
+    "mg_create", "mg_create_slab", "mg_field_pointer", "mg_destroy", "mg_last_error", "mg_launch_count", "mg_set_operator", "mg_set_boundary",
     "mg_set_coarse_solver", "mg_add_smoother", "mg_clear_smoothers", "mg_upload", "mg_download",
     "mg_upload_device", "mg_save_initial_guess", "mg_restore_initial_guess", "mg_exec_ops", "mg_build_cycle",
     "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_set_outer_operator",
@@ -150,16 +150,27 @@ def smoother_tables(stmt: lowering.LocalSolve, dimension: int, dtype):
 class Workspace:
     """One level hierarchy on one GPU.  Reused across individuals of the same problem."""
 
-    def __init__(self, dimension, min_level, max_level, n_fields, dtype="f64", device=0, lib=None):
+    def __init__(self, dimension, min_level, max_level, n_fields, dtype="f64", device=0, lib=None, slab=None):
+        """`slab` = {level: (first owned plane, last owned plane)} makes a z-slab of a domain-decomposed
+        3D grid (mg_create_slab); host arrays are then [nz][n][n] with one ghost plane on either side."""
         self.lib = lib or load_library()
         self.dimension, self.min_level, self.max_level = dimension, min_level, max_level
         self.n_fields = n_fields
         self.dtype = dtype
         self.np_dtype = np.complex128 if dtype == "c128" else np.float64
         self.device = device
+        self.slab = dict(slab) if slab else None
         self._h = C.c_void_p()
-        self._check(self.lib.mg_create(C.byref(self._h), dimension, min_level, max_level, n_fields,
-                                       MG_C128 if dtype == "c128" else MG_F64, device))
+        code = MG_C128 if dtype == "c128" else MG_F64
+        if self.slab:
+            if dimension != 3:
+                raise EngineError("z-slabs exist for 3D grids only")
+            count = max_level - min_level + 1
+            zb = (C.c_int32 * count)(*[self.slab[level][0] for level in range(min_level, max_level + 1)])
+            ze = (C.c_int32 * count)(*[self.slab[level][1] for level in range(min_level, max_level + 1)])
+            self._check(self.lib.mg_create_slab(C.byref(self._h), min_level, max_level, n_fields, code, device, zb, ze))
+        else:
+            self._check(self.lib.mg_create(C.byref(self._h), dimension, min_level, max_level, n_fields, code, device))
         self._smoother_cache: Dict[tuple, int] = {}
         self._operators: Dict[int, list] = {}
 
@@ -287,12 +298,35 @@ class Workspace:
         return (MgOp * len(flat))(*flat)
 
     # -- data ------------------------------------------------------------------------------------
-    def _dense(self, level, array):
+    def shape(self, level):
+        """Host array shape of a field on `level` (slab: [owned planes + 2][n][n])."""
         n = 2 ** level + 1
+        if self.slab:
+            zb, ze = self.slab[level]
+            return (ze - zb + 3, n, n)
+        return (n,) * self.dimension
+
+    def _dense(self, level, array):
         a = np.ascontiguousarray(array, dtype=self.np_dtype)
-        if a.shape != (n,) * self.dimension:
-            raise EngineError(f"array shape {a.shape} does not match level {level}")
+        if a.shape != self.shape(level):
+            raise EngineError(f"array shape {a.shape} does not match level {level} ({self.shape(level)})")
         return a
+
+    def field_view(self, kind: str, level: int, field: int):
+        """Zero-copy torch view [nz][n][pitch] of a device field array (current solution buffer for
+        "sol"): planes are contiguous, so a halo exchange sends `view[k]` as it is."""
+        import torch
+        ptr, n, pitch, nz, z0 = C.c_void_p(), C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+        self._check(self.lib.mg_field_pointer(self._h, _FIELD[kind], level, field, C.byref(ptr), C.byref(n),
+                                              C.byref(pitch), C.byref(nz), C.byref(z0)))
+        shape = (nz.value, n.value, pitch.value) if self.dimension == 3 else (n.value, pitch.value)
+
+        class _Raw:
+            pass
+        raw = _Raw()
+        raw.__cuda_array_interface__ = {"shape": shape, "typestr": "<c16" if self.dtype == "c128" else "<f8",
+                                        "data": (ptr.value, False), "version": 2}
+        return torch.as_tensor(raw, device=torch.device("cuda", self.device))
 
     def upload(self, kind: str, level: int, field: int, array):
         a = self._dense(level, array)
@@ -302,8 +336,7 @@ class Workspace:
         self._check(self.lib.mg_upload_device(self._h, _FIELD[kind], level, field, C.c_void_p(device_ptr)))
 
     def download(self, kind: str, level: int, field: int) -> np.ndarray:
-        n = 2 ** level + 1
-        out = np.empty((n,) * self.dimension, dtype=self.np_dtype)
+        out = np.empty(self.shape(level), dtype=self.np_dtype)
         self._check(self.lib.mg_download(self._h, _FIELD[kind], level, field, out.ctypes.data_as(C.c_void_p)))
         return out
 

@@ -79,6 +79,13 @@ typedef struct {
 /* ---- lifetime ------------------------------------------------------------------------ */
 int mg_create(mg_workspace** out, int dimension, int min_level, int max_level, int n_fields,
               int dtype, int device);
+/* 3D z-slab of a domain-decomposed grid (BASELINE.json configs[2]; no reference counterpart: the
+ * reference runs one block / one fragment, example_problems/lib/domain_onePatch.knowledge:4-9).
+ * On level min_level + i the workspace owns the global interior planes z_begin[i] .. z_end[i] and
+ * holds one more plane on either side (a neighbour's data, filled by the caller's halo exchange, or
+ * the global Dirichlet plane).  Host arrays of mg_upload / mg_download are [nz][n][n]. */
+int mg_create_slab(mg_workspace** out, int min_level, int max_level, int n_fields, int dtype, int device,
+                   const int32_t* z_begin, const int32_t* z_end);
 int mg_destroy(mg_workspace* ws);
 const char* mg_last_error(void);
 /* number of kernels launched (directly or through graph replays) since creation */
@@ -108,6 +115,11 @@ int mg_upload(mg_workspace* ws, int field_kind, int level, int field, const void
 int mg_download(mg_workspace* ws, int field_kind, int level, int field, void* host);
 /* copy of device-resident dense data (same layout as the host arrays) */
 int mg_upload_device(mg_workspace* ws, int field_kind, int level, int field, const void* device_ptr);
+/* device address and geometry of a field array (current solution buffer for MG_SOL): rows of `pitch`
+ * elements, n rows per plane, nz planes, local plane 0 = global plane z0.  For zero-copy halo
+ * exchange by the caller (NCCL send/recv of whole planes, which are contiguous). */
+int mg_field_pointer(mg_workspace* ws, int field_kind, int level, int field, void** device_ptr, int32_t* n,
+                     int32_t* pitch, int32_t* nz, int32_t* z0);
 /* remember / restore the finest-level solution (initial guess for repeated samples) */
 int mg_save_initial_guess(mg_workspace* ws);
 int mg_restore_initial_guess(mg_workspace* ws);
