@@ -46,7 +46,7 @@ extern "C" int mg_create_slab(mg_workspace** out, int min_level, int max_level, 
     if (!z_begin || !z_end) return fail(MG_ERR_INVALID, "slab plane ranges are null");
     for (int level = min_level; level <= max_level; ++level) {
         const int n = (1 << level) + 1, zb = z_begin[level - min_level], ze = z_end[level - min_level];
-        if (zb < 1 || ze > n - 2 || ze < zb) return fail(MG_ERR_INVALID, "slab must own a non-empty range of interior planes");
+        if (zb < 1 || ze > n - 2 || ze < zb - 1) return fail(MG_ERR_INVALID, "slab plane range outside the interior");
     }
     return create_impl(out, 3, min_level, max_level, n_fields, dtype, device, z_begin, z_end);
 }

@@ -124,9 +124,12 @@ int exec_smooth(mg_workspace* ws, const mg_op& op) {
     const T* w = static_cast<const T*>(sm.d_w);
     FieldSet<T> rhs = fieldset<T>(lv.rhs);
     if (sm.point) {
-        if (ws->use_fast && fast_smooth<T, D, F>(ws, lv, sm)) return MG_OK;
-        const int colours = sm.colored ? 2 : 1;
-        for (int c = 0; c < colours; ++c) {
+        if (ws->use_fast && op.src == 0 && fast_smooth<T, D, F>(ws, lv, sm)) return MG_OK;
+        // op.src selects the colour passes of a coloured smoother: 0 = both (one op = one sweep),
+        // 1 = first colour only, 2 = second colour only (domain decomposition exchanges halos in between)
+        const int c_begin = (sm.colored && op.src == 2) ? 1 : 0;
+        const int c_end = sm.colored ? (op.src == 1 ? 1 : 2) : 1;
+        for (int c = c_begin; c < c_end; ++c) {
             FieldSet<T> src = cur_sol<T>(lv);
             FieldSet<T> dst = src;
             for (int s = 0; s < sm.m; ++s) {
@@ -380,8 +383,10 @@ int tail_append(mg_workspace* ws, const mg_op& op) {
             Smoother& sm = ws->smoothers[op.smoother];
             if (sm.level != op.level) return fail(MG_ERR_INVALID, "smoother registered for another level");
             if (lv.op_dirty) return fail(MG_ERR_STATE, "operator not uploaded (prepare not run)");
-            const int passes = (sm.point && sm.colored) ? 2 : 1;
-            for (int c = 0; c < passes; ++c) {
+            const bool coloured = sm.point && sm.colored;
+            const int c_begin = (coloured && op.src == 2) ? 1 : 0;
+            const int c_end = coloured ? (op.src == 1 ? 1 : 2) : 1;
+            for (int c = c_begin; c < c_end; ++c) {
                 FieldSet<T> src = cur_sol<T>(lv);
                 FieldSet<T> dst = src;
                 bool flip[MG_MAX_FIELDS] = {};

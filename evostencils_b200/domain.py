@@ -1,0 +1,377 @@
+"""Domain decomposition of one 3D multigrid solve over the GPUs of a node (BASELINE.json configs[2]:
+3D Poisson 512^3, V/W-cycles with red-black GS, 2/4/8 GPUs, halo exchange over NVLink).
+
+The reference has no counterpart: its generated solvers run one block / one fragment with OpenMP
+(/root/reference/example_problems/lib/domain_onePatch.knowledge:4-9,
+lib/parallelization_pureOmp.knowledge:2-9; `mpi_enabled = false`).  Design:
+
+* 1-D slabs along z (the slowest axis: a plane of n x pitch elements is contiguous, so a halo plane
+  is sent as it lies in the field array -- no pack kernels).  Split points are multiples of
+  2^(max_level - dd_min_level + 1) cells, so they coincide on every decomposed level (and one below) and restriction /
+  prolongation need one ghost plane only.  Rank r owns the global planes (s_r, s_{r+1}] of a level.
+* every op of the lowered cycle is executed by the rank-local slab workspace (mg_create_slab: the
+  same CUDA kernels, geometry {nz, z0}); after each write of a solution-type field -- every colour
+  pass of a red-black sweep, prolongation+correction -- and after a residual that a restriction
+  reads, the two boundary planes are exchanged with the neighbours;
+* levels below `dd_min_level` are agglomerated: the restricted right-hand side is all-gathered and
+  every rank runs the coarse part of the cycle redundantly on a whole-grid workspace (no scatter);
+* the residual norm is the square root of the rank-ordered sum of the local sums of squares.
+
+Ranks are *virtual*: a process drives the ranks listed in `local_ranks`.  With torch.distributed
+(one process per GPU, NCCL) that is its own rank and neighbours are reached by send/recv; in the
+single-GPU parity tests one process drives all ranks and the exchange is a device copy, which
+executes exactly the same schedule."""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence, Tuple
+
+from . import lowering
+
+
+# ----------------------------------------------------------------------------------------
+# partition
+# ----------------------------------------------------------------------------------------
+
+def slab_splits(max_level: int, dd_min_level: int, world: int) -> List[int]:
+    """Split points s_0 = 0 < s_1 < ... < s_world = 2^max_level (in fine cells / plane indices)."""
+    units = 2 ** (dd_min_level - 1)          # split points must also exist one level below dd_min_level
+    if units < world:
+        raise ValueError(f"level {dd_min_level} has {2 * units} cells along z: too few for {world} slabs of >= 2")
+    unit = 2 ** (max_level - dd_min_level + 1)
+    return [unit * ((r * units) // world) for r in range(world)] + [2 ** max_level]
+
+
+def owned_planes(level: int, max_level: int, splits: Sequence[int], rank: int) -> Tuple[int, int]:
+    """First and last global interior plane rank `rank` owns on `level` (empty when last < first)."""
+    shift = max_level - level
+    if any(s % (1 << shift) for s in splits):
+        raise ValueError("split points do not exist on this level")
+    lo, hi = splits[rank] >> shift, splits[rank + 1] >> shift
+    return lo + 1, min(hi, 2 ** level - 1)
+
+
+def slab_ranges(min_level: int, max_level: int, splits: Sequence[int], rank: int) -> Dict[int, Tuple[int, int]]:
+    return {level: owned_planes(level, max_level, splits, rank) for level in range(min_level, max_level + 1)}
+
+
+# ----------------------------------------------------------------------------------------
+# communication between (virtual) ranks: torch tensors, NCCL on the box / gloo in CPU tests
+# ----------------------------------------------------------------------------------------
+
+class SlabComm:
+    """Neighbour exchange and gathers between the slabs of one decomposed solve.
+
+    `local_ranks`: the virtual ranks this process drives.  `dist` = torch.distributed when the other
+    ranks live in other processes (process rank == virtual rank), else None (all ranks local)."""
+
+    def __init__(self, world: int, local_ranks: Sequence[int], dist=None, group=None):
+        self.world = world
+        self.local_ranks = list(local_ranks)
+        self.dist = dist
+        self.group = group
+        if dist is None and sorted(self.local_ranks) != list(range(world)):
+            raise ValueError("without torch.distributed one process must drive every rank")
+        if dist is not None and len(self.local_ranks) != 1:
+            raise ValueError("with torch.distributed a process drives exactly one rank")
+        self.bytes_sent = 0
+
+    @staticmethod
+    def from_environment(group=None) -> "SlabComm":
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            return SlabComm(dist.get_world_size(group), [dist.get_rank(group)], dist, group)
+        return SlabComm(1, [0])
+
+    def exchange_halos(self, views: Dict[int, object]):
+        """views[rank] = tensor [nz][...] of that rank's slab; local planes 1 .. nz-2 are owned.
+        Fills plane 0 from the lower neighbour's last owned plane and plane nz-1 from the upper
+        neighbour's first owned plane.  Slabs without owned planes (nz == 2) take no part."""
+        if self.dist is None:
+            for r in range(self.world - 1):
+                lo, hi = views[r], views[r + 1]
+                if lo.shape[0] < 3 or hi.shape[0] < 3:
+                    continue
+                hi[0].copy_(lo[lo.shape[0] - 2])
+                lo[lo.shape[0] - 1].copy_(hi[1])
+                self.bytes_sent += 2 * lo[0].numel() * lo.element_size()
+            return
+        (r,) = self.local_ranks
+        v = views[r]
+        if v.shape[0] < 3:
+            return
+        ops = []
+        P2POp, isend, irecv = self.dist.P2POp, self.dist.isend, self.dist.irecv
+        if r > 0:
+            ops.append(P2POp(isend, v[1], r - 1, self.group))
+            ops.append(P2POp(irecv, v[0], r - 1, self.group))
+        if r < self.world - 1:
+            ops.append(P2POp(isend, v[v.shape[0] - 2], r + 1, self.group))
+            ops.append(P2POp(irecv, v[v.shape[0] - 1], r + 1, self.group))
+        self.bytes_sent += (len(ops) // 2) * v[0].numel() * v.element_size()
+        if ops:
+            for req in self.dist.batch_isend_irecv(ops):
+                req.wait()
+
+    def gather_planes(self, owned: Dict[int, object], counts: Sequence[int]):
+        """owned[rank] = tensor [counts[rank]][...] (the rank's owned planes, possibly empty).
+        -> the concatenation over ranks, on every rank (a tensor per local rank)."""
+        import torch
+        if self.dist is None:
+            full = torch.cat([owned[r] for r in range(self.world)], dim=0)
+            return {r: full for r in self.local_ranks}
+        (r,) = self.local_ranks
+        mine = owned[r].contiguous()
+        m = max(counts)
+        padded = torch.zeros((m,) + tuple(mine.shape[1:]), dtype=mine.dtype, device=mine.device)
+        padded[: counts[r]] = mine
+        out = [torch.empty_like(padded) for _ in range(self.world)]
+        self.dist.all_gather(out, padded, group=self.group)
+        self.bytes_sent += padded.numel() * padded.element_size()
+        return {r: torch.cat([out[q][: counts[q]] for q in range(self.world)], dim=0)}
+
+    def sum_in_rank_order(self, values: Dict[int, float]) -> float:
+        """Deterministic: every rank adds the world's values in rank order."""
+        import torch
+        if self.dist is None:
+            total = 0.0
+            for r in range(self.world):
+                total += values[r]
+            return total
+        (r,) = self.local_ranks
+        device = "cuda" if self.dist.get_backend(self.group) == "nccl" else "cpu"
+        mine = torch.tensor([values[r]], dtype=torch.float64, device=device)
+        out = [torch.empty_like(mine) for _ in range(self.world)]
+        self.dist.all_gather(out, mine, group=self.group)
+        total = 0.0
+        for t in out:
+            total += float(t.item())
+        return total
+
+
+# ----------------------------------------------------------------------------------------
+# the decomposed solve
+# ----------------------------------------------------------------------------------------
+
+def default_dd_min_level(min_level: int, world: int) -> int:
+    """Coarsest decomposed level: every rank still owns >= 4 planes (SURVEY.md 8e agglomerates below)."""
+    return max(min_level + 1, int(math.ceil(math.log2(4 * world))))
+
+
+class _Local:
+    def __init__(self, rank, slab, coarse):
+        self.rank, self.slab, self.coarse = rank, slab, coarse
+
+
+class DomainDecomposedSolver:
+    """One 3D solve spread over `comm.world` slabs.  Same op vocabulary as the single-GPU engine
+    (`lowering.Program.ops`, unfused), same kernels, same results bit for bit."""
+
+    def __init__(self, problem, min_level: int, max_level: int, comm: SlabComm, dd_min_level: Optional[int] = None,
+                 device_of=None, params: Optional[dict] = None):
+        from .engine import EngineError, Workspace
+        if problem.dimension != 3:
+            raise EngineError("domain decomposition is implemented for 3D grids")
+        self.problem, self.comm = problem, comm
+        self.min_level, self.max_level = min_level, max_level
+        self.dd_min_level = default_dd_min_level(min_level, comm.world) if dd_min_level is None else dd_min_level
+        if not min_level < self.dd_min_level <= max_level:
+            raise EngineError("dd_min_level must lie in (min_level, max_level]")
+        self.base = self.dd_min_level - 1           # finest replicated level = extra coarse level of the slabs
+        self.splits = slab_splits(max_level, self.dd_min_level, comm.world)
+        self.params = dict(problem.parameters)
+        self.params.update(params or {})
+        device_of = device_of or (lambda rank: 0)
+        self.locals: List[_Local] = []
+        for r in comm.local_ranks:
+            ranges = slab_ranges(self.base, max_level, self.splits, r)
+            slab = Workspace(3, self.base, max_level, problem.n_fields, problem.dtype, device_of(r), slab=ranges)
+            coarse = Workspace(3, min_level, self.base, problem.n_fields, problem.dtype, device_of(r))
+            for ws in (slab, coarse):
+                for level in range(ws.min_level, ws.max_level + 1):
+                    ws.set_operator(level, lowering.operator_table(problem.system_operator(level, 0, self.params)))
+            coarse.set_coarse_solver(problem.solver.cgs, problem.solver.cgs_max_iterations,
+                                     problem.solver.cgs_target_reduction)
+            self.locals.append(_Local(r, slab, coarse))
+        self._pending_coarse: List[object] = []
+        self.halo_exchanges = 0
+
+    def close(self):
+        for loc in self.locals:
+            loc.slab.close()
+            loc.coarse.close()
+        self.locals = []
+
+    # -- data ------------------------------------------------------------------------------------
+    def plane_range(self, rank: int, level: int) -> Tuple[int, int]:
+        """Global planes [z0, z0 + nz) held by `rank` on `level` (owned + ghost/boundary planes)."""
+        zb, ze = owned_planes(level, self.max_level, self.splits, rank)
+        return zb - 1, ze + 2
+
+    def set_fields(self, rhs, u0):
+        """rhs, u0: per field either a full host array [n][n][n] or a callable (z_lo, z_hi) -> slab array."""
+        L = self.max_level
+        for loc in self.locals:
+            z_lo, z_hi = self.plane_range(loc.rank, L)
+            for f in range(self.problem.n_fields):
+                for kind, src in (("rhs", rhs[f]), ("sol", u0[f])):
+                    loc.slab.upload(kind, L, f, src(z_lo, z_hi) if callable(src) else src[z_lo:z_hi])
+
+    def gather_solution(self, field: int = 0):
+        """Full finest-level solution on the host (tests; not part of the timed path)."""
+        import numpy as np
+        import torch
+        L = self.max_level
+        owned, counts = {}, []
+        for r in range(self.comm.world):
+            zb, ze = owned_planes(L, L, self.splits, r)
+            counts.append(ze - zb + 1)
+        for loc in self.locals:
+            v = loc.slab.field_view("sol", L, field)
+            owned[loc.rank] = v[1: v.shape[0] - 1]
+        full = self.comm.gather_planes(owned, counts)[self.locals[0].rank]
+        n = 2 ** L + 1
+        out = np.zeros((n, n, n), dtype=self.locals[0].slab.np_dtype)
+        out[1:-1] = full[:, :, :n].cpu().numpy()
+        first = [loc for loc in self.locals if loc.rank == 0]
+        last = [loc for loc in self.locals if loc.rank == self.comm.world - 1]
+        if first:
+            out[0] = first[0].slab.download("sol", L, field)[0]
+        if last:
+            out[-1] = last[0].slab.download("sol", L, field)[-1]
+        return out
+
+    # -- op interpreter ----------------------------------------------------------------------------
+    def _sync(self):
+        import torch
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+
+    def _flush_coarse(self):
+        if self._pending_coarse:
+            for loc in self.locals:
+                loc.coarse.exec_ops(self._pending_coarse)
+            self._pending_coarse = []
+
+    def _slab_exec(self, op):
+        for loc in self.locals:
+            loc.slab.exec_ops([op])
+
+    def _exchange(self, kind: str, level: int):
+        for f in range(self.problem.n_fields):
+            self.comm.exchange_halos({loc.rank: loc.slab.field_view(kind, level, f) for loc in self.locals})
+        self._sync()
+        self.halo_exchanges += 1
+
+    def run_ops(self, ops: Sequence[object]):
+        import copy
+        base, dd = self.base, self.dd_min_level
+        for op in ops:
+            kind = op.kind
+            if kind in ("residual_restrict",):
+                raise ValueError("pass the unfused op list: the decomposed restriction reads exchanged residual planes")
+            if kind == "smooth":
+                if op.level <= base:
+                    self._pending_coarse.append(op)
+                    continue
+                self._flush_coarse()
+                if op.colored:
+                    for colour_pass in (1, 2):
+                        half = copy.copy(op)
+                        half.colour_pass = colour_pass
+                        self._slab_exec(half)
+                        self._exchange("sol", op.level)
+                else:
+                    self._slab_exec(op)
+                    self._exchange("sol", op.level)
+            elif kind == "residual":
+                if op.level <= base:
+                    self._pending_coarse.append(op)
+                    continue
+                self._flush_coarse()
+                self._slab_exec(op)
+                self._exchange("res", op.level)
+            elif kind == "restrict":
+                if op.level < base:
+                    self._pending_coarse.append(op)
+                    continue
+                self._flush_coarse()
+                self._slab_exec(op)
+                if op.level == base:
+                    self._rhs_to_coarse()
+            elif kind == "zero":
+                if op.level <= base:
+                    self._pending_coarse.append(op)
+                else:
+                    self._flush_coarse()
+                    self._slab_exec(op)
+            elif kind == "prolong_add":
+                if op.level <= base:
+                    self._pending_coarse.append(op)
+                    continue
+                self._flush_coarse()
+                if op.level == dd:
+                    self._sol_from_coarse()
+                self._slab_exec(op)
+                self._exchange("sol", op.level)
+            elif kind == "cgs":
+                if op.level != self.min_level or op.inner:
+                    raise ValueError("decomposed solves place the coarse-grid solver on the engine's min level")
+                self._pending_coarse.append(op)
+            else:
+                raise ValueError(f"op kind '{kind}' is not available in a decomposed solve")
+        self._flush_coarse()
+
+    def _rhs_to_coarse(self):
+        """All-gather the restricted right-hand side of level `base` into the replicated workspaces."""
+        level = self.base
+        counts = []
+        for r in range(self.comm.world):
+            zb, ze = owned_planes(level, self.max_level, self.splits, r)
+            counts.append(max(0, ze - zb + 1))
+        for f in range(self.problem.n_fields):
+            owned = {}
+            for loc in self.locals:
+                v = loc.slab.field_view("rhs", level, f)
+                owned[loc.rank] = v[1: 1 + counts[loc.rank]]
+            full = self.comm.gather_planes(owned, counts)
+            for loc in self.locals:
+                loc.coarse.field_view("rhs", level, f)[1:-1].copy_(full[loc.rank])
+        self._sync()
+
+    def _sol_from_coarse(self):
+        """Slab copy of the replicated coarse solution of level `base` (local: every rank has all of it)."""
+        level = self.base
+        for loc in self.locals:
+            z_lo, z_hi = self.plane_range(loc.rank, level)
+            for f in range(self.problem.n_fields):
+                loc.slab.field_view("sol", level, f).copy_(loc.coarse.field_view("sol", level, f)[z_lo:z_hi])
+        self._sync()
+
+    # -- outer iteration ---------------------------------------------------------------------------
+    def residual_norm(self) -> float:
+        partial = {}
+        for loc in self.locals:
+            v = loc.slab.residual_norm(self.max_level)
+            partial[loc.rank] = v * v
+        return math.sqrt(self.comm.sum_in_rank_order(partial))
+
+    def solve(self, ops: Sequence[object], tol: float, max_its: int):
+        """Outer iteration of the generated solver (same conventions as mg_solve)
+        -> (history, converged, milliseconds)."""
+        import time
+        self._sync()
+        t0 = time.perf_counter()
+        history = [self.residual_norm()]
+        converged = False
+        for _ in range(max_its):
+            self.run_ops(ops)
+            r = self.residual_norm()
+            history.append(r)
+            if not math.isfinite(r):
+                break
+            if r < tol * history[0]:
+                converged = True
+                break
+        self._sync()
+        return history, converged, (time.perf_counter() - t0) * 1e3

@@ -268,7 +268,7 @@ class Workspace:
             for op in seq:
                 k = op.kind
                 if k == "smooth":
-                    add(MG_OP_SMOOTH, op.level, op.omega, MG_SOL, self.smoother_handle(op))
+                    add(MG_OP_SMOOTH, op.level, op.omega, int(getattr(op, "colour_pass", 0)), self.smoother_handle(op))
                 elif k == "residual":
                     add(MG_OP_RESIDUAL, op.level)
                 elif k == "restrict":

@@ -72,7 +72,8 @@ typedef struct {
     int32_t kind;        /* mg_op_kind */
     int32_t level;       /* level of the field that is written */
     double  omega;       /* relaxation factor (SMOOTH uses the one baked into its W table) */
-    int32_t src;         /* mg_field read by RESTRICT / PROLONG* */
+    int32_t src;         /* mg_field read by RESTRICT / PROLONG*; SMOOTH with a coloured smoother:
+                            0 = both colour passes, 1 = first colour only, 2 = second colour only */
     int32_t smoother;    /* SMOOTH: handle returned by mg_add_smoother */
 } mg_op;
 
