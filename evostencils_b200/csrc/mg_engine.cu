@@ -68,6 +68,7 @@ static int create_impl(mg_workspace** out, int dimension, int min_level, int max
     ws->dim = dimension; ws->min_level = min_level; ws->max_level = max_level;
     ws->n_fields = n_fields; ws->dtype = dtype; ws->device = device;
     ws->elem = dtype == MG_F64 ? 8 : 16;
+    ws->tail_max_level = dimension == 3 ? 4 : 6;        // <= ~5000 nodes per level: 65^2 or 17^3
     if (const char* v = std::getenv("MG_TAIL_LEVEL")) ws->tail_max_level = std::atoi(v);
     if (const char* v = std::getenv("MG_PDL")) ws->use_pdl = std::atoi(v) != 0;
     MG_CUDA(cudaStreamCreateWithFlags(&ws->stream, cudaStreamNonBlocking));

@@ -124,11 +124,11 @@ int exec_smooth(mg_workspace* ws, const mg_op& op) {
     const T* w = static_cast<const T*>(sm.d_w);
     FieldSet<T> rhs = fieldset<T>(lv.rhs);
     if (sm.point) {
-        if (ws->use_fast && op.src == 0 && fast_smooth<T, D, F>(ws, lv, sm)) return MG_OK;
         // op.src selects the colour passes of a coloured smoother: 0 = both (one op = one sweep),
         // 1 = first colour only, 2 = second colour only (domain decomposition exchanges halos in between)
         const int c_begin = (sm.colored && op.src == 2) ? 1 : 0;
         const int c_end = sm.colored ? (op.src == 1 ? 1 : 2) : 1;
+        if (ws->use_fast && fast_smooth<T, D, F>(ws, lv, sm, c_begin, c_end)) return MG_OK;
         for (int c = c_begin; c < c_end; ++c) {
             FieldSet<T> src = cur_sol<T>(lv);
             FieldSet<T> dst = src;
@@ -195,6 +195,15 @@ int exec_restrict(mg_workspace* ws, const mg_op& op, bool fused) {
         int rc = upload_operator<T>(ws, lf);
         if (rc) return rc;
         if (ws->use_fast && fast_residual_restrict<T, D, F>(ws, lf, lc)) return MG_OK;
+        if constexpr (D == 3) {
+            // 3D star: the fused generic kernel recomputes 27 residuals per coarse node; the specialised
+            // residual kernel + plain restriction moves fewer bytes and is bit-identical
+            if (ws->use_fast && fast_residual<T, D, F>(ws, lf)) {
+                launch_k(ws, k_restrict<T, D, F>, node_grid<D>(lc.g), 128, 0, lc.g, lf.g, fieldset<T>(lf.res), fieldset<T>(lc.rhs));
+                count(ws);
+                return MG_OK;
+            }
+        }
         launch_k(ws, k_residual_restrict<T, D, F>, node_grid<D>(lc.g), 128, 0, 
             lc.g, lf.g, static_cast<const OperatorTable<T>*>(lf.d_op), cur_sol<T>(lf), fieldset<T>(lf.rhs),
             fieldset<T>(lc.rhs));

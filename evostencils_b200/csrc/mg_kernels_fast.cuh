@@ -6,6 +6,7 @@
 #include <cstdlib>
 
 #include "mg_fast2d.cuh"
+#include "mg_fast3d.cuh"
 #include "mg_workspace.cuh"
 
 namespace mg {
@@ -93,9 +94,60 @@ inline bool fast_tile_smooth(mg_workspace* ws, Level& lv, Smoother& sm) {
     return false;
 }
 
+// ---- 3D: 7-point star, whole grids and z-slabs ------------------------------------------------------
+inline Star3D star3d(const Level& lv) {
+    Star3D s;
+    s.cz = lv.star_z; s.cy = lv.star_y; s.cx = lv.star_x; s.cc = lv.star_c;
+    return s;
+}
+
+// threads per CTA of the 3D kernels: the strip of 2*NT columns must tile [0, n-1)
+inline int star3d_nt(const mg_workspace* ws, const Level& lv) {
+    if (!(ws->dim == 3 && ws->dtype == MG_F64 && ws->n_fields == 1 && lv.star)) return 0;
+    static const int enabled = tunable("MG_FAST_3D", 1);
+    if (!enabled) return 0;
+    for (int nt = 128; nt >= 32; nt >>= 1)
+        if ((lv.g.n - 1) % (2 * nt) == 0) return nt;
+    return 0;
+}
+
+template <int MODE>
+inline dim3 launch_star3d(mg_workspace* ws, Level& lv, int nt, const double* u, const double* f, double* out, double w,
+                          int colour, double* partial) {
+    static const int ry_env = tunable("MG_3D_RY", 0), zc_env = tunable("MG_3D_ZCHUNK", 0);
+    const int ry = (ry_env == 2 || ry_env == 4) ? ry_env : 4;
+    const int strips = (lv.g.n - 1) / (2 * nt), bands = (lv.g.n - 2 + ry - 1) / ry, planes = lv.g.nz - 2;
+    int zchunk = zc_env > 0 ? zc_env : 32;
+    while (zchunk > 4 && strips * bands * ((planes + zchunk - 1) / zchunk) < 1024) zchunk >>= 1;
+    dim3 grid(strips, bands, (planes + zchunk - 1) / zchunk);
+    const Star3D s = star3d(lv);
+#define MG_L3(NT_, RY_) launch_k(ws, k_star3d<MODE, NT_, RY_>, grid, NT_, 0, lv.g, s, u, f, out, w, colour, zchunk, partial)
+    if (ry == 4) {
+        if (nt == 128) MG_L3(128, 4); else if (nt == 64) MG_L3(64, 4); else MG_L3(32, 4);
+    } else {
+        if (nt == 128) MG_L3(128, 2); else if (nt == 64) MG_L3(64, 2); else MG_L3(32, 2);
+    }
+#undef MG_L3
+    return grid;
+}
+
 template <typename T, int D, int F>
-inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm) {
+inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm, int c_begin, int c_end) {
+    if constexpr (D == 3 && F == 1 && sizeof(T) == sizeof(double)) {
+        const int nt = star3d_nt(ws, lv);
+        if (!nt || !sm.point || sm.m != 1 || lv.g.nz < 3) return false;
+        const double* rhs = static_cast<const double*>(lv.rhs[0]);
+        for (int c = c_begin; c < c_end; ++c) {
+            const double* src = static_cast<const double*>(lv.sol[lv.cur[0]][0]);
+            double* dst = static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]);
+            launch_star3d<STAR3_SMOOTH>(ws, lv, nt, src, rhs, dst, sm.w00, sm.colored ? c : -1, nullptr);
+            lv.cur[0] ^= 1;
+            fast_count(ws);
+        }
+        return true;
+    }
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
+        if (sm.colored && !(c_begin == 0 && c_end == 2)) return false;        // single colour passes: generic kernel
         if (!star_level_ok<D>(ws, lv, 2) || !sm.point || sm.m != 1) return false;
         static const int rows_j = tunable("MG_JACOBI_ROWS", 0), rows_rb = tunable("MG_RBGS_ROWS", 0);
         const double* src = static_cast<const double*>(lv.sol[lv.cur[0]][0]);
@@ -119,6 +171,14 @@ inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm) {
 
 template <typename T, int D, int F>
 inline bool fast_residual(mg_workspace* ws, Level& lv) {
+    if constexpr (D == 3 && F == 1 && sizeof(T) == sizeof(double)) {
+        const int nt = star3d_nt(ws, lv);
+        if (!nt || lv.g.nz < 3) return false;
+        launch_star3d<STAR3_RESIDUAL>(ws, lv, nt, static_cast<const double*>(lv.sol[lv.cur[0]][0]),
+                                      static_cast<const double*>(lv.rhs[0]), static_cast<double*>(lv.res[0]), 0.0, -1, nullptr);
+        fast_count(ws);
+        return true;
+    }
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         if (!star_level_ok<D>(ws, lv, 2)) return false;
         static const int rows = tunable("MG_RESIDUAL_ROWS", 0);
@@ -133,6 +193,16 @@ inline bool fast_residual(mg_workspace* ws, Level& lv) {
 
 template <typename T, int D, int F>
 inline bool fast_norm(mg_workspace* ws, Level& lv) {
+    if constexpr (D == 3 && F == 1 && sizeof(T) == sizeof(double)) {
+        const int nt = star3d_nt(ws, lv);
+        if (!nt || lv.g.nz < 3) return false;
+        dim3 grid = launch_star3d<STAR3_NORM>(ws, lv, nt, static_cast<const double*>(lv.sol[lv.cur[0]][0]),
+                                              static_cast<const double*>(lv.rhs[0]), nullptr, 0.0, -1,
+                                              static_cast<double*>(lv.partial));
+        lv.norm_count = grid.x * grid.y * grid.z;
+        fast_count(ws);
+        return true;
+    }
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         if (!star_level_ok<D>(ws, lv, 2)) return false;
         static const int rows = tunable("MG_NORM_ROWS", 0);

@@ -152,3 +152,12 @@ def test_decomposed_solve_is_bitwise_the_single_domain_solve(world, lo, hi):
     dd.close()
     assert np.array_equal(got, want)
     assert np.allclose(hist, single_hist, rtol=1e-12, atol=0)
+
+
+@pytest.mark.gpu
+def test_decomposed_solve_with_the_specialised_3d_kernels(monkeypatch):
+    """Levels 6 and 7 run the 2.5-D blocked 7-point kernels on slabs (tail kernel restricted to
+    levels <= 3 so that the grid kernels see slab geometry on the levels above)."""
+    monkeypatch.setenv("MG_TAIL_LEVEL", "3")
+    test_decomposed_solve_is_bitwise_the_single_domain_solve(2, 2, 7)
+    test_decomposed_solve_is_bitwise_the_single_domain_solve(4, 3, 7)

@@ -393,3 +393,25 @@ def test_helmholtz_reference_wave_number_converges():
     assert got[-1] < 1e-7 * got[0]
     assert np.allclose(got[:5], np.array(hist)[:5], rtol=1e-9)
     gen.close()
+
+
+@pytest.mark.parametrize("hi", [6, 7])
+def test_fast_3d_stages_bit_identical(hi):
+    """2.5-D blocked 7-point kernels (levels >= 6 of 3D Poisson) against the oracle and the generic kernels."""
+    from oracle import driver, mg_oracle
+    problem, lo = problems.POISSON_3D, hi - 1
+    ws, h = make_pair(problem, lo, hi, seed=13)
+    run_both(ws, h, [lowering.Op("residual", hi, dst="res")], problem)
+    compare(ws, h, "res", hi, True, "fast 3D residual")
+    got, want = ws.residual_norm(hi), mg_oracle.residual_norm(h, hi)
+    assert abs(got - want) <= 1e-12 * want
+    for partitioning in (ir.Single, ir.RedBlack):
+        stmts = smoother_statements(problem, hi, "collective", partitioning, omega=1.25)
+        for sweep in range(3):
+            run_both(ws, h, stmts, problem)
+        compare(ws, h, "sol", hi, True, f"fast 3D smoother {partitioning.get_name()}")
+    ops = [lowering.Op("residual", hi, dst="res"), lowering.Op("restrict", hi - 1, src="res", dst="rhs")]
+    mg_oracle.run_ops(h, ops, driver.settings_for(problem))
+    ws.exec_ops(ops, fused=True)
+    compare(ws, h, "rhs", hi - 1, True, "3D residual_restrict (fast residual + restriction)")
+    ws.close()
