@@ -177,4 +177,70 @@ __global__ void __launch_bounds__(NT) k_star3d(Geom g, Star3D s, const double* _
     }
 }
 
+// ---- fused prolongation + correction: u += omega * (P e), in place --------------------------------------
+// Thread = two adjacent fine columns (x0 even, x0+1 odd) of RY consecutive fine rows of one plane.
+// Coarse values at column X = x0/2 are loaded by the thread, those at X+1 come from the next lane
+// (lane 31 loads them); every coarse value is shared by 8 fine nodes and served by L1/L2.
+// Summation order of prolong_at: coarse planes outer, rows, columns inner; then the power-of-two scale.
+template <int NT, int RY>
+__global__ void __launch_bounds__(NT) k_prolong3d(Geom gf, Geom gc, const double* __restrict__ e, double* __restrict__ u,
+                                                   double omega) {
+    pdl_sync();
+    const int lane = threadIdx.x & 31;
+    const int x0 = (blockIdx.x * NT + threadIdx.x) * 2;       // even fine column, <= n-3
+    const int X = x0 >> 1;
+    const int n = gf.n;
+    const int y0 = 1 + blockIdx.y * RY;                         // odd
+    const int z = 1 + blockIdx.z;                               // local fine plane 1 .. nz-2
+    const int zg = z + gf.z0;
+    if (zg < 1 || zg > n - 2) return;
+    const int pz = zg & 1;
+    const int Zl = (zg >> 1) - gc.z0;                           // local coarse plane
+    const int Ylo = y0 >> 1;
+    double a[2][RY / 2 + 1], b[2][RY / 2 + 1];
+    double2 uu[RY];
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+#pragma unroll
+        for (int j = 0; j < RY / 2 + 1; ++j) {
+            const int Y = imin(Ylo + j, gc.n - 1);
+            const double* p = e + (long long)(Zl + (k & pz)) * gc.plane + (long long)Y * gc.pitch + X;
+            a[k][j] = ldf1(p);
+            b[k][j] = 0.0;
+            if (lane == 31) b[k][j] = ldf1(p + 1);
+        }
+#pragma unroll
+    for (int i = 0; i < RY; ++i)
+        uu[i] = ldf2(u + (long long)z * gf.plane + (long long)imin(y0 + i, n - 1) * gf.pitch + x0);
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+#pragma unroll
+        for (int j = 0; j < RY / 2 + 1; ++j) {
+            const double nb = __shfl_down_sync(0xffffffffu, a[k][j], 1);
+            if (lane != 31) b[k][j] = nb;
+        }
+#pragma unroll
+    for (int i = 0; i < RY; ++i) {
+        const int y = y0 + i;
+        if (y > n - 2) continue;
+        const int py = y & 1;
+        const int j = (y >> 1) - Ylo;
+        // even column (px = 0): a only ; odd column (px = 1): a, b alternating
+        double s0 = a[0][j], s1 = a[0][j] + b[0][j];
+        if (py) { s0 = s0 + a[0][j + 1]; s1 = s1 + a[0][j + 1]; s1 = s1 + b[0][j + 1]; }
+        if (pz) {
+            s0 = s0 + a[1][j]; s1 = s1 + a[1][j]; s1 = s1 + b[1][j];
+            if (py) { s0 = s0 + a[1][j + 1]; s1 = s1 + a[1][j + 1]; s1 = s1 + b[1][j + 1]; }
+        }
+        const int k0 = py + pz, k1 = 1 + py + pz;
+        if (k0 > 0) s0 = (k0 == 1 ? 0.5 : 0.25) * s0;
+        s1 = (k1 == 1 ? 0.5 : (k1 == 2 ? 0.25 : 0.125)) * s1;
+        double2 v = uu[i];
+        if (x0 >= 1) v.x = v.x + omega * s0;
+        v.y = v.y + omega * s1;
+        st2(u + (long long)z * gf.plane + (long long)y * gf.pitch + x0, v);
+    }
+}
+
 }  // namespace mg

@@ -235,6 +235,19 @@ inline bool fast_residual_restrict(mg_workspace* ws, Level& lf, Level& lc) {
 
 template <typename T, int D, int F>
 inline bool fast_prolong_add(mg_workspace* ws, Level& lf, Level& lc, const FieldSet<T>& src, double omega) {
+    if constexpr (D == 3 && F == 1 && sizeof(T) == sizeof(double)) {
+        const int nt = star3d_nt(ws, lf);
+        if (!nt || lf.g.nz < 3) return false;
+        constexpr int RY = 4;
+        dim3 grid((lf.g.n - 1) / (2 * nt), (lf.g.n - 2 + RY - 1) / RY, lf.g.nz - 2);
+        const double* e = reinterpret_cast<const double*>(src.p[0]);
+        double* u = static_cast<double*>(lf.sol[lf.cur[0]][0]);
+        if (nt == 128) launch_k(ws, k_prolong3d<128, RY>, grid, 128, 0, lf.g, lc.g, e, u, omega);
+        else if (nt == 64) launch_k(ws, k_prolong3d<64, RY>, grid, 64, 0, lf.g, lc.g, e, u, omega);
+        else launch_k(ws, k_prolong3d<32, RY>, grid, 32, 0, lf.g, lc.g, e, u, omega);
+        fast_count(ws);
+        return true;
+    }
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         if (ws->dtype != MG_F64 || (lf.g.n - 1) % (4 * FAST_NT) != 0) return false;
         static const int rows_env = tunable("MG_PROLONG_ROWS", 0);

@@ -414,4 +414,6 @@ def test_fast_3d_stages_bit_identical(hi):
     mg_oracle.run_ops(h, ops, driver.settings_for(problem))
     ws.exec_ops(ops, fused=True)
     compare(ws, h, "rhs", hi - 1, True, "3D residual_restrict (fast residual + restriction)")
+    run_both(ws, h, [lowering.Op("prolong_add", hi, omega=0.55, src="sol", dst="sol")], problem)
+    compare(ws, h, "sol", hi, True, "fast 3D prolong_add")
     ws.close()
