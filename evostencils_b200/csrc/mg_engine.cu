@@ -144,6 +144,20 @@ static void free_cycles(mg_workspace* ws) {
     ws->cycles.clear();
 }
 
+// drop the instantiated graphs (they are bound to a stream's capture) but keep the op lists
+static void free_cycles_graphs(mg_workspace* ws) {
+    for (auto& c : ws->cycles) {
+        for (auto& kv : c.variants)
+            if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+        c.variants.clear();
+    }
+    if (ws->outer_graph) {
+        cudaGraphExecDestroy(ws->outer_graph);
+        ws->outer_graph = nullptr;
+        ws->outer_graph_cycle = -1;
+    }
+}
+
 extern "C" int mg_destroy(mg_workspace* ws) {
     if (!ws) return MG_OK;
     cudaSetDevice(ws->device);
@@ -168,6 +182,7 @@ extern "C" int mg_destroy(mg_workspace* ws) {
     if (ws->mark[0]) cudaEventDestroy(ws->mark[0]);
     if (ws->mark[1]) cudaEventDestroy(ws->mark[1]);
     if (ws->flush_buf) cudaFree(ws->flush_buf);
+    if (ws->own_stream) ws->stream = ws->own_stream;          // a borrowed stream is not ours to destroy
     if (ws->stream) cudaStreamDestroy(ws->stream);
     delete ws;
     return MG_OK;

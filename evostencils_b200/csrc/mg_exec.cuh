@@ -262,11 +262,14 @@ int prepare(mg_workspace* ws) {
     ws->cgs_smem_bytes = bytes <= 200 * 1024 ? bytes : 0;
     if (!ws->tail) ws->tail = new TailProgram();
     ws->tail->n_cmds = 0;
-    if (bytes <= 200 * 1024) {
-        MG_CUDA(cudaFuncSetAttribute(k_coarse_cg<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        MG_CUDA(cudaFuncSetAttribute(k_coarse_bicgstab<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-        MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    } else if (ws->cgs_work_bytes < bytes) {
+    // The opt-in is a property of the function, not of the workspace: several workspaces live in
+    // one process (slab + replicated coarse levels, one per virtual rank), so always allow the
+    // maximum instead of this workspace's size.
+    const int smem_cap = 200 * 1024;
+    MG_CUDA(cudaFuncSetAttribute(k_coarse_cg<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    MG_CUDA(cudaFuncSetAttribute(k_coarse_bicgstab<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    if (bytes > (size_t)smem_cap && ws->cgs_work_bytes < bytes) {
         if (ws->cgs_work) cudaFree(ws->cgs_work);
         MG_CUDA(cudaMalloc(&ws->cgs_work, bytes));
         ws->cgs_work_bytes = bytes;

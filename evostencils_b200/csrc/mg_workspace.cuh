@@ -91,6 +91,7 @@ struct mg_workspace {
     size_t elem = 8;
     bool slab = false;                          // 3D z-slab of a domain-decomposed grid (mg_create_slab)
     cudaStream_t stream = nullptr;
+    cudaStream_t own_stream = nullptr;          // set once a caller's stream has been installed (mg_set_stream)
     std::vector<mg::Level> levels;              // index = level - min_level
     std::vector<mg::Smoother> smoothers;
     std::vector<mg::Cycle> cycles;

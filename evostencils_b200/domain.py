@@ -154,8 +154,10 @@ class SlabComm:
 # ----------------------------------------------------------------------------------------
 
 def default_dd_min_level(min_level: int, world: int) -> int:
-    """Coarsest decomposed level: every rank still owns >= 4 planes (SURVEY.md 8e agglomerates below)."""
-    return max(min_level + 1, int(math.ceil(math.log2(4 * world))))
+    """Coarsest decomposed level: every rank still owns >= 32 planes; the levels below are agglomerated
+     -- an exchange costs tens of microseconds of latency whatever the plane size, and a
+    replicated 65^3 level costs less than one exchange."""
+    return max(min_level + 1, int(math.ceil(math.log2(32 * world))))
 
 
 class _Local:
@@ -174,7 +176,8 @@ class DomainDecomposedSolver:
             raise EngineError("domain decomposition is implemented for 3D grids")
         self.problem, self.comm = problem, comm
         self.min_level, self.max_level = min_level, max_level
-        self.dd_min_level = default_dd_min_level(min_level, comm.world) if dd_min_level is None else dd_min_level
+        self.dd_min_level = (min(max_level, default_dd_min_level(min_level, comm.world)) if dd_min_level is None
+                             else dd_min_level)
         if not min_level < self.dd_min_level <= max_level:
             raise EngineError("dd_min_level must lie in (min_level, max_level]")
         self.base = self.dd_min_level - 1           # finest replicated level = extra coarse level of the slabs
@@ -183,6 +186,8 @@ class DomainDecomposedSolver:
         self.params.update(params or {})
         device_of = device_of or (lambda rank: 0)
         self.locals: List[_Local] = []
+        self._streams = {}
+        self._previous_streams = {}
         for r in comm.local_ranks:
             ranges = slab_ranges(self.base, max_level, self.splits, r)
             slab = Workspace(3, self.base, max_level, problem.n_fields, problem.dtype, device_of(r), slab=ranges)
@@ -192,11 +197,34 @@ class DomainDecomposedSolver:
                     ws.set_operator(level, lowering.operator_table(problem.system_operator(level, 0, self.params)))
             coarse.set_coarse_solver(problem.solver.cgs, problem.solver.cgs_max_iterations,
                                      problem.solver.cgs_target_reduction)
+            for ws in (slab, coarse):
+                ws.exec_ops([])                     # one-time preparation (operator upload, kernel attributes)
+                ws.set_stream(self._torch_stream(device_of(r)))
             self.locals.append(_Local(r, slab, coarse))
         self._pending_coarse: List[object] = []
         self.halo_exchanges = 0
 
+    def _torch_stream(self, device: int) -> int:
+        """Kernels, halo exchanges (NCCL on torch's current stream) and device copies share one stream,
+        so a cycle is enqueued without any host synchronisation.  A dedicated non-default stream per
+        device is made torch's current stream for the lifetime of the solver (the legacy default
+        stream has handle 0 and cannot be handed to the engine)."""
+        import torch
+        if not torch.cuda.is_available():
+            return 0
+        if device not in self._streams:
+            self._previous_streams[device] = torch.cuda.current_stream(device)
+            self._streams[device] = torch.cuda.Stream(device)
+            torch.cuda.set_stream(self._streams[device])
+        return int(self._streams[device].cuda_stream)
+
     def close(self):
+        self._sync()
+        if self._previous_streams:
+            import torch
+            for device, stream in self._previous_streams.items():
+                torch.cuda.set_stream(stream)
+            self._previous_streams = {}
         for loc in self.locals:
             loc.slab.close()
             loc.coarse.close()
@@ -250,17 +278,16 @@ class DomainDecomposedSolver:
     def _flush_coarse(self):
         if self._pending_coarse:
             for loc in self.locals:
-                loc.coarse.exec_ops(self._pending_coarse)
+                loc.coarse.enqueue_ops(self._pending_coarse)
             self._pending_coarse = []
 
     def _slab_exec(self, op):
         for loc in self.locals:
-            loc.slab.exec_ops([op])
+            loc.slab.enqueue_ops([op])
 
     def _exchange(self, kind: str, level: int):
         for f in range(self.problem.n_fields):
             self.comm.exchange_halos({loc.rank: loc.slab.field_view(kind, level, f) for loc in self.locals})
-        self._sync()
         self.halo_exchanges += 1
 
     def run_ops(self, ops: Sequence[object]):
@@ -337,7 +364,6 @@ class DomainDecomposedSolver:
             full = self.comm.gather_planes(owned, counts)
             for loc in self.locals:
                 loc.coarse.field_view("rhs", level, f)[1:-1].copy_(full[loc.rank])
-        self._sync()
 
     def _sol_from_coarse(self):
         """Slab copy of the replicated coarse solution of level `base` (local: every rank has all of it)."""
@@ -346,7 +372,6 @@ class DomainDecomposedSolver:
             z_lo, z_hi = self.plane_range(loc.rank, level)
             for f in range(self.problem.n_fields):
                 loc.slab.field_view("sol", level, f).copy_(loc.coarse.field_view("sol", level, f)[z_lo:z_hi])
-        self._sync()
 
     # -- outer iteration ---------------------------------------------------------------------------
     def residual_norm(self) -> float:

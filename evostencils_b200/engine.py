@@ -31,7 +31,7 @@ _FIELD = {"sol": MG_SOL, "rhs": MG_RHS, "res": MG_RES, "cor": MG_COR, "": MG_SOL
 EXPORTED_SYMBOLS = [
     "mg_create", "mg_create_slab", "mg_field_pointer", "mg_destroy", "mg_last_error", "mg_launch_count", "mg_set_operator", "mg_set_boundary",
     "mg_set_coarse_solver", "mg_add_smoother", "mg_clear_smoothers", "mg_upload", "mg_download",
-    "mg_upload_device", "mg_save_initial_guess", "mg_restore_initial_guess", "mg_exec_ops", "mg_build_cycle",
+    "mg_upload_device", "mg_save_initial_guess", "mg_restore_initial_guess", "mg_exec_ops", "mg_enqueue_ops", "mg_set_stream", "mg_build_cycle",
     "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_set_outer_operator",
     "mg_solve_bicgstab", "mg_synchronize",
     "mg_time_ops", "mg_profile_ops", "mg_mark", "mg_elapsed", "mg_flush_l2", "mg_set_fast_kernels",
@@ -78,6 +78,9 @@ def load_library(path: Optional[str] = None):
     lib.mg_save_initial_guess.argtypes = [vp]
     lib.mg_restore_initial_guess.argtypes = [vp]
     lib.mg_exec_ops.argtypes = [vp, C.POINTER(MgOp), i32]
+    if path == LIB_PATH or hasattr(lib, "mg_enqueue_ops"):
+        lib.mg_enqueue_ops.argtypes = [vp, C.POINTER(MgOp), i32]
+        lib.mg_set_stream.argtypes = [vp, vp]
     lib.mg_build_cycle.argtypes = [vp, C.POINTER(MgOp), i32, C.POINTER(C.c_int)]
     lib.mg_free_cycles.argtypes = [vp]
     lib.mg_run_cycles.argtypes = [vp, i32, i32, C.POINTER(C.c_float)]
@@ -350,6 +353,15 @@ class Workspace:
     def exec_ops(self, ops, default_cycle=None, fused=False):
         enc = self.encode(lowering.fuse(ops) if fused else ops, default_cycle)
         self._check(self.lib.mg_exec_ops(self._h, enc, len(enc)))
+
+    def enqueue_ops(self, ops, default_cycle=None, fused=False):
+        """Issue the ops on the workspace stream without waiting (see set_stream)."""
+        enc = self.encode(lowering.fuse(ops) if fused else ops, default_cycle)
+        self._check(self.lib.mg_enqueue_ops(self._h, enc, len(enc)))
+
+    def set_stream(self, cuda_stream: int):
+        """Run on the caller's CUDA stream (e.g. torch.cuda.current_stream().cuda_stream); 0 = own stream."""
+        self._check(self.lib.mg_set_stream(self._h, C.c_void_p(cuda_stream or None)))
 
     def build_cycle(self, ops, default_cycle=None, fused=True) -> int:
         enc = self.encode(lowering.fuse(ops) if fused else ops, default_cycle)

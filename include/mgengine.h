@@ -128,6 +128,11 @@ int mg_restore_initial_guess(mg_workspace* ws);
 /* ---- execution ------------------------------------------------------------------------- */
 /* run ops immediately on the workspace stream (no graph); used by the parity tests */
 int mg_exec_ops(mg_workspace* ws, const mg_op* ops, int n_ops);
+/* issue the ops on the workspace stream without waiting for them; mg_set_stream installs a stream
+ * of the caller (NULL: back to the workspace's own), so that the caller's NCCL halo exchanges and
+ * the engine's kernels are ordered by the stream, not by host synchronisation */
+int mg_enqueue_ops(mg_workspace* ws, const mg_op* ops, int n_ops);
+int mg_set_stream(mg_workspace* ws, void* cuda_stream);
 /* capture the op list (plus the fused residual-norm of the finest level) as a CUDA graph */
 int mg_build_cycle(mg_workspace* ws, const mg_op* ops, int n_ops, int* cycle);
 int mg_free_cycles(mg_workspace* ws);

@@ -144,7 +144,9 @@ def test_decomposed_solve_is_bitwise_the_single_domain_solve(world, lo, hi):
     ws.close()
 
     comm = domain.SlabComm(world, list(range(world)))
-    dd = domain.DomainDecomposedSolver(problem, lo, hi, comm)
+    import math
+    deepest = max(lo + 1, int(math.ceil(math.log2(world))) + 1)         # decompose as many levels as possible
+    dd = domain.DomainDecomposedSolver(problem, lo, hi, comm, dd_min_level=deepest)
     dd.set_fields(fs, us)
     hist, converged, ms = dd.solve(program.ops, 0.0, 3)
     got = dd.gather_solution()
