@@ -411,7 +411,7 @@ class B200ProgramGenerator:
                                 use_global_weights=False) -> str:
         from .exaslang import emit_cycle_function
         return emit_cycle_function(self._problem, expression, min_level, level, max_level, self._cycle_name,
-                                   self._parameters)
+                                   self._parameters, use_global_weights)
 
     def close(self):
         if self._workspace is not None:
