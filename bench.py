@@ -42,6 +42,9 @@ def parse_args():
     ap.add_argument("--engine-min-level", type=int, default=2)
     ap.add_argument("--cpu-sample-cycles", type=int, default=2)
     ap.add_argument("--generic-kernels", action="store_true", help="disable the specialised kernels")
+    ap.add_argument("--stages-only", action="store_true",
+                    help="time the finest-level stage kernels alone and print their rooflines (ncu target)")
+    ap.add_argument("--stage-reps", type=int, default=20)
     return ap.parse_args()
 
 
@@ -123,13 +126,23 @@ def synthetic_inputs(problem, level, pinned=True):
     return [u], [f]
 
 
+def captured_traffic(stage):
+    """DRAM bytes per launch of the stage kernel from the committed `ncu --set full` capture
+    (profiles/r1_traffic.json; read + write), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            return json.load(f)["stages"][stage]["traffic_bytes"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def algorithmic_bytes_per_dof(stage, dim=2):
     """SURVEY.md 8d table (fp64)."""
     return {"jacobi": 24.0, "rbgs": 24.0, "residual": 24.0, "residual_restrict": 16.0 + 8.0 / 2 ** dim,
             "prolong_add": 16.0 + 8.0 / 2 ** dim, "residual_norm": 16.0}[stage]
 
 
-def stage_rooflines(gen, problem, level, peak_gbs):
+def stage_rooflines(gen, problem, level, peak_gbs, reps=20, warm=3):
     """Time every finest-level stage kernel alone (CUDA events on the engine stream, arrays of
     134 MB each > the 126 MB L2, 20 back-to-back launches after 3 warm-up launches)."""
     from evostencils_b200 import ir, lowering
@@ -144,9 +157,8 @@ def stage_rooflines(gen, problem, level, peak_gbs):
         "prolong_add": [lowering.Op("prolong_add", level, omega=1.0, src="sol", dst="sol")],
     }
     out = {}
-    reps = 20
     for name, ops in stages.items():
-        ws.time_ops(ops, 3)
+        ws.time_ops(ops, warm)
         ws.flush_l2()
         ms = ws.time_ops(ops, reps) / reps
         bytes_per_launch = algorithmic_bytes_per_dof(name, problem.dimension) * dof
@@ -169,14 +181,40 @@ def make_generator(args, device, resident):
     return gen, problem, lo, hi
 
 
-def evaluate_shard(gen, grammar, shard, lo, hi):
+def finest_stage_counts(program, hi):
+    """Finest-level launches of one cycle of `program`, by stage kernel."""
+    from evostencils_b200 import lowering
+    counts = {}
+    for op in lowering.fuse(program.ops):
+        if isinstance(op, lowering.LocalSolve):
+            if op.level != hi:
+                continue
+            if any(p != 1 for p in op.period):
+                name = "block_jacobi"
+            else:
+                name = "rbgs" if op.colored else "jacobi"
+        elif op.kind in ("residual", "prolong_add") and op.level == hi:
+            name = op.kind
+        elif op.kind == "residual_restrict" and op.level == hi - 1:
+            name = op.kind
+        else:
+            continue
+        counts[name] = counts.get(name, 0) + 1
+    return counts
+
+
+def evaluate_shard(gen, grammar, shard, lo, hi, stage_counts=None):
     """One step: evaluate every individual of the shard.  -> (cycles executed, results)."""
     cycles = 0
     results = []
     for string in shard:
         expression, _ = grammar.compile(string)
         t, rho, n = gen.generate_and_evaluate(expression, None, lo, hi, "", evaluation_samples=1)
-        cycles += max(0, len(gen.last_residual_history) - 1)
+        c = max(0, len(gen.last_residual_history) - 1)
+        cycles += c
+        if stage_counts is not None and gen.last_program is not None:
+            for name, k in finest_stage_counts(gen.last_program, hi).items():
+                stage_counts[name] = stage_counts.get(name, 0) + k * c
         results.append((t, rho, n))
     return cycles, results
 
@@ -216,8 +254,9 @@ def run_b200(args):
         t0 = time.perf_counter()
         cycles = 0
         results = None
+        counts = {}
         for _ in range(args.steps):
-            c, results = evaluate_shard(gen, grammar, shard, lo, hi)
+            c, results = evaluate_shard(gen, grammar, shard, lo, hi, counts)
             cycles += c
         ws.mark(1)
         ws.synchronize()
@@ -237,13 +276,13 @@ def run_b200(args):
             h2d, d2h = sm[4].item(), sm[5].item()
         else:
             h2d, d2h = stats[4].item(), stats[5].item()
-        return gen, problem, lo, hi, dev_ms, wall_ms, cycles, launches, h2d, d2h, results
+        return gen, problem, lo, hi, dev_ms, wall_ms, cycles, launches, h2d, d2h, results, counts
 
     with ClockSampler(local) as clocks:
-        gen, problem, lo, hi, dev_ms, wall_ms, cycles, launches, _, _, results = timed_phase(resident=True)
+        gen, problem, lo, hi, dev_ms, wall_ms, cycles, launches, _, _, results, counts = timed_phase(resident=True)
         stages = stage_rooflines(gen, problem, hi, peak) if rank == 0 else None
         gen.close()
-        gen2, _, _, _, dev2, wall2, cycles2, launches2, h2d, d2h, _ = timed_phase(resident=False)
+        gen2, _, _, _, dev2, wall2, cycles2, launches2, h2d, d2h, _, _ = timed_phase(resident=False)
         gen2.close()
     dof = float((2 ** hi - 1) ** 2)
     value = dof * cycles / (dev_ms * 1e-3)
@@ -253,7 +292,12 @@ def run_b200(args):
             dist.destroy_process_group()
         return
     converged = sum(1 for r in results if r[2] < 1e99)
-    dominant = "rbgs"
+    # share of rank 0's timed region spent in each finest-level stage kernel: launches counted from
+    # the op lists x the stage's measured launch time; the largest is the dominant kernel
+    share = {name: {"launches": k, "est_ms": k * stages[name]["ms"] if name in stages else None,
+                    "share": k * stages[name]["ms"] / dev_ms if name in stages else None}
+             for name, k in sorted(counts.items())}
+    dominant = max((n for n in share if share[n]["share"] is not None), key=lambda n: share[n]["share"], default="rbgs")
     cpu = cpu_baseline(args, sample_only=True)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -273,16 +317,33 @@ def run_b200(args):
                 "d2h_bytes_per_step": d2h / args.steps, "ms_per_step": max(dev2, wall2) / args.steps},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": stages[dominant]["achieved_gbs"], "peak": peak,
-                     "unit": "GB/s", "frac": stages[dominant]["frac"], "traffic": None, "peak_source": peak_src,
+                     "unit": "GB/s", "frac": stages[dominant]["frac"], "traffic": captured_traffic(dominant), "peak_source": peak_src,
+                     "traffic_source": "profiles/r1_traffic.json (ncu --set full, same kernel and size)",
                      "algorithmic_bytes_per_launch": stages[dominant]["bytes"],
                      "ms_per_launch": stages[dominant]["ms"]},
-        "stages": stages,
+        "stages": stages, "finest_level_share_rank0": share,
         "cpu_baseline": cpu,
         "clocks": clocks.summary(),
     }
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_stages(args):
+    """`--stages-only`: the five finest-level stage kernels alone (used as the ncu target)."""
+    import torch
+    torch.cuda.set_device(0)
+    peak, peak_src = measured_peaks()
+    gen, problem, lo, hi = make_generator(args, 0, True)
+    ws = gen._ensure_workspace(lo, hi)
+    gen._configure(ws, {})
+    us, fs = synthetic_inputs(problem, hi, pinned=False)
+    ws.upload("sol", hi, 0, us[0])
+    ws.upload("rhs", hi, 0, fs[0])
+    stages = stage_rooflines(gen, problem, hi, peak, reps=args.stage_reps, warm=min(3, args.stage_reps))
+    gen.close()
+    print(json.dumps({"stages": stages, "peak": peak, "peak_source": peak_src, "level": hi, "reps": args.stage_reps}))
 
 
 def cpu_baseline(args, sample_only=False):
@@ -355,5 +416,7 @@ if __name__ == "__main__":
     a = parse_args()
     if a.impl == "reference":
         run_reference(a)
+    elif a.stages_only:
+        run_stages(a)
     else:
         run_b200(a)

@@ -161,6 +161,7 @@ class B200ProgramGenerator:
         self._front_end = None
         self.last_residual_history: List[float] = []
         self.last_launch_count = 0
+        self.last_program = None
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self._update_grids()
@@ -341,6 +342,7 @@ class B200ProgramGenerator:
         if ws.min_level < program.min_level:
             default_cycle = lambda level: lowering.default_cycle_ops(p, level, ws.min_level, params)
         cycle = ws.build_cycle(program.ops, default_cycle)
+        self.last_program = program
         tol = p.solver.target_reduction
         max_its = p.solver.max_iterations if max_iterations is None else max_iterations
         total_time = total_rho = total_n = 0.0

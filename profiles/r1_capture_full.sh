@@ -1,11 +1,14 @@
 #!/bin/bash
-# Round 1, call B: one `--set full` capture of the dominant kernel (fused two-colour RB-GS at
-# 4096^2) and of the Jacobi/residual tile kernel, two launches each, inside the bench program.
+# Round 1, call B: `--set full` captures of the finest-level (4096^2) stage kernels, launched by
+# `bench.py --stages-only` (the same stage_rooflines() the bench line's roofline comes from;
+# 1 warm-up + 1 timed launch per stage under ncu, so 10 captured launches).
 set -u
 mkdir -p gpurun_out
-python bench.py --steps 1 --warmup 1 --individuals-per-gpu 1 > /dev/null 2>&1 || exit 1
-ncu --set full --clock-control none --import-source on -k regex:'k_rbgs2d|k_star2d' \
-    --launch-skip 40 -c 6 -o gpurun_out/r1_full_top -f \
-    python bench.py --steps 1 --warmup 1 --individuals-per-gpu 1 > gpurun_out/r1_full_top.log 2>&1
+python bench.py --stages-only --stage-reps 1 > gpurun_out/r1_stages_plain1.json 2>&1 || { cat gpurun_out/r1_stages_plain1.json; exit 1; }
+python bench.py --stages-only > gpurun_out/r1_stages_plain20.json 2>&1 || exit 1
+ncu --set full --clock-control none --import-source on \
+    -k regex:'k_rbgs2d|k_star2d|k_resrestrict2d|k_prolong2d' -c 12 -o gpurun_out/r1_full_stages -f \
+    python bench.py --stages-only --stage-reps 1 > gpurun_out/r1_full_stages.log 2>&1
 echo "ncu rc=$?"
+cat gpurun_out/r1_stages_plain20.json
 ls -la gpurun_out
