@@ -45,6 +45,13 @@ __device__ __forceinline__ double2 ldf2(const double* p) { return ld2(p); }
 __device__ __forceinline__ double ldf1(const double* p) { return *p; }
 #endif
 
+// L2 prefetch of one contiguous row segment (bytes % 16 == 0, 16-byte aligned): issued by the CTA
+// that runs `pf` bands ahead of the one that will load the segment, so that band finds its rows in
+// L2 instead of paying the DRAM latency (each line is still fetched from DRAM once).
+__device__ __forceinline__ void l2_prefetch_rows(const double* p, unsigned bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 // (A u) at one node, canonical order S, W, C, E, N
 __device__ __forceinline__ double star_at(const Star2D& s, double S, double W, double Cc, double E, double N) {
     double a = s.cs * S;
@@ -171,15 +178,24 @@ __device__ __forceinline__ double red_value(const Star2D& s, double w, double S,
     return Cc + w * (fv - star_at(s, S, W, Cc, E, N));
 }
 
+#ifndef MG_RBGS_MIN_CTAS
+#define MG_RBGS_MIN_CTAS 1
+#endif
 template <int NT, int R>
-__global__ void __launch_bounds__(NT) k_rbgs2d(Geom g, Star2D s, const double* __restrict__ u,
-                                                const double* __restrict__ f, double* __restrict__ out, double w) {
+__global__ void __launch_bounds__(NT, R <= 4 ? MG_RBGS_MIN_CTAS : 1) k_rbgs2d(Geom g, Star2D s, const double* __restrict__ u,
+                                                const double* __restrict__ f, double* __restrict__ out, double w,
+                                                int pf) {
     pdl_sync();
     const int lane = threadIdx.x & 31;
     const int x0 = (blockIdx.x * NT + threadIdx.x) * 2;       // even column; x0+1 odd
     const int n = g.n;
     const long long pitch = g.pitch;
     const int y0 = 1 + blockIdx.y * R;
+    if (pf > 0 && threadIdx.x < 2 * R) {                       // own rows of the band `pf` bands ahead
+        const int row = y0 + pf * R + (threadIdx.x % R);
+        if (row <= n - 1)
+            l2_prefetch_rows((threadIdx.x < R ? u : f) + (long long)row * pitch + blockIdx.x * NT * 2, NT * 16);
+    }
     const bool in0 = x0 >= 1;
     const bool last = x0 == n - 3;
     const bool edge = (lane == 0 && x0 > 0) || lane == 31;
@@ -505,6 +521,127 @@ __global__ void __launch_bounds__(NT) k_prolong2d(Geom gf, Geom gc, const double
         a0 = b0; a1 = b1; a2 = b2;
     }
     (void)nf;
+}
+
+// ---- tile versions of the two inter-grid stages (all loads of a band issued up front) ----------------
+//
+// Fused residual + full weighting.  A thread owns the fine columns x0 = 2X, x0+1 of coarse column X
+// and a band of RC coarse rows: it forms the fine residuals at (x0, x0+1) of the 2RC+1 fine rows
+// the band needs and takes the residual at x0-1 from the lane to its left.  Warps overlap by one
+// lane (lane 0 of every warp only donates, a warp stores 31 coarse columns), so that no lane has
+// to recompute a neighbour's residual from extra halo loads; the overlap costs 1/32 more L2 reads.
+// Accumulation order per coarse node: fine rows 2Y-1, 2Y, 2Y+1, columns -1, 0, +1 (memory order),
+// term = (w_x * w_y) * r -- identical to the generic kernel.
+template <int NT, int RC>
+__global__ void __launch_bounds__(NT) k_resrestrict2d_t(Geom gc, Geom gf, Star2D s, const double* __restrict__ u,
+                                                         const double* __restrict__ f, double* __restrict__ coarse,
+                                                         int ahead) {
+    pdl_sync();
+    constexpr int NR = 2 * RC + 1, NU = NR + 2;
+    if (ahead > 0 && threadIdx.x < 4 * RC) {                   // the 2RC fine rows 2Y, 2Y+1 of the band `ahead` bands on
+        const int row = 2 * (1 + (blockIdx.y + ahead) * RC) + (threadIdx.x % (2 * RC));
+        const long long col = (long long)blockIdx.x * (NT / 32) * 62;      // first fine column of the CTA (16-byte aligned)
+        if (row <= gf.n - 1 && col + NT * 2 <= gf.pitch)
+            l2_prefetch_rows((threadIdx.x < 2 * RC ? u : f) + (long long)row * gf.pitch + col, NT * 16);
+    }
+    const int lane = threadIdx.x & 31;
+    const int nc = gc.n, nf = gf.n;
+    const long long pf = gf.pitch, pc = gc.pitch;
+    const int X = (blockIdx.x * (NT / 32) + (threadIdx.x >> 5)) * 31 + lane;    // coarse column
+    const int x0 = 2 * imin(X, nc - 1);                                          // <= nf-1 (x0+1 < pitch)
+    const bool store = lane >= 1 && X <= nc - 2;
+    const int Y0 = 1 + blockIdx.y * RC;                                          // coarse rows Y0 .. Y0+RC-1
+    const int yr0 = 2 * Y0 - 1;                                                  // first fine residual row
+    double2 uu[NU], ff[NR];
+    double er[NR];
+#pragma unroll
+    for (int i = 0; i < NU; ++i) uu[i] = ldf2(u + (long long)imin(yr0 - 1 + i, nf) * pf + x0);    // row nf: guard
+#pragma unroll
+    for (int j = 0; j < NR; ++j) ff[j] = ldf2(f + (long long)imin(yr0 + j, nf) * pf + x0);
+#pragma unroll
+    for (int j = 0; j < NR; ++j) {
+        er[j] = 0.0;
+        if (lane == 31) er[j] = ldf1(u + (long long)imin(yr0 + j, nf) * pf + x0 + 2);
+    }
+    __syncthreads();      // scheduling fence (see k_star2d)
+    double rl[NR], r0[NR], r1[NR];
+#pragma unroll
+    for (int j = 0; j < NR; ++j) {
+        const double2 um = uu[j], uc = uu[j + 1], un = uu[j + 2];
+        const double left = __shfl_up_sync(0xffffffffu, uc.y, 1);
+        double right = __shfl_down_sync(0xffffffffu, uc.x, 1);
+        if (lane == 31) right = er[j];
+        r0[j] = ff[j].x - star_at(s, um.x, left, uc.x, uc.y, un.x);
+        r1[j] = ff[j].y - star_at(s, um.y, uc.x, uc.y, right, un.y);
+        rl[j] = __shfl_up_sync(0xffffffffu, r1[j], 1);
+    }
+#pragma unroll
+    for (int i = 0; i < RC; ++i) {
+        const int Y = Y0 + i;
+        if (store && Y <= nc - 2) {
+            const int m = 2 * i, c = 2 * i + 1, n_ = 2 * i + 2;
+            double a = 0.0625 * rl[m];
+            a = a + 0.125 * r0[m];
+            a = a + 0.0625 * r1[m];
+            a = a + 0.125 * rl[c];
+            a = a + 0.25 * r0[c];
+            a = a + 0.125 * r1[c];
+            a = a + 0.0625 * rl[n_];
+            a = a + 0.125 * r0[n_];
+            a = a + 0.0625 * r1[n_];
+            coarse[(long long)Y * pc + X] = a;
+        }
+    }
+}
+
+// Fused prolongation + correction, u += omega * (P e), in place.  A thread owns the fine columns
+// x0 = 2X, x0+1 and the fine rows 2Y, 2Y+1 of RC coarse rows Y; e(., X+1) comes from the lane to
+// the right (lane 31 loads it).
+template <int NT, int RC>
+__global__ void __launch_bounds__(NT) k_prolong2d_t(Geom gf, Geom gc, const double* __restrict__ e,
+                                                     double* __restrict__ u, double omega) {
+    pdl_sync();
+    const int lane = threadIdx.x & 31;
+    const int x0 = (blockIdx.x * NT + threadIdx.x) * 2;        // <= nf-3
+    const int X = x0 >> 1;
+    const int nf = gf.n, nc = gc.n;
+    const long long pf = gf.pitch, pc = gc.pitch;
+    const int Y0 = blockIdx.y * RC;                             // coarse rows Y0 .. Y0+RC-1 (<= nc-2)
+    double c0[RC + 1], c1[RC + 1];
+    double2 uu[2 * RC];
+#pragma unroll
+    for (int i = 0; i <= RC; ++i) c0[i] = ldf1(e + (long long)imin(Y0 + i, nc - 1) * pc + X);
+#pragma unroll
+    for (int i = 0; i <= RC; ++i) {
+        c1[i] = 0.0;
+        if (lane == 31) c1[i] = ldf1(e + (long long)imin(Y0 + i, nc - 1) * pc + X + 1);
+    }
+#pragma unroll
+    for (int k = 0; k < 2 * RC; ++k) uu[k] = ldf2(u + (long long)imin(2 * Y0 + k, nf) * pf + x0);
+    __syncthreads();      // scheduling fence
+#pragma unroll
+    for (int i = 0; i <= RC; ++i) {
+        const double r = __shfl_down_sync(0xffffffffu, c0[i], 1);
+        if (lane != 31) c1[i] = r;
+    }
+    const bool in0 = x0 >= 1;                                   // column 0 is Dirichlet
+#pragma unroll
+    for (int i = 0; i < RC; ++i) {
+        const int Y = Y0 + i;
+        if (Y <= nc - 2) {
+            const double a0 = c0[i], a1 = c1[i], b0 = c0[i + 1], b1 = c1[i + 1];
+            if (Y >= 1) {                                       // even fine row 2Y (row 0 is Dirichlet)
+                double2 v = uu[2 * i];
+                if (in0) v.x = v.x + omega * a0;
+                v.y = v.y + omega * (0.5 * (a0 + a1));
+                st2(u + (long long)(2 * Y) * pf + x0, v);
+            }
+            double2 v = uu[2 * i + 1];                          // odd fine row 2Y+1 <= nf-2
+            if (in0) v.x = v.x + omega * (0.5 * (a0 + b0));
+            v.y = v.y + omega * (0.25 * (((a0 + a1) + b0) + b1));
+            st2(u + (long long)(2 * Y + 1) * pf + x0, v);
+        }
+    }
 }
 
 }  // namespace mg

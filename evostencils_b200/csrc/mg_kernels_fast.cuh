@@ -156,9 +156,11 @@ inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm, int c_begin, 
         if (sm.colored) {
             const int r = valid_rows(rows_rb, pick_rows(lv, 2));
             dim3 grid = strip_grid(lv, 2, r, lv.g.n - 2);
-            if (r == 8) launch_k(ws, k_rbgs2d<FAST_NT, 8>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00);
-            else if (r == 4) launch_k(ws, k_rbgs2d<FAST_NT, 4>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00);
-            else launch_k(ws, k_rbgs2d<FAST_NT, 2>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00);
+            static const int pf_env = tunable("MG_RBGS_PF", 20);
+            const int pf = lv.g.n > 2049 ? pf_env : 0;            // smaller levels are L2 resident anyway
+            if (r == 8) launch_k(ws, k_rbgs2d<FAST_NT, 8>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00, pf);
+            else if (r == 4) launch_k(ws, k_rbgs2d<FAST_NT, 4>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00, pf);
+            else launch_k(ws, k_rbgs2d<FAST_NT, 2>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00, pf);
         } else {
             launch_star2d<STAR_JACOBI>(ws, lv, valid_rows(rows_j, pick_rows(lv, 2)), src, rhs, dst, sm.w00, nullptr);
         }
@@ -222,6 +224,26 @@ template <typename T, int D, int F>
 inline bool fast_residual_restrict(mg_workspace* ws, Level& lf, Level& lc) {
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         if (!star_level_ok<D>(ws, lf, 4) || (lc.g.n - 1) % (2 * FAST_NT) != 0) return false;
+        static const int tile_rc = tunable("MG_RESTRICT_RC", 3);     // 0: marching kernel
+        if (tile_rc > 0) {
+            const double* u = static_cast<const double*>(lf.sol[lf.cur[0]][0]);
+            const double* f = static_cast<const double*>(lf.rhs[0]);
+            double* out = static_cast<double*>(lc.rhs[0]);
+            const int warps = (lc.g.n - 2 + 30) / 31, nrows = lc.g.n - 2;
+            const int gx = (warps + FAST_NT / 32 - 1) / (FAST_NT / 32);
+            static const int pf_env = tunable("MG_RESTRICT_PF", 20);
+            const int pf = lf.g.n > 2049 ? pf_env : 0;            // smaller levels are L2 resident anyway
+            if (tile_rc == 1)
+                launch_k(ws, k_resrestrict2d_t<FAST_NT, 1>, dim3(gx, nrows, 1), FAST_NT, 0, lc.g, lf.g, star2d(lf), u, f, out, pf);
+            else if (tile_rc == 2)
+                launch_k(ws, k_resrestrict2d_t<FAST_NT, 2>, dim3(gx, (nrows + 1) / 2, 1), FAST_NT, 0, lc.g, lf.g, star2d(lf), u, f, out, pf);
+            else if (tile_rc == 3)
+                launch_k(ws, k_resrestrict2d_t<FAST_NT, 3>, dim3(gx, (nrows + 2) / 3, 1), FAST_NT, 0, lc.g, lf.g, star2d(lf), u, f, out, pf);
+            else
+                launch_k(ws, k_resrestrict2d_t<FAST_NT, 4>, dim3(gx, (nrows + 3) / 4, 1), FAST_NT, 0, lc.g, lf.g, star2d(lf), u, f, out, pf);
+            fast_count(ws);
+            return true;
+        }
         static const int rows_env = tunable("MG_RESTRICT_ROWS", 0);
         const int rows = rows_env > 0 ? rows_env : march_rows(lc.g.n - 2, (lc.g.n - 1) / (2 * FAST_NT));
         launch_k(ws, k_resrestrict2d<FAST_NT>, strip_grid(lc, 2, rows, lc.g.n - 2), FAST_NT, 0, 
@@ -250,6 +272,20 @@ inline bool fast_prolong_add(mg_workspace* ws, Level& lf, Level& lc, const Field
     }
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         if (ws->dtype != MG_F64 || (lf.g.n - 1) % (4 * FAST_NT) != 0) return false;
+        static const int tile_rc = tunable("MG_PROLONG_RC", 4);      // 0: marching kernel
+        if (tile_rc > 0) {
+            const double* e = reinterpret_cast<const double*>(src.p[0]);
+            double* u = static_cast<double*>(lf.sol[lf.cur[0]][0]);
+            const int gx = (lf.g.n - 1) / (2 * FAST_NT), nrows = lc.g.n - 1;
+            if (tile_rc == 1)
+                launch_k(ws, k_prolong2d_t<FAST_NT, 1>, dim3(gx, nrows, 1), FAST_NT, 0, lf.g, lc.g, e, u, omega);
+            else if (tile_rc == 2)
+                launch_k(ws, k_prolong2d_t<FAST_NT, 2>, dim3(gx, (nrows + 1) / 2, 1), FAST_NT, 0, lf.g, lc.g, e, u, omega);
+            else
+                launch_k(ws, k_prolong2d_t<FAST_NT, 4>, dim3(gx, (nrows + 3) / 4, 1), FAST_NT, 0, lf.g, lc.g, e, u, omega);
+            fast_count(ws);
+            return true;
+        }
         static const int rows_env = tunable("MG_PROLONG_ROWS", 0);
         const int rows = rows_env > 0 ? rows_env : march_rows(lc.g.n - 1, (lf.g.n - 1) / (4 * FAST_NT));
         launch_k(ws, k_prolong2d<FAST_NT>, strip_grid(lf, 4, rows, lc.g.n - 1), FAST_NT, 0, 

@@ -26,7 +26,7 @@ def main():
         ws.upload("rhs", level, 0, f)
         ws.upload("sol", level, 0, np.zeros((n, n)))
     out = {}
-    for top in range(3, a.top + 1):
+    for top in range(2, a.top + 1):
         ops = [lowering.Op("zero", top, dst="sol")] + lowering.fuse(lowering.default_cycle_ops(problem, top, lo))
         row = {}
         for name, tail in (("tail", True), ("launches", False)):
