@@ -71,6 +71,7 @@ static int create_impl(mg_workspace** out, int dimension, int min_level, int max
     ws->tail_max_level = dimension == 3 ? 4 : 6;        // <= ~5000 nodes per level: 65^2 or 17^3
     if (const char* v = std::getenv("MG_TAIL_LEVEL")) ws->tail_max_level = std::atoi(v);
     if (const char* v = std::getenv("MG_PDL")) ws->use_pdl = std::atoi(v) != 0;
+    if (const char* v = std::getenv("MG_LAZY_ZERO")) ws->lazy_zero = std::atoi(v) != 0;
     MG_CUDA(cudaStreamCreateWithFlags(&ws->stream, cudaStreamNonBlocking));
     MG_CUDA(cudaEventCreate(&ws->ev0));
     MG_CUDA(cudaEventCreate(&ws->ev1));

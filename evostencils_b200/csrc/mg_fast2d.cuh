@@ -96,12 +96,16 @@ __global__ void __launch_bounds__(NT) k_star2d(Geom g, Star2D s, const double* _
     const int y0 = 1 + blockIdx.y * R;                         // rows y0 .. y0+R-1 (those <= n-2)
     const bool in0 = x0 >= 1;                                  // column x0+1 is always interior
     const bool last = x0 == n - 3;                             // also owns the Dirichlet column n-1
-    const bool edge = (lane == 0 && x0 > 0) || lane == 31;
+    const bool zin = u == nullptr;                             // u == 0 everywhere (pending zero fill): no loads of u
+    const bool edge = ((lane == 0 && x0 > 0) || lane == 31) && !zin;
     const int xe = lane == 0 ? x0 - 1 : x0 + 2;
     double2 uu[R + 2], ff[R];
     double ue[R];
 #pragma unroll
-    for (int i = 0; i < R + 2; ++i) uu[i] = ldf2(u + (long long)imin(y0 - 1 + i, n) * pitch + x0);   // row n: guard
+    for (int i = 0; i < R + 2; ++i) {
+        uu[i] = make_double2(0.0, 0.0);
+        if (!zin) uu[i] = ldf2(u + (long long)imin(y0 - 1 + i, n) * pitch + x0);   // row n: guard
+    }
 #pragma unroll
     for (int i = 0; i < R; ++i) ff[i] = ldf2(f + (long long)imin(y0 + i, n) * pitch + x0);
 #pragma unroll
@@ -112,7 +116,7 @@ __global__ void __launch_bounds__(NT) k_star2d(Geom g, Star2D s, const double* _
     __syncthreads();      // scheduling fence: keeps every load above ahead of the first use / store
     if (MODE == STAR_JACOBI && blockIdx.y == 0) {              // Dirichlet row 0
         st2(out + x0, uu[0]);
-        if (last) out[n - 1] = u[n - 1];
+        if (last) out[n - 1] = zin ? 0.0 : u[n - 1];
     }
     double acc = 0.0;
 #pragma unroll
@@ -151,7 +155,7 @@ __global__ void __launch_bounds__(NT) k_star2d(Geom g, Star2D s, const double* _
 #pragma unroll
         for (int i = 1; i < R + 2; ++i)
             if (y0 - 1 + i == n - 1) st2(out + (long long)(n - 1) * pitch + x0, uu[i]);
-        if (last) out[(long long)(n - 1) * pitch + n - 1] = u[(long long)(n - 1) * pitch + n - 1];
+        if (last) out[(long long)(n - 1) * pitch + n - 1] = zin ? 0.0 : u[(long long)(n - 1) * pitch + n - 1];
     }
     if (MODE == STAR_NORM) {
         __shared__ double s32[32];
@@ -191,7 +195,8 @@ __global__ void __launch_bounds__(NT, R <= 4 ? MG_RBGS_MIN_CTAS : 1) k_rbgs2d(Ge
     const int n = g.n;
     const long long pitch = g.pitch;
     const int y0 = 1 + blockIdx.y * R;
-    if (pf > 0 && threadIdx.x < 2 * R) {                       // own rows of the band `pf` bands ahead
+    const bool zin = u == nullptr;                             // u == 0 everywhere (pending zero fill): no loads of u
+    if (pf > 0 && threadIdx.x < 2 * R && !(zin && threadIdx.x < R)) {      // own rows of the band `pf` bands ahead
         const int row = y0 + pf * R + (threadIdx.x % R);
         if (row <= n - 1)
             l2_prefetch_rows((threadIdx.x < R ? u : f) + (long long)row * pitch + blockIdx.x * NT * 2, NT * 16);
@@ -199,19 +204,23 @@ __global__ void __launch_bounds__(NT, R <= 4 ? MG_RBGS_MIN_CTAS : 1) k_rbgs2d(Ge
     const bool in0 = x0 >= 1;
     const bool last = x0 == n - 3;
     const bool edge = (lane == 0 && x0 > 0) || lane == 31;
+    const bool edge_u = edge && !zin;
     const int xe = lane == 0 ? x0 - 2 : x0 + 2;                // halo column pair (xe, xe+1)
     double2 o[R + 4];          // row y0-2+k
     double2 fr[R + 2];         // row y0-1+k
     double2 eh[R + 2];         // halo pair of row y0-1+k (edge lanes)
     double ef[R];              // f at the halo red node of black row y0+k
 #pragma unroll
-    for (int k = 0; k < R + 4; ++k) o[k] = ldf2(u + (long long)imin(y0 - 2 + k, n) * pitch + x0);      // row -1 / n: guard rows
+    for (int k = 0; k < R + 4; ++k) {
+        o[k] = make_double2(0.0, 0.0);
+        if (!zin) o[k] = ldf2(u + (long long)imin(y0 - 2 + k, n) * pitch + x0);      // row -1 / n: guard rows
+    }
 #pragma unroll
     for (int k = 0; k < R + 2; ++k) fr[k] = ldf2(f + (long long)imin(y0 - 1 + k, n) * pitch + x0);
 #pragma unroll
     for (int k = 0; k < R + 2; ++k) {
         eh[k] = make_double2(0.0, 0.0);
-        if (edge) eh[k] = ldf2(u + (long long)imin(y0 - 1 + k, n) * pitch + xe);
+        if (edge_u) eh[k] = ldf2(u + (long long)imin(y0 - 1 + k, n) * pitch + xe);
     }
 #pragma unroll
     for (int k = 0; k < R; ++k) {
@@ -237,7 +246,7 @@ __global__ void __launch_bounds__(NT, R <= 4 ? MG_RBGS_MIN_CTAS : 1) k_rbgs2d(Ge
     }
     if (blockIdx.y == 0) {                                      // Dirichlet row 0 (k = 1)
         st2(out + x0, o[1]);
-        if (last) out[n - 1] = u[n - 1];
+        if (last) out[n - 1] = zin ? 0.0 : u[n - 1];
     }
     // black half-sweep of rows y0 .. y0+R-1 (k = 2 .. R+1)
 #pragma unroll
@@ -270,7 +279,7 @@ __global__ void __launch_bounds__(NT, R <= 4 ? MG_RBGS_MIN_CTAS : 1) k_rbgs2d(Ge
 #pragma unroll
         for (int k = 2; k < R + 3; ++k)
             if (y0 - 2 + k == n - 1) st2(out + (long long)(n - 1) * pitch + x0, o[k]);
-        if (last) out[(long long)(n - 1) * pitch + n - 1] = u[(long long)(n - 1) * pitch + n - 1];
+        if (last) out[(long long)(n - 1) * pitch + n - 1] = zin ? 0.0 : u[(long long)(n - 1) * pitch + n - 1];
     }
 }
 

@@ -132,10 +132,12 @@ inline dim3 launch_star3d(mg_workspace* ws, Level& lv, int nt, const double* u, 
 }
 
 template <typename T, int D, int F>
-inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm, int c_begin, int c_end) {
+inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm, int c_begin, int c_end, bool zero_in) {
+    // zero_in: the current solution is a pending zero fill (Level::zero_pending); true is returned only
+    // when the kernel ran without reading it
     if constexpr (D == 3 && F == 1 && sizeof(T) == sizeof(double)) {
         const int nt = star3d_nt(ws, lv);
-        if (!nt || !sm.point || sm.m != 1 || lv.g.nz < 3) return false;
+        if (zero_in || !nt || !sm.point || sm.m != 1 || lv.g.nz < 3) return false;
         const double* rhs = static_cast<const double*>(lv.rhs[0]);
         for (int c = c_begin; c < c_end; ++c) {
             const double* src = static_cast<const double*>(lv.sol[lv.cur[0]][0]);
@@ -150,7 +152,7 @@ inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm, int c_begin, 
         if (sm.colored && !(c_begin == 0 && c_end == 2)) return false;        // single colour passes: generic kernel
         if (!star_level_ok<D>(ws, lv, 2) || !sm.point || sm.m != 1) return false;
         static const int rows_j = tunable("MG_JACOBI_ROWS", 0), rows_rb = tunable("MG_RBGS_ROWS", 0);
-        const double* src = static_cast<const double*>(lv.sol[lv.cur[0]][0]);
+        const double* src = zero_in ? nullptr : static_cast<const double*>(lv.sol[lv.cur[0]][0]);
         double* dst = static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]);
         const double* rhs = static_cast<const double*>(lv.rhs[0]);
         if (sm.colored) {

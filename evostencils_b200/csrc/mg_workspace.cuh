@@ -46,6 +46,7 @@ struct Level {
     void* cor[MG_MAX_FIELDS] = {};      // finest only
     void* init[MG_MAX_FIELDS] = {};     // finest only: saved initial guess
     int cur[MG_MAX_FIELDS] = {};        // which sol buffer is current
+    bool zero_pending = false;          // sol[0] is logically zero; the fill has not been issued (mg_exec.cuh)
     HostOperator hop;
     void* d_op = nullptr;               // OperatorTable<T>
     bool op_dirty = true;
@@ -109,6 +110,7 @@ struct mg_workspace {
     long long launches = 0;                     // kernels launched (incl. graph replays)
     long long pending_count = 0;                // kernels issued since the counter was last sampled
     bool use_fast = true;                       // specialised kernels where applicable
+    bool lazy_zero = true;              // defer zero fills so that the next smoother can skip reading u
     bool use_pdl = false;                       // programmatic dependent launch between consecutive kernels (MG_PDL=1):
                                                 // measured neutral inside captured graphs, so off by default
     bool use_tail = true;                       // small levels run inside the single-CTA tail kernel

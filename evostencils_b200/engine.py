@@ -255,10 +255,18 @@ class Workspace:
         self._smoother_cache[key] = handle.value
         return handle.value
 
-    def clear_programs(self):
-        """Drop captured cycles and smoother tables (between individuals)."""
-        self._check(self.lib.mg_clear_smoothers(self._h))
-        self._smoother_cache.clear()
+    MAX_CACHED_SMOOTHERS = 2048
+
+    def clear_programs(self, smoothers=False):
+        """Drop the captured cycles (between individuals).  Smoother tables are keyed by their
+        content (level, weight, partitioning, tile shape, local matrix), so they stay valid for the
+        next individual and are kept unless `smoothers` is set, the operators changed
+        (set_operator) or the cache has grown beyond MAX_CACHED_SMOOTHERS tables."""
+        if smoothers or len(self._smoother_cache) > self.MAX_CACHED_SMOOTHERS:
+            self._check(self.lib.mg_clear_smoothers(self._h))
+            self._smoother_cache.clear()
+        else:
+            self._check(self.lib.mg_free_cycles(self._h))
 
     # -- op encoding -------------------------------------------------------------------------
     def encode(self, ops: Sequence[object], default_cycle=None) -> "C.Array":

@@ -162,6 +162,7 @@ class B200ProgramGenerator:
         self.last_residual_history: List[float] = []
         self.last_launch_count = 0
         self.last_program = None
+        self._default_cycle_cache = {}
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self._update_grids()
@@ -340,7 +341,12 @@ class B200ProgramGenerator:
         ws.clear_programs()
         default_cycle = None
         if ws.min_level < program.min_level:
-            default_cycle = lambda level: lowering.default_cycle_ops(p, level, ws.min_level, params)
+            def default_cycle(level, _cache=self._default_cycle_cache):
+                # the `.exa3` solver block below the grammar's coarsest level: same for every individual
+                key = (p.name, level, ws.min_level, tuple(sorted(params.items())))
+                if key not in _cache:
+                    _cache[key] = lowering.fuse(lowering.default_cycle_ops(p, level, ws.min_level, params))
+                return _cache[key]
         cycle = ws.build_cycle(program.ops, default_cycle)
         self.last_program = program
         tol = p.solver.target_reduction
