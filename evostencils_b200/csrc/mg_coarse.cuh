@@ -44,6 +44,28 @@ __device__ __forceinline__ FieldSet<T> as_fields(T* base, const Geom& g) {
     return fs;
 }
 
+// Element loop of the Krylov team with the first element of every thread decoded once (on the
+// coarsest levels a thread owns at most one unknown, so no iteration pays the index arithmetic).
+template <int D>
+struct ElemCache {
+    int f0;
+    long long idx0;
+    bool has0;
+    __device__ ElemCache(const Geom& g, const InteriorIter<D>& it) : f0(0), idx0(0), has0(krylov_tid() < it.total) {
+        if (has0) it.decode(krylov_tid(), g, f0, idx0);
+    }
+    template <class Fn>
+    __device__ __forceinline__ void each(const Geom& g, const InteriorIter<D>& it, Fn fn) const {
+        if (!has0) return;
+        fn(f0, idx0);
+        for (int e = krylov_tid() + 256; e < it.total; e += 256) {
+            int f; long long idx;
+            it.decode(e, g, f, idx);
+            fn(f, idx);
+        }
+    }
+};
+
 template <typename T, int D>
 __device__ T coarse_dot(const T* a, const T* b, const Geom& g, const InteriorIter<D>& it, T* s8) {
     T acc = t_zero(T());
@@ -52,6 +74,13 @@ __device__ T coarse_dot(const T* a, const T* b, const Geom& g, const InteriorIte
         it.decode(e, g, f, idx);
         acc = t_add(acc, t_mul(a[idx], b[idx]));
     }
+    return block_sum_256<T>(acc, s8);
+}
+
+template <typename T, int D>
+__device__ T coarse_dot(const T* a, const T* b, const Geom& g, const InteriorIter<D>& it, const ElemCache<D>& ec, T* s8) {
+    T acc = t_zero(T());
+    ec.each(g, it, [&](int, long long idx) { acc = t_add(acc, t_mul(a[idx], b[idx])); });
     return block_sum_256<T>(acc, s8);
 }
 
@@ -95,44 +124,33 @@ __device__ void coarse_cg_body(const Geom& g, const OperatorTable<T>* __restrict
     T* p = work + 2 * vec;
     T* ap = work + 3 * vec;
     InteriorIter<D> it(g, F);
+    const ElemCache<D> ec(g, it);
     for (long long i = krylov_tid(); i < 4 * vec; i += 256) work[i] = t_zero(T());
     __syncthreads();
-    for (int e = krylov_tid(); e < it.total; e += 256) {
-        int f; long long idx;
-        it.decode(e, g, f, idx);
+    ec.each(g, it, [&](int f, long long idx) {
         T v = rhs.p[f][idx - (long long)f * g.total];
         r[idx] = v;
         p[idx] = v;
-    }
+    });
     __syncthreads();
-    T rs = coarse_dot<T, D>(r, r, g, it, s8);
+    T rs = coarse_dot<T, D>(r, r, g, it, ec, s8);
     const double r0 = t_abs(t_sqrt(rs));
     if (r0 != 0.0) {
         FieldSet<T> pf = as_fields<T, F>(p, g);
         for (int iter = 1; iter <= max_its; ++iter) {
-            for (int e = krylov_tid(); e < it.total; e += 256) {
-                int f; long long idx;
-                it.decode(e, g, f, idx);
-                ap[idx] = apply_row<T, F>(op, pf, f, idx - (long long)f * g.total);
-            }
+            ec.each(g, it, [&](int f, long long idx) { ap[idx] = apply_row<T, F>(op, pf, f, idx - (long long)f * g.total); });
             __syncthreads();
-            T pap = coarse_dot<T, D>(p, ap, g, it, s8);
+            T pap = coarse_dot<T, D>(p, ap, g, it, ec, s8);
             T alpha = t_div(rs, pap);
-            for (int e = krylov_tid(); e < it.total; e += 256) {
-                int f; long long idx;
-                it.decode(e, g, f, idx);
+            ec.each(g, it, [&](int, long long idx) {
                 x[idx] = t_add(x[idx], t_mul(alpha, p[idx]));
                 r[idx] = t_sub(r[idx], t_mul(alpha, ap[idx]));
-            }
+            });
             __syncthreads();
-            T rs_new = coarse_dot<T, D>(r, r, g, it, s8);
+            T rs_new = coarse_dot<T, D>(r, r, g, it, ec, s8);
             if (t_abs(t_sqrt(rs_new)) <= reduction * r0) break;
             T beta = t_div(rs_new, rs);
-            for (int e = krylov_tid(); e < it.total; e += 256) {
-                int f; long long idx;
-                it.decode(e, g, f, idx);
-                p[idx] = t_add(r[idx], t_mul(beta, p[idx]));
-            }
+            ec.each(g, it, [&](int, long long idx) { p[idx] = t_add(r[idx], t_mul(beta, p[idx])); });
             rs = rs_new;
             __syncthreads();
         }

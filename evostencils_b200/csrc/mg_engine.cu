@@ -70,6 +70,7 @@ static int create_impl(mg_workspace** out, int dimension, int min_level, int max
     ws->elem = dtype == MG_F64 ? 8 : 16;
     ws->tail_max_level = dimension == 3 ? 4 : 6;        // <= ~5000 nodes per level: 65^2 or 17^3
     if (const char* v = std::getenv("MG_TAIL_LEVEL")) ws->tail_max_level = std::atoi(v);
+    if (const char* v = std::getenv("MG_TAIL_LEAN")) ws->tail_lean = std::atoi(v) != 0;
     if (const char* v = std::getenv("MG_PDL")) ws->use_pdl = std::atoi(v) != 0;
     if (const char* v = std::getenv("MG_LAZY_ZERO")) ws->lazy_zero = std::atoi(v) != 0;
     MG_CUDA(cudaStreamCreateWithFlags(&ws->stream, cudaStreamNonBlocking));
@@ -157,6 +158,7 @@ static void free_cycles_graphs(mg_workspace* ws) {
         ws->outer_graph = nullptr;
         ws->outer_graph_cycle = -1;
     }
+    ws->tail_pool_used = 0;       // the tail programs of the destroyed graphs
 }
 
 extern "C" int mg_destroy(mg_workspace* ws) {
@@ -172,6 +174,9 @@ extern "C" int mg_destroy(mg_workspace* ws) {
     }
     if (ws->cgs_work) cudaFree(ws->cgs_work);
     delete ws->tail;
+    if (ws->tail_pool) cudaFree(ws->tail_pool);
+    if (ws->tail_stage) cudaFreeHost(ws->tail_stage);
+    if (ws->aux_stream) cudaStreamDestroy(ws->aux_stream);
     if (ws->outer_graph) cudaGraphExecDestroy(ws->outer_graph);
     if (ws->outer_slab) cudaFree(ws->outer_slab);
     if (ws->d_outer_scalars) cudaFree(ws->d_outer_scalars);

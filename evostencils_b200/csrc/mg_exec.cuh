@@ -13,6 +13,9 @@ namespace mg {
 template <typename T>
 int materialise_zero(mg_workspace* ws, Level& lv);      // deferred zero fill, defined with exec_zero below
 
+constexpr int TAIL_RING_SLOTS = 32;                          // device slots for directly launched tail programs
+constexpr size_t TAIL_POOL_BYTES = (size_t)16 << 20;         // device slots for the programs of captured cycles
+
 template <typename T>
 inline FieldSet<T> fieldset(void* const* arr) {
     FieldSet<T> fs;
@@ -299,14 +302,22 @@ int prepare(mg_workspace* ws) {
     size_t bytes = (size_t)nvec * F * lv.g.total * sizeof(T);
     ws->cgs_smem_bytes = bytes <= 200 * 1024 ? bytes : 0;
     if (!ws->tail) ws->tail = new TailProgram();
-    ws->tail->n_cmds = 0;
+    ws->tail->h.n_cmds = 0;
+    if (!ws->tail_pool) {
+        ws->tail_ring_begin = TAIL_POOL_BYTES;
+        ws->tail_pool_bytes = TAIL_POOL_BYTES + (size_t)TAIL_RING_SLOTS * sizeof(TailProgram);
+        MG_CUDA(cudaMalloc(&ws->tail_pool, ws->tail_pool_bytes));
+        MG_CUDA(cudaHostAlloc(&ws->tail_stage, sizeof(TailProgram), cudaHostAllocDefault));
+        MG_CUDA(cudaStreamCreateWithFlags(&ws->aux_stream, cudaStreamNonBlocking));
+    }
     // The opt-in is a property of the function, not of the workspace: several workspaces live in
     // one process (slab + replicated coarse levels, one per virtual rank), so always allow the
     // maximum instead of this workspace's size.
     const int smem_cap = 200 * 1024;
     MG_CUDA(cudaFuncSetAttribute(k_coarse_cg<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
     MG_CUDA(cudaFuncSetAttribute(k_coarse_bicgstab<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
-    MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
     if (bytes > (size_t)smem_cap && ws->cgs_work_bytes < bytes) {
         if (ws->cgs_work) cudaFree(ws->cgs_work);
         MG_CUDA(cudaMalloc(&ws->cgs_work, bytes));
@@ -378,7 +389,7 @@ inline void tail_set(void** dst, const FieldSet<T>& fs) {
 
 inline TailCmd& tail_new(mg_workspace* ws, int kind, int level) {
     TailProgram& p = *ws->tail;
-    TailCmd& c = p.cmd[p.n_cmds++];
+    TailCmd& c = p.cmd[p.h.n_cmds++];
     memset(&c, 0, sizeof(c));
     c.kind = kind;
     c.lv = level - ws->min_level;
@@ -388,28 +399,71 @@ inline TailCmd& tail_new(mg_workspace* ws, int kind, int level) {
 
 template <typename T, int D, int F>
 int tail_flush(mg_workspace* ws) {
-    if (!ws->tail || ws->tail->n_cmds == 0) return MG_OK;
+    if (!ws->tail || ws->tail->h.n_cmds == 0) return MG_OK;
     TailProgram& p = *ws->tail;
-    p.cgs_kind = ws->cgs_kind;
-    p.cgs_max_its = ws->cgs_max_its;
-    p.cgs_reduction = ws->cgs_reduction;
-    p.robin = ws->bc_kind == MG_BC_HELMHOLTZ_ROBIN ? 1 : 0;
-    p.gwork = ws->cgs_work;
-    p.cgs_in_smem = ws->cgs_smem_bytes > 0 ? 1 : 0;
+    p.h.cgs_kind = ws->cgs_kind;
+    p.h.cgs_max_its = ws->cgs_max_its;
+    p.h.cgs_reduction = ws->cgs_reduction;
+    p.h.robin = ws->bc_kind == MG_BC_HELMHOLTZ_ROBIN ? 1 : 0;
+    p.h.gwork = ws->cgs_work;
+    p.h.cgs_in_smem = ws->cgs_smem_bytes > 0 ? 1 : 0;
     bool has_cgs = false;
-    for (int i = 0; i < p.n_cmds; ++i) has_cgs = has_cgs || p.cmd[i].kind == T_CGS;
+    for (int i = 0; i < p.h.n_cmds; ++i) has_cgs = has_cgs || p.cmd[i].kind == T_CGS;
     for (int level = ws->min_level; level <= ws->max_level && level - ws->min_level < TAIL_MAX_LEVELS; ++level) {
         Level& lv = ws->L(level);
-        TailLevel& tl = p.lv[level - ws->min_level];
+        TailLevel& tl = p.h.lv[level - ws->min_level];
         tl.g = lv.g;
         tl.op = lv.d_op;
         double h = 1.0 / (double)(lv.g.n - 1);
         tl.bc_factor = t_div(make_cplx(1.0, 0.0), make_cplx(1.0, -ws->bc_k * h));
         tl.st.c = lv.star_c; tl.st.x = lv.star_x; tl.st.y = lv.star_y; tl.st.z = lv.star_z;
     }
-    launch_k(ws, k_tail<T, D, F>, 1, TAIL_NT, has_cgs ? ws->cgs_smem_bytes : 0, p);
+    // upload: header + the commands in use.  A program of a cycle being captured keeps its slot until
+    // the cycles are freed; a direct launch takes the next ring slot (the stream is drained when the
+    // ring wraps, so no kernel still reads the slot that is overwritten).
+    const size_t bytes = sizeof(TailHeader) + (size_t)p.h.n_cmds * sizeof(TailCmd);
+    cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+    MG_CUDA(cudaStreamIsCapturing(ws->stream, &capturing));
+    unsigned char* slot = nullptr;
+    if (capturing != cudaStreamCaptureStatusNone) {
+        const size_t need = (bytes + 255) & ~(size_t)255;
+        if (ws->tail_pool_used + need > ws->tail_ring_begin) return fail(MG_ERR_STATE, "tail program pool exhausted");
+        slot = ws->tail_pool + ws->tail_pool_used;
+        ws->tail_pool_used += need;
+    } else {
+        if (ws->tail_ring_cursor == TAIL_RING_SLOTS) {
+            MG_CUDA(cudaStreamSynchronize(ws->stream));
+            ws->tail_ring_cursor = 0;
+        }
+        slot = ws->tail_pool + ws->tail_ring_begin + (size_t)ws->tail_ring_cursor++ * sizeof(TailProgram);
+    }
+    memcpy(ws->tail_stage, &p, bytes);
+    {
+        // the upload is not part of the cycle graph: it runs now, on its own stream (a synchronising call
+        // is only allowed inside a capture sequence of this thread in relaxed mode)
+        cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
+        MG_CUDA(cudaThreadExchangeStreamCaptureMode(&mode));
+        cudaError_t e1 = cudaMemcpyAsync(slot, ws->tail_stage, bytes, cudaMemcpyHostToDevice, ws->aux_stream);
+        cudaError_t e2 = cudaStreamSynchronize(ws->aux_stream);
+        MG_CUDA(cudaThreadExchangeStreamCaptureMode(&mode));
+        if (e1 != cudaSuccess || e2 != cudaSuccess)
+            return fail(MG_ERR_CUDA, std::string("tail program upload: ") + cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+    }
+    // lean interpreter when every command is one a scalar real star-stencil cycle uses (mg_tail.cuh)
+    bool lean = F == 1 && sizeof(T) == sizeof(double) && ws->cgs_kind == MG_CGS_CG && ws->tail_lean;
+    for (int i = 0; i < p.h.n_cmds && lean; ++i) {
+        const TailCmd& c = p.cmd[i];
+        switch (c.kind) {
+            case T_SMOOTH_POINT: case T_RESIDUAL: case T_RESIDUAL_RESTRICT: lean = c.star != 0; break;
+            case T_RESTRICT: case T_ZERO: case T_PROLONG: case T_CGS: break;
+            default: lean = false;
+        }
+    }
+    const size_t smem = has_cgs ? ws->cgs_smem_bytes : 0;
+    if (lean) launch_k(ws, k_tail<T, D, F, true>, 1, TAIL_NT, smem, reinterpret_cast<const TailProgram*>(slot));
+    else launch_k(ws, k_tail<T, D, F, false>, 1, TAIL_NT, smem, reinterpret_cast<const TailProgram*>(slot));
     count(ws);
-    p.n_cmds = 0;
+    p.h.n_cmds = 0;
     return MG_OK;
 }
 
@@ -421,7 +475,7 @@ int tail_append(mg_workspace* ws, const mg_op& op) {
     if (op.kind == MG_OP_RESTRICT || op.kind == MG_OP_RESIDUAL_RESTRICT) top = op.level + 1;
     int bottom = (op.kind == MG_OP_PROLONG_ADD || op.kind == MG_OP_PROLONG) ? op.level - 1 : op.level;
     if (!tail_level_ok(ws, top) || !ws->has_level(bottom)) return 0;
-    if (ws->tail->n_cmds + 6 > TAIL_MAX_CMDS) {
+    if (ws->tail->h.n_cmds + 6 > TAIL_MAX_CMDS) {
         int rc = tail_flush<T, D, F>(ws);
         if (rc) return rc;
     }
@@ -446,6 +500,11 @@ int tail_append(mg_workspace* ws, const mg_op& op) {
                 TailCmd& cmd = tail_new(ws, sm.point ? T_SMOOTH_POINT : T_SMOOTH_TILE, op.level);
                 cmd.colour = (sm.point && sm.colored) ? c : -1;
                 cmd.star = (ws->use_fast && lv.star && sm.point && sm.m == 1) ? 1 : 0;
+                if (cmd.star && cmd.colour >= 0 && F == 1) {      // in place: no buffer flip, only the colour's nodes
+                    cmd.inplace = 1;
+                    dst = src;
+                    flip[0] = false;
+                }
                 cmd.omega = sm.w00;
                 cmd.sm = sm.d_table;
                 cmd.w = sm.d_w;

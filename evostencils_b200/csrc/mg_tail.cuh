@@ -6,6 +6,13 @@
 // captured graph.  The commands call the same per-node device functions as the grid kernels
 // (mg_kernels_generic.cuh) and the same Krylov bodies (mg_coarse.cuh): results are bit-identical.
 // Fields of these levels are L1/L2 resident (65^2 doubles = 34 KB per array).
+//
+// The program lives in device memory (uploaded once when the cycle is captured): its header (level
+// table, Krylov settings) and the commands in use are copied to shared memory in one pass at kernel
+// start (measured with clock64: reading each command from the kernel parameter bank, or from L2
+// one step ahead, put ~1000 cycles under every step -- more than the work of a step on levels <= 4).
+// Coloured star sweeps run in place and visit only the nodes of their colour (a node of one
+// colour reads only nodes of the other), which halves the work of a Gauss-Seidel step.
 #pragma once
 #include "../../include/mgengine.h"
 #include "mg_coarse.cuh"
@@ -26,7 +33,7 @@ struct TailCmd {
     int colour;                    // SMOOTH_POINT: -1 all, 0/1 colour
     int add;                       // PROLONG: 1 = sol += omega P e, 0 = dst = P e
     int star;                      // scalar real star stencil: coefficients from TailLevel::st, weight = omega
-    int pad_;
+    int inplace;                   // coloured star sweep in place (c == a): only nodes of `colour` are visited
     double omega;
     const void* sm;                // SmootherTable<T>
     const void* w;                 // W tables
@@ -34,6 +41,9 @@ struct TailCmd {
     void* b[MG_MAX_FIELDS];        // right-hand side of the level the residual is formed on
     void* c[MG_MAX_FIELDS];        // destination
 };
+
+static_assert(sizeof(TailCmd) % 16 == 0, "commands are fetched in 16-byte words");
+constexpr int TAIL_CMD_WORDS = sizeof(TailCmd) / 16;
 
 struct StarCoef {                   // (2d+1)-point star, canonical order z-, y-, x-, c, x+, y+, z+
     double c, x, y, z;
@@ -63,15 +73,27 @@ __device__ __forceinline__ double star_apply(const StarCoef& s, const double* u,
     return a;
 }
 
-struct TailProgram {
+struct TailHeader {
     int n_cmds;
     int cgs_kind, cgs_max_its, robin;
     double cgs_reduction;
     void* gwork;                   // global Krylov scratch when the vectors do not fit into shared memory
     int cgs_in_smem;
+    int pad_[3];
     TailLevel lv[TAIL_MAX_LEVELS];
-    TailCmd cmd[TAIL_MAX_CMDS];
 };
+static_assert(sizeof(TailHeader) % 16 == 0, "the header is copied to shared memory in 16-byte words");
+
+struct TailProgram {
+    TailHeader h;
+    TailCmd cmd[TAIL_MAX_CMDS];    // only the first h.n_cmds are uploaded
+};
+
+__device__ __forceinline__ uint4 ld_cmd_word(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
 
 template <typename T>
 __device__ __forceinline__ FieldSet<T> tail_fields(void* const* p) {
@@ -108,13 +130,40 @@ __device__ inline void tail_bc(const Geom& g, cplx* u, cplx c) {
     }
 }
 
-template <typename T, int D, int F>
-__global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailProgram prog) {
+// LEAN: only the commands of a scalar real star-stencil cycle (star sweeps, star residual /
+// restriction, zero, prolongation, CG).  The full interpreter is ~200 KB of code, more than the
+// instruction cache holds, and since every step runs a different part of it each step paid
+// ~1000 cycles of instruction fetch (clock64, even for a zero fill); the lean variant is what a
+// Poisson cycle needs and stays cache resident.  The host picks it when the program qualifies
+// (tail_is_lean in mg_exec.cuh).
+template <typename T, int D, int F, bool LEAN>
+__global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict__ gprog) {
     pdl_sync();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ T s8[8];
-    for (int ci = 0; ci < prog.n_cmds; ++ci) {
-        const TailCmd& cmd = prog.cmd[ci];
+    __shared__ __align__(16) unsigned char s_head[sizeof(TailHeader)];
+    __shared__ __align__(16) uint4 s_cmd[TAIL_MAX_CMDS * TAIL_CMD_WORDS];
+#ifdef MG_TAIL_TIMING
+    __shared__ long long t_step[TAIL_MAX_CMDS + 1];
+#endif
+    {
+        // the whole program (header + commands in use) in one coalesced pass: one L2 latency in total
+        // (fetching command i+1 during step i put an L2 round trip, ~1200 cycles, under every step)
+        const uint4* src = reinterpret_cast<const uint4*>(gprog);
+        uint4* dst = reinterpret_cast<uint4*>(s_head);
+        const int n = reinterpret_cast<const int*>(gprog)[0];           // TailHeader::n_cmds
+        for (int k = threadIdx.x; k < (int)(sizeof(TailHeader) / 16); k += TAIL_NT) dst[k] = src[k];
+        const uint4* csrc = reinterpret_cast<const uint4*>(&gprog->cmd[0]);
+        for (int k = threadIdx.x; k < n * TAIL_CMD_WORDS; k += TAIL_NT) s_cmd[k] = csrc[k];
+    }
+    __syncthreads();
+    const TailHeader& prog = *reinterpret_cast<const TailHeader*>(s_head);
+    const int n_cmds = prog.n_cmds;
+    for (int ci = 0; ci < n_cmds; ++ci) {
+#ifdef MG_TAIL_TIMING
+        if (threadIdx.x == 0) t_step[ci] = clock64();
+#endif
+        const TailCmd& cmd = reinterpret_cast<const TailCmd*>(s_cmd)[ci];
         const Geom g = prog.lv[cmd.lv].g;
         const OperatorTable<T>* op = static_cast<const OperatorTable<T>*>(prog.lv[cmd.lv].op);
         const int nodes = (D == 3) ? g.n * g.n * g.nz : g.n * g.n;
@@ -123,6 +172,25 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
         switch (cmd.kind) {
             case T_SMOOTH_POINT: {
                 if constexpr (F == 1 && sizeof(T) == sizeof(double)) {
+                    if (cmd.star && cmd.inplace) {                  // u += w (f - A u) on the nodes of the colour only
+                        const StarCoef st = prog.lv[cmd.lv].st;
+                        const double* rhs = static_cast<const double*>(cmd.b[0]);
+                        double* u = static_cast<double*>(cmd.c[0]);
+                        // n - 1 = 2^L: slots of (n-1)/2 colour nodes per interior row (y, z), decoded by shifts
+                        const int half = (g.n - 1) >> 1, sh = 31 - __clz(half);
+                        const int rows = (D == 3) ? (g.n - 2) * (g.nz - 2) : g.n - 2;
+#pragma unroll 4
+                        for (int i = threadIdx.x; i < rows * half; i += TAIL_NT) {
+                            const int r = i >> sh, k = i & (half - 1);
+                            y = 1 + ((D == 3) ? r % (g.n - 2) : r);
+                            z = (D == 3) ? 1 + r / (g.n - 2) : 0;
+                            x = 1 + 2 * k + ((1 + y + z + g.z0 + cmd.colour) & 1);
+                            if (x > g.n - 2 || (D == 3 && (z + g.z0 < 1 || z + g.z0 > g.n - 2))) continue;
+                            const long long idx = node_index<D>(g, x, y, z);
+                            u[idx] = u[idx] + cmd.omega * (rhs[idx] - star_apply<D>(st, u, idx, g));
+                        }
+                        break;
+                    }
                     if (cmd.star) {                                 // dst = src + w (f - A src) on the colour
                         const StarCoef st = prog.lv[cmd.lv].st;
                         const double* src = static_cast<const double*>(cmd.a[0]);
@@ -140,15 +208,17 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
                         break;
                     }
                 }
-                const SmootherTable<T>* sm = static_cast<const SmootherTable<T>*>(cmd.sm);
-                const T* w = static_cast<const T*>(cmd.w);
-                for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
-                    tail_decode<D>(i, g.n, x, y, z);
-                    smooth_point_node<T, D, F>(g, op, sm, w, A, B, C, cmd.colour, x, y, z);
+                if constexpr (!LEAN) {
+                    const SmootherTable<T>* sm = static_cast<const SmootherTable<T>*>(cmd.sm);
+                    const T* w = static_cast<const T*>(cmd.w);
+                    for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                        tail_decode<D>(i, g.n, x, y, z);
+                        smooth_point_node<T, D, F>(g, op, sm, w, A, B, C, cmd.colour, x, y, z);
+                    }
                 }
                 break;
             }
-            case T_SMOOTH_TILE: {
+            case T_SMOOTH_TILE: if constexpr (!LEAN) {
                 const SmootherTable<T>* sm = static_cast<const SmootherTable<T>*>(cmd.sm);
                 const T* w = static_cast<const T*>(cmd.w);
                 const int t0 = (g.n - 1) / sm->period[0] + 1, t1 = (g.n - 1) / sm->period[1] + 1;
@@ -158,7 +228,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
                     smooth_tile_node<T, D, F>(g, op, sm, w, A, B, C, tx, r % t1, r / t1);
                 }
                 break;
-            }
+            } else break;
             case T_RESIDUAL:
                 if constexpr (F == 1 && sizeof(T) == sizeof(double)) {
                     if (cmd.star) {
@@ -176,10 +246,11 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
                         break;
                     }
                 }
-                for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
-                    tail_decode<D>(i, g.n, x, y, z);
-                    residual_node<T, D, F>(g, op, A, B, C, x, y, z);
-                }
+                if constexpr (!LEAN)
+                    for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                        tail_decode<D>(i, g.n, x, y, z);
+                        residual_node<T, D, F>(g, op, A, B, C, x, y, z);
+                    }
                 break;
             case T_RESTRICT:
             case T_RESIDUAL_RESTRICT: {
@@ -220,7 +291,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
                 for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
                     tail_decode<D>(i, g.n, x, y, z);
                     if (cmd.kind == T_RESTRICT) restrict_node<T, D, F>(g, gf, A, C, x, y, z);
-                    else residual_restrict_node<T, D, F>(g, gf, opf, A, B, C, x, y, z);
+                    else if constexpr (!LEAN) residual_restrict_node<T, D, F>(g, gf, opf, A, B, C, x, y, z);
                 }
                 break;
             }
@@ -230,6 +301,50 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
                 break;
             case T_PROLONG: {
                 const Geom gc = prog.lv[cmd.lv - 1].g;
+                if constexpr (F == 1 && sizeof(T) == sizeof(double)) {
+                    // branch-free form of prolong_node: all corner candidates are loaded (a coarse node is
+                    // its own candidate where the fine index is even) and added in the order (cz, cy, cx)
+                    const double* e = static_cast<const double*>(cmd.a[0]);
+                    double* u = static_cast<double*>(cmd.c[0]);
+                    const int sh = 31 - __clz(g.n - 1);
+                    const int rows = (D == 3) ? (g.n - 2) * (g.nz - 2) : g.n - 2;
+#pragma unroll 2
+                    for (int i = threadIdx.x; i < (rows << sh); i += TAIL_NT) {
+                        const int r = i >> sh;
+                        x = 1 + (i & (g.n - 2));
+                        y = 1 + ((D == 3) ? r % (g.n - 2) : r);
+                        z = (D == 3) ? 1 + r / (g.n - 2) : 0;
+                        if (x > g.n - 2 || (D == 3 && (z + g.z0 < 1 || z + g.z0 > g.n - 2))) continue;
+                        const int zg = z + g.z0;
+                        const int px = x & 1, py = y & 1, pz = (D == 3) ? (zg & 1) : 0;
+                        const long long c = node_index<D>(gc, x >> 1, y >> 1, (D == 3) ? (zg >> 1) - gc.z0 : 0);
+                        const long long dy = py ? gc.pitch : 0, dz = pz ? gc.plane : 0;
+                        double acc = e[c];
+                        const double c100 = e[c + px], c010 = e[c + dy], c110 = e[c + dy + px];
+                        if (px) acc = acc + c100;
+                        if (py) {
+                            acc = acc + c010;
+                            if (px) acc = acc + c110;
+                        }
+                        if (D == 3) {
+                            const double c001 = e[c + dz], c101 = e[c + dz + px], c011 = e[c + dz + dy],
+                                         c111 = e[c + dz + dy + px];
+                            if (pz) {
+                                acc = acc + c001;
+                                if (px) acc = acc + c101;
+                                if (py) {
+                                    acc = acc + c011;
+                                    if (px) acc = acc + c111;
+                                }
+                            }
+                        }
+                        const int k = px + py + pz;
+                        const double pe = k == 0 ? acc : (k == 1 ? 0.5 : (k == 2 ? 0.25 : 0.125)) * acc;
+                        const long long idx = node_index<D>(g, x, y, z);
+                        u[idx] = cmd.add ? u[idx] + cmd.omega * pe : pe;
+                    }
+                    break;
+                }
                 for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
                     tail_decode<D>(i, g.n, x, y, z);
                     prolong_node<T, D, F>(g, gc, A, C, cmd.omega, cmd.add, x, y, z);
@@ -238,20 +353,29 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const __grid_constant__ TailPr
             }
             case T_CGS: {
                 T* work = prog.cgs_in_smem ? reinterpret_cast<T*>(smem_raw) : static_cast<T*>(prog.gwork);
-                if (prog.cgs_kind == MG_CGS_CG)
+                if (LEAN || prog.cgs_kind == MG_CGS_CG)
                     coarse_cg_body<T, D, F>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, s8);
-                else
+                else if constexpr (!LEAN)
                     coarse_bicgstab_body<T, D, F>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, prog.robin,
                                                   prog.lv[cmd.lv].bc_factor, s8);
                 break;
             }
             case T_BC:
-                for (int f = 0; f < F; ++f) tail_bc(g, C.p[f], prog.lv[cmd.lv].bc_factor);
+                if constexpr (!LEAN)
+                    for (int f = 0; f < F; ++f) tail_bc(g, C.p[f], prog.lv[cmd.lv].bc_factor);
                 break;
             default: break;
         }
         __syncthreads();
     }
+#ifdef MG_TAIL_TIMING
+    if (threadIdx.x == 0) {
+        t_step[n_cmds] = clock64();
+        for (int ci = 0; ci < n_cmds; ++ci)
+            printf("step %d kind %d lv %d colour %d star %d cycles %lld\n", ci, gprog->cmd[ci].kind, gprog->cmd[ci].lv,
+                   gprog->cmd[ci].colour, gprog->cmd[ci].star, t_step[ci + 1] - t_step[ci]);
+    }
+#endif
 }
 
 }  // namespace mg

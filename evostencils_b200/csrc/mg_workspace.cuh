@@ -115,7 +115,15 @@ struct mg_workspace {
                                                 // measured neutral inside captured graphs, so off by default
     bool use_tail = true;                       // small levels run inside the single-CTA tail kernel
     int tail_max_level = 6;                     // levels <= this are "small" (MG_TAIL_LEVEL overrides)
-    mg::TailProgram* tail = nullptr;            // command list being assembled (host copy, passed by value)
+    bool tail_lean = true;                      // use the lean interpreter when a program qualifies (MG_TAIL_LEAN)
+    mg::TailProgram* tail = nullptr;            // command list being assembled (host copy)
+    // device copies of the tail programs: [0, tail_ring_begin) holds the programs of captured cycles
+    // (bump allocation, reset when the cycles are freed), the rest is a ring for direct launches
+    unsigned char* tail_pool = nullptr;
+    size_t tail_pool_bytes = 0, tail_pool_used = 0, tail_ring_begin = 0;
+    int tail_ring_cursor = 0;
+    void* tail_stage = nullptr;                 // pinned staging buffer for the upload
+    cudaStream_t aux_stream = nullptr;          // uploads that must not be captured into the cycle graph
     // preconditioned BiCGStab outer solver (mg_outer.cuh)
     mg::HostOperator hop_outer;                 // unshifted operator A of the finest level
     bool outer_set = false, outer_dirty = true;

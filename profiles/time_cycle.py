@@ -19,16 +19,20 @@ def main():
     us, fs = bench.synthetic_inputs(problem, hi, pinned=False)
     ws.upload("sol", hi, 0, us[0]); ws.upload("rhs", hi, 0, fs[0])
     grammar = Grammar(problem, lo, hi, maximum_local_system_size=4)
-    pop = bench.load_population()[:4]
+    pop = bench.load_population()[:8]
     default_cycle = lambda level: lowering.default_cycle_ops(problem, level, elo, {})
-    out = []
+    out, solve_ms = [], []
     for string in pop:
         program = lowering.lower(grammar.compile(string)[0], lo, hi)
         ws.clear_programs()
         cyc = ws.build_cycle(program.ops, default_cycle)
         ws.run_cycles(cyc, 3)
         out.append(round(ws.run_cycles(cyc, 20) / 20, 4))
-    print(json.dumps({"tail_level": os.environ.get("MG_TAIL_LEVEL", "6"), "ms_per_cycle": out}))
+        ws.upload("sol", hi, 0, us[0])
+        hist, conv, ms = ws.solve(cyc, 1e-12, 100)          # one graph launch + stream sync + host check per iteration
+        solve_ms.append(round(ms / (len(hist) - 1), 4))
+    print(json.dumps({"tail_level": os.environ.get("MG_TAIL_LEVEL", "6"), "ms_per_cycle": out,
+                      "ms_per_cycle_in_solve": solve_ms}))
     gen.close()
 
 
