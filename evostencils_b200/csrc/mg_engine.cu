@@ -68,7 +68,14 @@ static int create_impl(mg_workspace** out, int dimension, int min_level, int max
     ws->dim = dimension; ws->min_level = min_level; ws->max_level = max_level;
     ws->n_fields = n_fields; ws->dtype = dtype; ws->device = device;
     ws->elem = dtype == MG_F64 ? 8 : 16;
-    ws->tail_max_level = dimension == 3 ? 4 : 6;        // <= ~5000 nodes per level: 65^2 or 17^3
+    // small levels run in the tail kernel: a cluster of 16 CTAs up to 129^2 nodes (2D; measured best:
+    // level 7, CTA 0 alone up to level 5), a single CTA up to 17^3 nodes (3D)
+    ws->tail_max_level = dimension == 3 ? 4 : 7;
+    ws->tail_ctas = dimension == 3 ? 1 : 16;
+    if (const char* v = std::getenv("MG_TAIL_CTAS")) ws->tail_ctas = std::atoi(v);
+    if (ws->tail_ctas < 1 || ws->tail_ctas > 16) ws->tail_ctas = 1;
+    ws->tail_solo_level = dimension == 3 ? 3 : 5;
+    if (const char* v = std::getenv("MG_TAIL_SOLO")) ws->tail_solo_level = std::atoi(v);
     if (const char* v = std::getenv("MG_TAIL_LEVEL")) ws->tail_max_level = std::atoi(v);
     if (const char* v = std::getenv("MG_TAIL_LEAN")) ws->tail_lean = std::atoi(v) != 0;
     if (const char* v = std::getenv("MG_PDL")) ws->use_pdl = std::atoi(v) != 0;

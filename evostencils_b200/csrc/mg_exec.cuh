@@ -307,7 +307,7 @@ int prepare(mg_workspace* ws) {
         ws->tail_ring_begin = TAIL_POOL_BYTES;
         ws->tail_pool_bytes = TAIL_POOL_BYTES + (size_t)TAIL_RING_SLOTS * sizeof(TailProgram);
         MG_CUDA(cudaMalloc(&ws->tail_pool, ws->tail_pool_bytes));
-        MG_CUDA(cudaHostAlloc(&ws->tail_stage, sizeof(TailProgram), cudaHostAllocDefault));
+        MG_CUDA(cudaHostAlloc(&ws->tail_stage, (size_t)(TAIL_RING_SLOTS + 1) * sizeof(TailProgram), cudaHostAllocDefault));
         MG_CUDA(cudaStreamCreateWithFlags(&ws->aux_stream, cudaStreamNonBlocking));
     }
     // The opt-in is a property of the function, not of the workspace: several workspaces live in
@@ -318,6 +318,10 @@ int prepare(mg_workspace* ws) {
     MG_CUDA(cudaFuncSetAttribute(k_coarse_bicgstab<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
     MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
     MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    if (ws->tail_ctas > 8) {
+        MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    }
     if (bytes > (size_t)smem_cap && ws->cgs_work_bytes < bytes) {
         if (ws->cgs_work) cudaFree(ws->cgs_work);
         MG_CUDA(cudaMalloc(&ws->cgs_work, bytes));
@@ -409,6 +413,7 @@ int tail_flush(mg_workspace* ws) {
     p.h.cgs_in_smem = ws->cgs_smem_bytes > 0 ? 1 : 0;
     bool has_cgs = false;
     for (int i = 0; i < p.h.n_cmds; ++i) has_cgs = has_cgs || p.cmd[i].kind == T_CGS;
+    for (int i = 0; i < p.h.n_cmds; ++i) p.cmd[i].next_wide = i + 1 < p.h.n_cmds ? p.cmd[i + 1].wide : 1;
     for (int level = ws->min_level; level <= ws->max_level && level - ws->min_level < TAIL_MAX_LEVELS; ++level) {
         Level& lv = ws->L(level);
         TailLevel& tl = p.h.lv[level - ws->min_level];
@@ -430,17 +435,9 @@ int tail_flush(mg_workspace* ws) {
         if (ws->tail_pool_used + need > ws->tail_ring_begin) return fail(MG_ERR_STATE, "tail program pool exhausted");
         slot = ws->tail_pool + ws->tail_pool_used;
         ws->tail_pool_used += need;
-    } else {
-        if (ws->tail_ring_cursor == TAIL_RING_SLOTS) {
-            MG_CUDA(cudaStreamSynchronize(ws->stream));
-            ws->tail_ring_cursor = 0;
-        }
-        slot = ws->tail_pool + ws->tail_ring_begin + (size_t)ws->tail_ring_cursor++ * sizeof(TailProgram);
-    }
-    memcpy(ws->tail_stage, &p, bytes);
-    {
         // the upload is not part of the cycle graph: it runs now, on its own stream (a synchronising call
         // is only allowed inside a capture sequence of this thread in relaxed mode)
+        memcpy(ws->tail_stage, &p, bytes);
         cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
         MG_CUDA(cudaThreadExchangeStreamCaptureMode(&mode));
         cudaError_t e1 = cudaMemcpyAsync(slot, ws->tail_stage, bytes, cudaMemcpyHostToDevice, ws->aux_stream);
@@ -448,6 +445,17 @@ int tail_flush(mg_workspace* ws) {
         MG_CUDA(cudaThreadExchangeStreamCaptureMode(&mode));
         if (e1 != cudaSuccess || e2 != cudaSuccess)
             return fail(MG_ERR_CUDA, std::string("tail program upload: ") + cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+    } else {
+        // stream-ordered copy from the pinned ring slot: no host synchronisation except when the ring wraps
+        if (ws->tail_ring_cursor == TAIL_RING_SLOTS) {
+            MG_CUDA(cudaStreamSynchronize(ws->stream));
+            ws->tail_ring_cursor = 0;
+        }
+        const size_t k = (size_t)ws->tail_ring_cursor++;
+        slot = ws->tail_pool + ws->tail_ring_begin + k * sizeof(TailProgram);
+        unsigned char* stage = static_cast<unsigned char*>(ws->tail_stage) + (k + 1) * sizeof(TailProgram);
+        memcpy(stage, &p, bytes);
+        MG_CUDA(cudaMemcpyAsync(slot, stage, bytes, cudaMemcpyHostToDevice, ws->stream));
     }
     // lean interpreter when every command is one a scalar real star-stencil cycle uses (mg_tail.cuh)
     bool lean = F == 1 && sizeof(T) == sizeof(double) && ws->cgs_kind == MG_CGS_CG && ws->tail_lean;
@@ -459,9 +467,33 @@ int tail_flush(mg_workspace* ws) {
             default: lean = false;
         }
     }
-    const size_t smem = has_cgs ? ws->cgs_smem_bytes : 0;
-    if (lean) launch_k(ws, k_tail<T, D, F, true>, 1, TAIL_NT, smem, reinterpret_cast<const TailProgram*>(slot));
-    else launch_k(ws, k_tail<T, D, F, false>, 1, TAIL_NT, smem, reinterpret_cast<const TailProgram*>(slot));
+    {
+        // one cluster of tail_ctas CTAs (mg_tail.cuh); every CTA gets the Krylov scratch of CTA 0
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(ws->tail_ctas, 1, 1);
+        cfg.blockDim = dim3(TAIL_NT, 1, 1);
+        cfg.dynamicSmemBytes = has_cgs ? ws->cgs_smem_bytes : 0;
+        cfg.stream = ws->stream;
+        cudaLaunchAttribute attr[2];
+        int na = 0;
+        if (ws->tail_ctas > 1) {
+            attr[na].id = cudaLaunchAttributeClusterDimension;
+            attr[na].val.clusterDim.x = ws->tail_ctas;
+            attr[na].val.clusterDim.y = 1;
+            attr[na].val.clusterDim.z = 1;
+            ++na;
+        }
+        if (ws->use_pdl) {
+            attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[na].val.programmaticStreamSerializationAllowed = 1;
+            ++na;
+        }
+        cfg.attrs = attr;
+        cfg.numAttrs = na;
+        const TailProgram* dev = reinterpret_cast<const TailProgram*>(slot);
+        if (lean) cudaLaunchKernelEx(&cfg, k_tail<T, D, F, true>, dev);
+        else cudaLaunchKernelEx(&cfg, k_tail<T, D, F, false>, dev);
+    }
     count(ws);
     p.h.n_cmds = 0;
     return MG_OK;
@@ -481,6 +513,15 @@ int tail_append(mg_workspace* ws, const mg_op& op) {
     }
     const bool robin = ws->bc_kind == MG_BC_HELMHOLTZ_ROBIN && sizeof(T) == sizeof(cplx);
     Level& lv = ws->L(op.level);
+    // commands appended below for this op: wide (all CTAs of the cluster) unless the op stays on the
+    // smallest levels; the Krylov solve and the boundary update always run on CTA 0
+    struct WideMarker {
+        TailProgram& p; int begin; bool wide;
+        ~WideMarker() {
+            for (int i = begin; i < p.h.n_cmds; ++i)
+                p.cmd[i].wide = (wide && p.cmd[i].kind != T_CGS && p.cmd[i].kind != T_BC) ? 1 : 0;
+        }
+    } marker{*ws->tail, ws->tail->h.n_cmds, top > ws->tail_solo_level};
     switch (op.kind) {
         case MG_OP_SMOOTH: {
             if (op.smoother < 0 || op.smoother >= (int)ws->smoothers.size()) return fail(MG_ERR_INVALID, "bad smoother handle");

@@ -185,7 +185,9 @@ __device__ __forceinline__ double red_value(const Star2D& s, double w, double S,
 #ifndef MG_RBGS_MIN_CTAS
 #define MG_RBGS_MIN_CTAS 1
 #endif
-template <int NT, int R>
+// ZIN: u == 0 everywhere (pending zero fill, `u` is not dereferenced); a template parameter because the
+// run-time flag cost 8 registers and with them the fifth resident CTA of the R = 4 kernel.
+template <int NT, int R, bool ZIN>
 __global__ void __launch_bounds__(NT, R <= 4 ? MG_RBGS_MIN_CTAS : 1) k_rbgs2d(Geom g, Star2D s, const double* __restrict__ u,
                                                 const double* __restrict__ f, double* __restrict__ out, double w,
                                                 int pf) {
@@ -195,7 +197,7 @@ __global__ void __launch_bounds__(NT, R <= 4 ? MG_RBGS_MIN_CTAS : 1) k_rbgs2d(Ge
     const int n = g.n;
     const long long pitch = g.pitch;
     const int y0 = 1 + blockIdx.y * R;
-    const bool zin = u == nullptr;                             // u == 0 everywhere (pending zero fill): no loads of u
+    constexpr bool zin = ZIN;
     if (pf > 0 && threadIdx.x < 2 * R && !(zin && threadIdx.x < R)) {      // own rows of the band `pf` bands ahead
         const int row = y0 + pf * R + (threadIdx.x % R);
         if (row <= n - 1)

@@ -160,9 +160,13 @@ inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm, int c_begin, 
             dim3 grid = strip_grid(lv, 2, r, lv.g.n - 2);
             static const int pf_env = tunable("MG_RBGS_PF", 20);
             const int pf = lv.g.n > 2049 ? pf_env : 0;            // smaller levels are L2 resident anyway
-            if (r == 8) launch_k(ws, k_rbgs2d<FAST_NT, 8>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00, pf);
-            else if (r == 4) launch_k(ws, k_rbgs2d<FAST_NT, 4>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00, pf);
-            else launch_k(ws, k_rbgs2d<FAST_NT, 2>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00, pf);
+#define MG_RB(R_, Z_) launch_k(ws, k_rbgs2d<FAST_NT, R_, Z_>, grid, FAST_NT, 0, lv.g, star2d(lv), src, rhs, dst, sm.w00, pf)
+            if (zero_in) {
+                if (r == 8) MG_RB(8, true); else if (r == 4) MG_RB(4, true); else MG_RB(2, true);
+            } else {
+                if (r == 8) MG_RB(8, false); else if (r == 4) MG_RB(4, false); else MG_RB(2, false);
+            }
+#undef MG_RB
         } else {
             launch_star2d<STAR_JACOBI>(ws, lv, valid_rows(rows_j, pick_rows(lv, 2)), src, rhs, dst, sm.w00, nullptr);
         }

@@ -11,6 +11,12 @@
 // table, Krylov settings) and the commands in use are copied to shared memory in one pass at kernel
 // start (measured with clock64: reading each command from the kernel parameter bank, or from L2
 // one step ahead, put ~1000 cycles under every step -- more than the work of a step on levels <= 4).
+// Cluster mode (tail_ctas > 1): the kernel is launched as ONE thread-block cluster.  Commands on
+// levels above `solo_level` are "wide": every CTA takes a slice of the nodes and the commands are
+// separated by barrier.cluster (release/acquire at cluster scope, ~0.2 us, makes the other CTAs'
+// stores visible to plain loads).  Commands on the smallest levels and the Krylov solve are run by
+// CTA 0 alone and separated by __syncthreads() only.  Every CTA walks the same command list, so
+// all of them execute the same sequence of cluster barriers.
 // Coloured star sweeps run in place and visit only the nodes of their colour (a node of one
 // colour reads only nodes of the other), which halves the work of a Gauss-Seidel step.
 #pragma once
@@ -34,6 +40,9 @@ struct TailCmd {
     int add;                       // PROLONG: 1 = sol += omega P e, 0 = dst = P e
     int star;                      // scalar real star stencil: coefficients from TailLevel::st, weight = omega
     int inplace;                   // coloured star sweep in place (c == a): only nodes of `colour` are visited
+    int wide;                      // executed by every CTA of the cluster (else by CTA 0 alone)
+    int next_wide;                 // `wide` of the following command (1 after the last): selects the barrier
+    int pad_[2];
     double omega;
     const void* sm;                // SmootherTable<T>
     const void* w;                 // W tables
@@ -116,6 +125,20 @@ __device__ __forceinline__ void tail_decode(int i, int n, int& x, int& y, int& z
     }
 }
 
+__device__ __forceinline__ unsigned cluster_rank() {
+    unsigned r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ unsigned cluster_size() {
+    unsigned r;
+    asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_barrier() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 __device__ inline void tail_bc(const Geom&, double*, cplx) {}
 __device__ inline void tail_bc(const Geom& g, cplx* u, cplx c) {
     for (int t = threadIdx.x; t < g.n; t += TAIL_NT) {
@@ -159,11 +182,20 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
     __syncthreads();
     const TailHeader& prog = *reinterpret_cast<const TailHeader*>(s_head);
     const int n_cmds = prog.n_cmds;
+    const int n_ctas = (int)cluster_size(), rank = (int)cluster_rank();
     for (int ci = 0; ci < n_cmds; ++ci) {
 #ifdef MG_TAIL_TIMING
         if (threadIdx.x == 0) t_step[ci] = clock64();
 #endif
         const TailCmd& cmd = reinterpret_cast<const TailCmd*>(s_cmd)[ci];
+        const bool wide = cmd.wide && n_ctas > 1;
+        const bool next_wide = cmd.next_wide && n_ctas > 1;
+        if (!wide && rank != 0) {                               // CTA 0 runs this command alone
+            if (next_wide) cluster_barrier();
+            continue;
+        }
+        const int first = (wide ? rank * TAIL_NT : 0) + (int)threadIdx.x;
+        const int stride = wide ? n_ctas * TAIL_NT : TAIL_NT;
         const Geom g = prog.lv[cmd.lv].g;
         const OperatorTable<T>* op = static_cast<const OperatorTable<T>*>(prog.lv[cmd.lv].op);
         const int nodes = (D == 3) ? g.n * g.n * g.nz : g.n * g.n;
@@ -180,7 +212,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                         const int half = (g.n - 1) >> 1, sh = 31 - __clz(half);
                         const int rows = (D == 3) ? (g.n - 2) * (g.nz - 2) : g.n - 2;
 #pragma unroll 4
-                        for (int i = threadIdx.x; i < rows * half; i += TAIL_NT) {
+                        for (int i = first; i < rows * half; i += stride) {
                             const int r = i >> sh, k = i & (half - 1);
                             y = 1 + ((D == 3) ? r % (g.n - 2) : r);
                             z = (D == 3) ? 1 + r / (g.n - 2) : 0;
@@ -197,7 +229,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                         const double* rhs = static_cast<const double*>(cmd.b[0]);
                         double* dst = static_cast<double*>(cmd.c[0]);
 #pragma unroll 4
-                        for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                        for (int i = first; i < nodes; i += stride) {
                             tail_decode<D>(i, g.n, x, y, z);
                             const long long idx = node_index<D>(g, x, y, z);
                             double v = src[idx];
@@ -211,7 +243,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                 if constexpr (!LEAN) {
                     const SmootherTable<T>* sm = static_cast<const SmootherTable<T>*>(cmd.sm);
                     const T* w = static_cast<const T*>(cmd.w);
-                    for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                    for (int i = first; i < nodes; i += stride) {
                         tail_decode<D>(i, g.n, x, y, z);
                         smooth_point_node<T, D, F>(g, op, sm, w, A, B, C, cmd.colour, x, y, z);
                     }
@@ -223,7 +255,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                 const T* w = static_cast<const T*>(cmd.w);
                 const int t0 = (g.n - 1) / sm->period[0] + 1, t1 = (g.n - 1) / sm->period[1] + 1;
                 const int t2 = (D == 3) ? (g.n - 1) / sm->period[2] + 1 : 1;
-                for (int i = threadIdx.x; i < t0 * t1 * t2; i += TAIL_NT) {
+                for (int i = first; i < t0 * t1 * t2; i += stride) {
                     int tx = i % t0, r = i / t0;
                     smooth_tile_node<T, D, F>(g, op, sm, w, A, B, C, tx, r % t1, r / t1);
                 }
@@ -237,7 +269,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                         const double* rhs = static_cast<const double*>(cmd.b[0]);
                         double* dst = static_cast<double*>(cmd.c[0]);
 #pragma unroll 4
-                        for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                        for (int i = first; i < nodes; i += stride) {
                             tail_decode<D>(i, g.n, x, y, z);
                             if (!is_interior<D>(g, x, y, z)) continue;
                             const long long idx = node_index<D>(g, x, y, z);
@@ -247,7 +279,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                     }
                 }
                 if constexpr (!LEAN)
-                    for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                    for (int i = first; i < nodes; i += stride) {
                         tail_decode<D>(i, g.n, x, y, z);
                         residual_node<T, D, F>(g, op, A, B, C, x, y, z);
                     }
@@ -264,7 +296,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                         double* dst = static_cast<double*>(cmd.c[0]);
                         const double w1[3] = {0.25, 0.5, 0.25};
 #pragma unroll 2
-                        for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                        for (int i = first; i < nodes; i += stride) {
                             tail_decode<D>(i, g.n, x, y, z);
                             if (!is_interior<D>(g, x, y, z)) continue;
                             const int zf = (D == 3) ? 2 * (z + g.z0) - gf.z0 : 0;
@@ -288,7 +320,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                         break;
                     }
                 }
-                for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                for (int i = first; i < nodes; i += stride) {
                     tail_decode<D>(i, g.n, x, y, z);
                     if (cmd.kind == T_RESTRICT) restrict_node<T, D, F>(g, gf, A, C, x, y, z);
                     else if constexpr (!LEAN) residual_restrict_node<T, D, F>(g, gf, opf, A, B, C, x, y, z);
@@ -297,7 +329,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
             }
             case T_ZERO:
                 for (int f = 0; f < F; ++f)
-                    for (long long i = threadIdx.x; i < g.total; i += TAIL_NT) C.p[f][i] = t_zero(T());
+                    for (long long i = first; i < g.total; i += stride) C.p[f][i] = t_zero(T());
                 break;
             case T_PROLONG: {
                 const Geom gc = prog.lv[cmd.lv - 1].g;
@@ -309,7 +341,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                     const int sh = 31 - __clz(g.n - 1);
                     const int rows = (D == 3) ? (g.n - 2) * (g.nz - 2) : g.n - 2;
 #pragma unroll 2
-                    for (int i = threadIdx.x; i < (rows << sh); i += TAIL_NT) {
+                    for (int i = first; i < (rows << sh); i += stride) {
                         const int r = i >> sh;
                         x = 1 + (i & (g.n - 2));
                         y = 1 + ((D == 3) ? r % (g.n - 2) : r);
@@ -345,7 +377,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                     }
                     break;
                 }
-                for (int i = threadIdx.x; i < nodes; i += TAIL_NT) {
+                for (int i = first; i < nodes; i += stride) {
                     tail_decode<D>(i, g.n, x, y, z);
                     prolong_node<T, D, F>(g, gc, A, C, cmd.omega, cmd.add, x, y, z);
                 }
@@ -366,7 +398,8 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                 break;
             default: break;
         }
-        __syncthreads();
+        if (n_ctas > 1 && (wide || next_wide)) cluster_barrier();
+        else __syncthreads();
     }
 #ifdef MG_TAIL_TIMING
     if (threadIdx.x == 0) {

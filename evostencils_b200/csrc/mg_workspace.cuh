@@ -115,6 +115,8 @@ struct mg_workspace {
                                                 // measured neutral inside captured graphs, so off by default
     bool use_tail = true;                       // small levels run inside the single-CTA tail kernel
     int tail_max_level = 6;                     // levels <= this are "small" (MG_TAIL_LEVEL overrides)
+    int tail_ctas = 1;                          // CTAs of the tail kernel's cluster (MG_TAIL_CTAS; 1: single CTA)
+    int tail_solo_level = 4;                    // levels <= this are run by CTA 0 alone (MG_TAIL_SOLO)
     bool tail_lean = true;                      // use the lean interpreter when a program qualifies (MG_TAIL_LEAN)
     mg::TailProgram* tail = nullptr;            // command list being assembled (host copy)
     // device copies of the tail programs: [0, tail_ring_begin) holds the programs of captured cycles
