@@ -138,7 +138,7 @@ def captured_traffic(stage):
 
 def algorithmic_bytes_per_dof(stage, dim=2):
     """SURVEY.md 8d table (fp64)."""
-    return {"jacobi": 24.0, "rbgs": 24.0, "residual": 24.0, "residual_restrict": 16.0 + 8.0 / 2 ** dim,
+    return {"jacobi": 24.0, "rbgs": 24.0, "block_jacobi": 24.0, "residual": 24.0, "residual_restrict": 16.0 + 8.0 / 2 ** dim,
             "prolong_add": 16.0 + 8.0 / 2 ** dim, "residual_norm": 16.0}[stage]
 
 
@@ -152,6 +152,9 @@ def stage_rooflines(gen, problem, level, peak_gbs, reps=20, warm=3):
     stages = {
         "jacobi": lowering.local_solve_statements(ir.ElementwiseDiagonal(op), op, level, 0.8, ir.Single),
         "rbgs": lowering.local_solve_statements(ir.ElementwiseDiagonal(op), op, level, 1.15, ir.RedBlack),
+        # block smoothers come in many tile shapes; 2x2 tiles stand for them in the share estimate
+        "block_jacobi": lowering.local_solve_statements(ir.generate_collective_block_jacobi(op, ((2, 2),)), op, level,
+                                                        0.6, ir.Single),
         "residual": [lowering.Op("residual", level, dst="res")],
         "residual_restrict": [lowering.Op("residual_restrict", level - 1, src="sol", dst="rhs")],
         "prolong_add": [lowering.Op("prolong_add", level, omega=1.0, src="sol", dst="sol")],

@@ -294,40 +294,54 @@ __global__ void __launch_bounds__(NT, R <= 4 ? MG_RBGS_MIN_CTAS : 1) k_rbgs2d(Ge
 // (thread = 2 adjacent columns), residuals exchanged through shared memory.  All loads up front.
 // Arithmetic identical to k_smooth_tile (ascending slot order, first term initialises the sum).
 struct Tile2D {
-    int px, py, m, cw, rb, full_index;
+    int px, py, m, cw, rb, full_index, pf;
 };
 
-template <int NT, int RMAX>
+// PX, PY are template parameters: slot positions, the row's position in its tile and the W row of
+// a complete tile are compile-time, only tiles cut by the Dirichlet boundary take the masked path
+// (with run-time tile shapes the index arithmetic made the sweep instruction-bound: 0.52 of the copy
+// peak at 4096^2).
+template <int NT, int PX, int PY>
 __global__ void __launch_bounds__(NT) k_tile2d(Geom g, Star2D s, Tile2D t, const SmootherTable<double>* __restrict__ st,
                                                 const double* __restrict__ wtab, const double* __restrict__ u,
                                                 const double* __restrict__ f, double* __restrict__ out) {
     pdl_sync();
-    __shared__ double r_s[RMAX][2 * NT];
-    __shared__ double w_s[16];
+    constexpr int M = PX * PY;
+    constexpr int RB = PY == 3 ? 3 : 4;                        // rows per band: a whole number of tiles
+    constexpr int CW = PX == 3 ? (2 * NT / 6) * 6 : 2 * NT;    // columns per strip: an even multiple of PX
+    __shared__ __align__(16) double r_s[RB][2 * NT];
+    __shared__ double w_s[M * M];
     const int lane = threadIdx.x & 31;
     const int n = g.n;
     const long long pitch = g.pitch;
     const int c0 = 2 * threadIdx.x;                            // column inside the strip
-    const int x0 = blockIdx.x * t.cw + c0;
+    const int x0 = blockIdx.x * CW + c0;
     const int xl = imin(x0, n - 1);                            // load column (even, in bounds)
-    const int yb = blockIdx.y * t.rb;                          // first row of the band (row 0 included)
-    const bool active = c0 < t.cw && x0 <= n - 2;
+    const int yb = blockIdx.y * RB;                            // first row of the band (row 0 included)
+    const bool active = c0 < CW && x0 <= n - 2;
     const int xe = lane == 0 ? imax(xl - 1, 0) : imin(xl + 2, n - 1);
-    if (threadIdx.x < t.m * t.m) w_s[threadIdx.x] = wtab[(long long)t.full_index * t.m * t.m + threadIdx.x];
-    double2 uu[RMAX + 2], ff[RMAX];
-    double ue[RMAX];
+    if (threadIdx.x < M * M) w_s[threadIdx.x] = wtab[(long long)t.full_index * M * M + threadIdx.x];
+    if (t.pf > 0 && threadIdx.x >= 32 && threadIdx.x < 32 + 2 * RB) {      // L2 prefetch, see k_rbgs2d
+        const int k = threadIdx.x - 32;
+        const int row = yb + t.pf * RB + (k % RB);
+        const long long col = (long long)blockIdx.x * CW;
+        if (row <= n - 1 && col + 2 * NT <= pitch) l2_prefetch_rows((k < RB ? u : f) + (long long)row * pitch + col, NT * 16);
+    }
+    double2 uu[RB + 2], ff[RB];
+    double ue[RB];
 #pragma unroll
-    for (int i = 0; i < RMAX + 2; ++i) uu[i] = ldf2(u + (long long)imin(yb - 1 + i, n) * pitch + xl);   // row -1 / n: guard rows
+    for (int i = 0; i < RB + 2; ++i) uu[i] = ldf2(u + (long long)imin(yb - 1 + i, n) * pitch + xl);   // row -1 / n: guard rows
 #pragma unroll
-    for (int i = 0; i < RMAX; ++i) ff[i] = ldf2(f + (long long)imin(yb + i, n) * pitch + xl);
+    for (int i = 0; i < RB; ++i) ff[i] = ldf2(f + (long long)imin(yb + i, n) * pitch + xl);
 #pragma unroll
-    for (int i = 0; i < RMAX; ++i) {
+    for (int i = 0; i < RB; ++i) {
         ue[i] = 0.0;
         if (lane == 0 || lane == 31) ue[i] = ldf1(u + (long long)imin(yb + i, n) * pitch + xe);
     }
+    __syncthreads();      // scheduling fence (see k_star2d); also publishes w_s
     const bool in0 = x0 >= 1 && x0 <= n - 2, in1 = x0 + 1 <= n - 2;
 #pragma unroll
-    for (int i = 0; i < RMAX; ++i) {
+    for (int i = 0; i < RB; ++i) {
         const int y = yb + i;
         const double2 um = uu[i], uc = uu[i + 1], un = uu[i + 2];
         double left = __shfl_up_sync(0xffffffffu, uc.y, 1);
@@ -338,49 +352,54 @@ __global__ void __launch_bounds__(NT) k_tile2d(Geom g, Star2D s, Tile2D t, const
         double r0 = 0.0, r1 = 0.0;
         if (rowin && in0) r0 = ff[i].x - star_at(s, um.x, left, uc.x, uc.y, un.x);
         if (rowin && in1) r1 = ff[i].y - star_at(s, um.y, uc.x, uc.y, right, un.y);
-        r_s[i][c0] = r0;
-        r_s[i][c0 + 1] = r1;
+        *reinterpret_cast<double2*>(&r_s[i][c0]) = make_double2(r0, r1);      // one 16-byte store: conflict-free
     }
     __syncthreads();
     if (!active) return;
-    const int full = (1 << t.m) - 1;
-    const int sx0 = c0 % t.px, sx1 = (c0 + 1) % t.px;
-    int qdx[4], qdy[4];                                        // slot q -> position in the tile (x outer)
+    constexpr int FULL = (1 << M) - 1;
+    const int sx0 = c0 % PX, sx1 = (c0 + 1) % PX;              // strips start at a multiple of PX
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        qdx[q] = q / t.py;
-        qdy[q] = q - qdx[q] * t.py;
-    }
-#pragma unroll
-    for (int i = 0; i < RMAX; ++i) {
+    for (int i = 0; i < RB; ++i) {
         const int y = yb + i;
-        if (i >= t.rb || y > n - 1) continue;
-        const int sy = i % t.py;
+        if (y > n - 1) continue;
+        const int sy = i % PY;                                  // bands start at a multiple of PY; i is unrolled
         double2 o = uu[i + 1];
         if (y >= 1 && y <= n - 2) {
+            const int by = y - sy;
+            const bool rows_full = by >= 1 && by + PY - 1 <= n - 2;
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 const int x = x0 + c;
                 if (x < 1 || x > n - 2) continue;
                 const int sx = c ? sx1 : sx0;
-                const int bx = x - sx, by = y - sy;                 // tile origin (global)
-                const int slot = sx * t.py + sy;
-                int mask = 0;
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int qx = bx + qdx[q], qy = by + qdy[q];
-                    if (q < t.m && qx >= 1 && qx <= n - 2 && qy >= 1 && qy <= n - 2) mask |= 1 << q;
-                }
-                const double* wrow = mask == full ? w_s + slot * t.m
-                                                  : wtab + ((long long)st->mask_index[mask] * t.m + slot) * t.m;
+                const int bx = x - sx;                          // tile origin (global)
+                const int slot = sx * PY + sy;
+                const double* rbase = &r_s[i - sy][c0 + c - sx];
                 double delta = 0.0;
-                bool first = true;
+                if (rows_full && bx >= 1 && bx + PX - 1 <= n - 2) {
+                    const double* wrow = w_s + slot * M;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    if (!((mask >> q) & 1)) continue;
-                    const double term = wrow[q] * r_s[i - sy + qdy[q]][c0 + c - sx + qdx[q]];
-                    delta = first ? term : delta + term;
-                    first = false;
+                    for (int q = 0; q < M; ++q) {               // slot q at (q / PY, q % PY), x outer
+                        const double term = wrow[q] * rbase[(q % PY) * 2 * NT + q / PY];
+                        delta = q == 0 ? term : delta + term;
+                    }
+                } else {
+                    int mask = 0;
+#pragma unroll
+                    for (int q = 0; q < M; ++q) {
+                        const int qx = bx + q / PY, qy = by + q % PY;
+                        if (qx >= 1 && qx <= n - 2 && qy >= 1 && qy <= n - 2) mask |= 1 << q;
+                    }
+                    const double* wrow = mask == FULL ? w_s + slot * M
+                                                      : wtab + ((long long)st->mask_index[mask] * M + slot) * M;
+                    bool first = true;
+#pragma unroll
+                    for (int q = 0; q < M; ++q) {
+                        if (!((mask >> q) & 1)) continue;
+                        const double term = wrow[q] * rbase[(q % PY) * 2 * NT + q / PY];
+                        delta = first ? term : delta + term;
+                        first = false;
+                    }
                 }
                 if (c) o.y = o.y + delta; else o.x = o.x + delta;
             }

@@ -82,11 +82,24 @@ inline bool fast_tile_smooth(mg_workspace* ws, Level& lv, Smoother& sm) {
         t.cw = (2 * FAST_NT) / (px == 3 ? 6 : 1) * (px == 3 ? 6 : 1);   // even multiple of px, <= 2*NT
         t.rb = py == 3 ? 3 : 4;
         t.full_index = sm.full_index;
+        static const int pf_env = tunable("MG_TILE_PF", 20);
+        t.pf = lv.g.n > 2049 ? pf_env : 0;
         dim3 grid((lv.g.n - 1 + t.cw - 1) / t.cw, (lv.g.n + t.rb - 1) / t.rb, 1);
-        launch_k(ws, k_tile2d<FAST_NT, 4>, grid, FAST_NT, 0, 
-            lv.g, star2d(lv), t, static_cast<const SmootherTable<double>*>(sm.d_table),
-            static_cast<const double*>(sm.d_w), static_cast<const double*>(lv.sol[lv.cur[0]][0]),
-            static_cast<const double*>(lv.rhs[0]), static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]));
+        const SmootherTable<double>* tab = static_cast<const SmootherTable<double>*>(sm.d_table);
+        const double* w = static_cast<const double*>(sm.d_w);
+        const double* src = static_cast<const double*>(lv.sol[lv.cur[0]][0]);
+        const double* rhs = static_cast<const double*>(lv.rhs[0]);
+        double* dst = static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]);
+#define MG_TILE(PX_, PY_) launch_k(ws, k_tile2d<FAST_NT, PX_, PY_>, grid, FAST_NT, 0, lv.g, star2d(lv), t, tab, w, src, rhs, dst)
+        if (px == 1 && py == 2) MG_TILE(1, 2);
+        else if (px == 2 && py == 1) MG_TILE(2, 1);
+        else if (px == 1 && py == 3) MG_TILE(1, 3);
+        else if (px == 3 && py == 1) MG_TILE(3, 1);
+        else if (px == 2 && py == 2) MG_TILE(2, 2);
+        else if (px == 1 && py == 4) MG_TILE(1, 4);
+        else if (px == 4 && py == 1) MG_TILE(4, 1);
+        else return false;
+#undef MG_TILE
         lv.cur[0] ^= 1;
         fast_count(ws);
         return true;
