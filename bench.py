@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--engine-min-level", type=int, default=2)
     ap.add_argument("--cpu-sample-cycles", type=int, default=2)
     ap.add_argument("--generic-kernels", action="store_true", help="disable the specialised kernels")
+    ap.add_argument("--no-prefetch", action="store_true",
+                    help="e2e leg: upload the inputs synchronously instead of one evaluation ahead on a copy stream")
     ap.add_argument("--stages-only", action="store_true",
                     help="time the finest-level stage kernels alone and print their rooflines (ncu target)")
     ap.add_argument("--stage-reps", type=int, default=20)
@@ -177,7 +179,8 @@ def make_generator(args, device, resident):
     hi = args.max_level
     lo = hi - args.grammar_depth
     gen = B200ProgramGenerator(problem=problem, min_level=lo, max_level=hi, device=device,
-                               engine_min_level=args.engine_min_level, resident_inputs=resident)
+                               engine_min_level=args.engine_min_level, resident_inputs=resident,
+                               prefetch_inputs=not resident and not args.no_prefetch)
     gen.initialize_code_generation(lo, hi)
     if args.generic_kernels:
         gen._workspace.set_fast_kernels(False)
@@ -317,7 +320,9 @@ def run_b200(args):
         "evals_per_s": world * p * args.steps / (dev_ms * 1e-3),
         "cycles_per_step": cycles / args.steps, "converged_in_last_step_rank0": converged,
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d / args.steps,
-                "d2h_bytes_per_step": d2h / args.steps, "ms_per_step": max(dev2, wall2) / args.steps},
+                "d2h_bytes_per_step": d2h / args.steps, "ms_per_step": max(dev2, wall2) / args.steps,
+                "input_copy": "synchronous before each solve" if args.no_prefetch else
+                              "pinned host -> device staging on a copy stream, one evaluation ahead of the solve"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dominant, "achieved": stages[dominant]["achieved_gbs"], "peak": peak,
                      "unit": "GB/s", "frac": stages[dominant]["frac"], "traffic": captured_traffic(dominant), "peak_source": peak_src,
