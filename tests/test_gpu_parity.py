@@ -317,6 +317,42 @@ def test_fast_and_generic_kernels_agree_on_a_solve():
         assert np.array_equal(u_fast, h.sol[hi][0])
 
 
+ENGINE_VARIANTS = [
+    {},                                                             # defaults: cluster tail (2D), lean, deferred zero fill
+    {"MG_TAIL_CTAS": "1", "MG_TAIL_LEVEL": "6"},                    # single-CTA tail
+    {"MG_TAIL_CTAS": "8", "MG_TAIL_LEVEL": "7", "MG_TAIL_SOLO": "3"},
+    {"MG_TAIL_LEAN": "0"},                                          # full interpreter
+    {"MG_LAZY_ZERO": "0"},                                          # zero fills issued where they stand
+]
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_engine_configurations_are_bitwise_equivalent(dim, monkeypatch):
+    """Tail kernel shape (single CTA / cluster / lean / full) and deferred zero fills are scheduling
+    choices (read from the environment when a workspace is created): the converged solution and the
+    residual history must not change by a single bit."""
+    from evostencils_b200.generator import B200ProgramGenerator
+    problem, lo, hi = (problems.POISSON_2D, 3, 10) if dim == 2 else (problems.POISSON_3D, 2, 6)
+    grammar = Grammar(problem, lo, hi)
+    expression, _ = grammar.compile(v_cycle_string(hi - lo, 2, 1, 21 if dim == 2 else 23, "red_black"))
+    reference = None
+    for variant in ENGINE_VARIANTS:
+        for name in ("MG_TAIL_CTAS", "MG_TAIL_LEVEL", "MG_TAIL_SOLO", "MG_TAIL_LEAN", "MG_LAZY_ZERO"):
+            monkeypatch.delenv(name, raising=False)
+        for name, value in variant.items():
+            monkeypatch.setenv(name, value)
+        gen = B200ProgramGenerator(problem=problem, min_level=lo, max_level=hi, device=0)
+        gen.initialize_code_generation(lo, hi)
+        gen.generate_and_evaluate(expression, None, lo, hi, "", evaluation_samples=1)
+        got = (np.array(gen.last_residual_history), gen._workspace.download("sol", hi, 0))
+        gen.close()
+        if reference is None:
+            reference = got
+        else:
+            assert np.array_equal(got[0], reference[0]), variant
+            assert np.array_equal(got[1], reference[1]), variant
+
+
 @pytest.mark.parametrize("block", [(1, 2), (1, 3), (1, 4), (2, 1), (2, 2), (3, 1), (4, 1)])
 def test_fast_tile_smoother_bit_identical_to_generic(block):
     """Every block shape of the config-2 grammar (maximum_local_system_size = 4): the node-parallel
