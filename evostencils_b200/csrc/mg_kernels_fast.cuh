@@ -242,8 +242,9 @@ inline bool fast_norm(mg_workspace* ws, Level& lv) {
 template <typename T, int D, int F>
 inline bool fast_residual_restrict(mg_workspace* ws, Level& lf, Level& lc) {
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
-        if (!star_level_ok<D>(ws, lf, 4) || (lc.g.n - 1) % (2 * FAST_NT) != 0) return false;
         static const int tile_rc = tunable("MG_RESTRICT_RC", 3);     // 0: marching kernel
+        // the tile kernel clamps its columns itself: any level the 2-column kernels accept (>= 257^2)
+        if (!star_level_ok<D>(ws, lf, tile_rc > 0 ? 2 : 4) || (tile_rc == 0 && (lc.g.n - 1) % (2 * FAST_NT) != 0)) return false;
         if (tile_rc > 0) {
             const double* u = static_cast<const double*>(lf.sol[lf.cur[0]][0]);
             const double* f = static_cast<const double*>(lf.rhs[0]);
@@ -290,8 +291,8 @@ inline bool fast_prolong_add(mg_workspace* ws, Level& lf, Level& lc, const Field
         return true;
     }
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
-        if (ws->dtype != MG_F64 || (lf.g.n - 1) % (4 * FAST_NT) != 0) return false;
         static const int tile_rc = tunable("MG_PROLONG_RC", 4);      // 0: marching kernel
+        if (ws->dtype != MG_F64 || (lf.g.n - 1) % ((tile_rc > 0 ? 2 : 4) * FAST_NT) != 0) return false;
         if (tile_rc > 0) {
             const double* e = reinterpret_cast<const double*>(src.p[0]);
             double* u = static_cast<double*>(lf.sol[lf.cur[0]][0]);

@@ -37,7 +37,7 @@ def main():
             ws.run_cycles(cyc, 5)
             row[name + "_graph"] = round(ws.run_cycles(cyc, 50) / 50 * 1e3, 2)      # + 2 launches of the level-(top+1) norm
         out[f"top{top}"] = row
-    print(json.dumps({"us_per_subcycle": out, "tail_level": os.environ.get("MG_TAIL_LEVEL", "6")}))
+    print(json.dumps({"us_per_subcycle": out, "tail_level": os.environ.get("MG_TAIL_LEVEL", "default")}))
     ws.close()
 
 
