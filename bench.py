@@ -2,8 +2,9 @@
 """bench.py -- BASELINE.json configs[1]: fitness evaluation of an evolved-cycle population on
 2D Poisson 4096^2 (fp64), sharded over the GPUs of one node (one process per GPU).
 
-Step  = every rank evaluates its fixed shard of `--individuals-per-gpu` individuals of the stored
-        256-individual population (weak scaling) through B200ProgramGenerator.generate_and_evaluate.
+Step  = the first N x `--individuals-per-gpu` individuals of the stored 256-individual population
+        (weak scaling; 32 per GPU = the whole population on 8 GPUs) are evaluated once through
+        B200ProgramGenerator.generate_and_evaluate; ranks take individuals from a shared counter.
 value = fine-grid DoF updates per second = sum over individuals of (interior DoF x multigrid
         cycles executed) / step time, whole job, inputs resident in HBM.
 e2e   = same metric with the RHS and the initial guess copied from pinned host memory for every
@@ -36,7 +37,11 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--individuals-per-gpu", type=int, default=8)
+    ap.add_argument("--individuals-per-gpu", type=int, default=32,
+                    help="weak scaling: a step evaluates the first N x this many individuals (256 / 8 GPUs = 32)")
+    ap.add_argument("--schedule", default="dynamic", choices=["dynamic", "static"],
+                    help="dynamic: ranks take the next individual of the step from a shared counter "
+                         "(population.WorkQueue); static: the reference's i %% nprocs striding")
     ap.add_argument("--max-level", type=int, default=12)
     ap.add_argument("--grammar-depth", type=int, default=5)
     ap.add_argument("--engine-min-level", type=int, default=2)
@@ -209,11 +214,19 @@ def finest_stage_counts(program, hi):
     return counts
 
 
-def evaluate_shard(gen, grammar, shard, lo, hi, stage_counts=None):
-    """One step: evaluate every individual of the shard.  -> (cycles executed, results)."""
+def evaluate_shard(gen, grammar, jobs, lo, hi, stage_counts=None, schedule="dynamic"):
+    """One step: this rank's part of the step's individuals `jobs` (self-scheduled over the ranks
+    through population.WorkQueue, or strided i % world).  -> (cycles executed, results)."""
+    from evostencils_b200 import population
     cycles = 0
     results = []
-    for string in shard:
+    if schedule == "dynamic":
+        mine = population.WorkQueue(len(jobs))
+    else:
+        rank, world, _ = population._world()
+        mine = population.shard_indices(len(jobs), rank, world)
+    for k in mine:
+        string = jobs[k]
         expression, _ = grammar.compile(string)
         t, rho, n = gen.generate_and_evaluate(expression, None, lo, hi, "", evaluation_samples=1)
         c = max(0, len(gen.last_residual_history) - 1)
@@ -228,6 +241,7 @@ def evaluate_shard(gen, grammar, shard, lo, hi, stage_counts=None):
 def run_b200(args):
     import torch
     import torch.distributed as dist
+    from evostencils_b200 import lowering
     from evostencils_b200.grammar import Grammar
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -237,7 +251,7 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     population = load_population()
     p = args.individuals_per_gpu
-    shard = [population[(rank * p + i) % len(population)] for i in range(p)]
+    jobs = [population[i % len(population)] for i in range(world * p)]
     peak, peak_src = measured_peaks()
 
     def barrier():
@@ -248,10 +262,14 @@ def run_b200(args):
     def timed_phase(resident):
         gen, problem, lo, hi = make_generator(args, local, resident)
         grammar = Grammar(problem, lo, hi, maximum_local_system_size=4)
+        # longest-first by the static cost of one cycle (the number of cycles is not known beforehand)
+        cost = [lowering.estimate_cycle_bytes(lowering.lower(grammar.compile(s)[0], lo, hi).ops, problem.dimension)
+                for s in jobs]
+        ordered = [jobs[i] for i in sorted(range(len(jobs)), key=lambda i: (-cost[i], i))]
         us, fs = synthetic_inputs(problem, hi)
         gen.set_inputs(rhs=fs, u0=us)
         for _ in range(args.warmup):
-            evaluate_shard(gen, grammar, shard, lo, hi)
+            evaluate_shard(gen, grammar, ordered, lo, hi, schedule=args.schedule)
         ws = gen._workspace
         gen.h2d_bytes = gen.d2h_bytes = 0
         launches0 = ws.launch_count()
@@ -262,7 +280,7 @@ def run_b200(args):
         results = None
         counts = {}
         for _ in range(args.steps):
-            c, results = evaluate_shard(gen, grammar, shard, lo, hi, counts)
+            c, results = evaluate_shard(gen, grammar, ordered, lo, hi, counts, schedule=args.schedule)
             cycles += c
         ws.mark(1)
         ws.synchronize()
@@ -312,7 +330,7 @@ def run_b200(args):
         "config": {"workload": "BASELINE.json configs[1]: 2D Poisson 5-point 4096^2 fp64, fitness evaluation of "
                                "evolved-cycle individuals (grammar levels %d..%d, default V(2,1) RB-GS cycle + CG "
                                "below, engine levels %d..%d)" % (lo, hi, args.engine_min_level, hi),
-                   "individuals_per_gpu": p, "population": os.path.relpath(POPULATION, ROOT),
+                   "individuals_per_gpu": p, "individuals_per_step": world * p, "schedule": args.schedule, "population": os.path.relpath(POPULATION, ROOT),
                    "evaluation_samples": 1, "target_reduction": 1e-12, "max_iterations": 100,
                    "inputs": "u0=0, f~N(0,1) seed 1234 (SURVEY.md 8d)",
                    "l2_policy": "every field array is 134 MB > 126 MB L2; stage timings additionally flush L2",

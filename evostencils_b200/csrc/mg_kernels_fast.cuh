@@ -7,6 +7,7 @@
 
 #include "mg_fast2d.cuh"
 #include "mg_fast3d.cuh"
+#include "mg_rbgs3d.cuh"
 #include "mg_workspace.cuh"
 
 namespace mg {
@@ -144,6 +145,28 @@ inline dim3 launch_star3d(mg_workspace* ws, Level& lv, int nt, const double* u, 
     return grid;
 }
 
+// one-pass 3D RB-GS sweep (mg_rbgs3d.cuh): whole grids of at least 65^3 nodes
+inline bool launch_rbgs3d(mg_workspace* ws, Level& lv, const double* u, const double* f, double* out, double w) {
+    static const int enabled = tunable("MG_RBGS3D", 1), zc_env = tunable("MG_RBGS3D_ZCHUNK", 0);
+    if (!enabled || lv.g.z0 != 0 || lv.g.nz != lv.g.n || lv.g.n < 65) return false;
+    constexpr int RY = 8;
+    static bool opted_in[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !opted_in[dev]) {
+        if (cudaFuncSetAttribute(k_rbgs3d<RY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbgs3d_smem_bytes<RY>()) != cudaSuccess)
+            return false;
+        opted_in[dev] = true;
+    }
+    const int n = lv.g.n;
+    const int gx = (n + RB3_TW - 1) / RB3_TW, gy = (n + RY - 1) / RY;
+    int zchunk = zc_env >= 3 ? zc_env : 32;
+    while (zc_env < 3 && zchunk > 4 && gx * gy * ((n + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
+    launch_k(ws, k_rbgs3d<RY>, dim3(gx, gy, (n + zchunk - 1) / zchunk), 32 * (RY + 2), rbgs3d_smem_bytes<RY>(), lv.g, star3d(lv), u, f,
+             out, w, zchunk);
+    return true;
+}
+
 template <typename T, int D, int F>
 inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm, int c_begin, int c_end, bool zero_in) {
     // zero_in: the current solution is a pending zero fill (Level::zero_pending); true is returned only
@@ -152,6 +175,13 @@ inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm, int c_begin, 
         const int nt = star3d_nt(ws, lv);
         if (zero_in || !nt || !sm.point || sm.m != 1 || lv.g.nz < 3) return false;
         const double* rhs = static_cast<const double*>(lv.rhs[0]);
+        if (sm.colored && c_begin == 0 && c_end == 2 &&
+            launch_rbgs3d(ws, lv, static_cast<const double*>(lv.sol[lv.cur[0]][0]), rhs,
+                          static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]), sm.w00)) {
+            lv.cur[0] ^= 1;
+            fast_count(ws);
+            return true;
+        }
         for (int c = c_begin; c < c_end; ++c) {
             const double* src = static_cast<const double*>(lv.sol[lv.cur[0]][0]);
             double* dst = static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]);

@@ -447,3 +447,32 @@ def fuse(ops: Sequence[object]) -> List[object]:
         out.append(op)
         i += 1
     return out
+
+
+def estimate_cycle_bytes(ops: Sequence[object], dimension: int, bytes_per_value: int = 8) -> float:
+    """Algorithmic HBM bytes of one cycle of `ops` (every input field read once,
+    every output written once; interior nodes only).  Static information about an individual,
+    used to order a population longest-first before it is dealt to the ranks."""
+    total = 0.0
+    for op in fuse(ops):
+        fine_level = op.level
+        if isinstance(op, LocalSolve):
+            fields = 3.0                                       # u, f in, u out
+        elif op.kind in ("residual", "richardson"):
+            fields = 3.0
+        elif op.kind in ("residual_restrict", "restrict"):
+            fields, fine_level = 2.0 + 0.5 ** dimension, op.level + 1
+        elif op.kind in ("prolong_add", "prolong"):
+            fields = 2.0 + 0.5 ** dimension
+        elif op.kind in ("zero",):
+            fields = 1.0
+        elif op.kind == "copy":
+            fields = 2.0
+        elif op.kind == "cgs":
+            if op.inner:
+                total += estimate_cycle_bytes(op.inner, dimension, bytes_per_value)
+            continue
+        else:
+            fields = 3.0
+        total += fields * bytes_per_value * float((2 ** fine_level - 1) ** dimension)
+    return total

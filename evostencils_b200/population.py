@@ -48,6 +48,46 @@ def _world(group=None):
     return 0, 1, None
 
 
+class WorkQueue:
+    """Self-scheduling of one batch of jobs over the ranks: a rank takes the next job index from an
+    atomic counter kept in the process group's key-value store (`Store.add`, a TCP round trip of
+    ~0.1 ms to rank 0 against tens of ms per evaluation).  The reference deals `i % nprocs`
+    (program.py:534-535), which leaves ranks idle when evaluation times differ (individuals that
+    converge in 15 cycles next to ones that run all 100); the set of individuals, the result per
+    individual and the exchange are unchanged, only *which* rank evaluates an individual.
+
+    Every rank must create its queues in the same order (the n-th queue of every rank shares a key)."""
+
+    _serial = 0
+
+    def __init__(self, n_jobs: int, group=None, store=None):
+        rank, world, dist = _world(group)
+        self.n_jobs = n_jobs
+        self.world = world
+        self._next = 0
+        self._store = None
+        if world > 1:
+            if store is None:
+                from torch.distributed import distributed_c10d
+                store = distributed_c10d._get_default_store()
+            WorkQueue._serial += 1
+            self._store = store
+            self._key = "evostencils_b200/workqueue/%d" % WorkQueue._serial
+
+    def __iter__(self):
+        return self
+
+    def __next__(self) -> int:
+        if self._store is None:
+            k = self._next
+            self._next += 1
+        else:
+            k = self._store.add(self._key, 1) - 1
+        if k >= self.n_jobs:
+            raise StopIteration
+        return k
+
+
 def gather_results(local: dict, n_items: int, group=None, device=None) -> List[Result]:
     """Combine `{index: (t, rho, n)}` of every rank into the full list on every rank.
 
@@ -76,12 +116,14 @@ def gather_results(local: dict, n_items: int, group=None, device=None) -> List[R
 
 
 def evaluate_population(evaluate: Callable[[str], Result], strings: Sequence[str], group=None, device=None,
-                        costs: Optional[Sequence[float]] = None) -> List[Result]:
+                        costs: Optional[Sequence[float]] = None, schedule: str = "static") -> List[Result]:
     """Evaluate every individual once across the ranks of `group`; every rank gets all results.
 
     `evaluate(grammar_string) -> (time_ms, rho, n)` runs on this rank's GPU.  With `costs`
     (e.g. op-list byte counts) the unique individuals are dealt longest-first so that the ranks
-    finish together; without, plain `i % world` striding."""
+    finish together; without, plain `i % world` striding.  `schedule="dynamic"`
+    replaces the striding by a `WorkQueue`: ranks take the next individual of the (cost-ordered)
+    list when they finish one."""
     rank, world, _ = _world(group)
     unique, back = deduplicate(strings)
     order = list(range(len(unique)))
@@ -92,8 +134,13 @@ def evaluate_population(evaluate: Callable[[str], Result], strings: Sequence[str
         for i, b in enumerate(back):
             first.setdefault(b, costs[i])
         order.sort(key=lambda u: (-first[u], u))
-    mine = [order[k] for k in shard_indices(len(order), rank, world)]
-    local = {u: evaluate(unique[u]) for u in mine}
+    if schedule == "dynamic":
+        local = {order[k]: evaluate(unique[order[k]]) for k in WorkQueue(len(order), group)}
+    elif schedule == "static":
+        mine = [order[k] for k in shard_indices(len(order), rank, world)]
+        local = {u: evaluate(unique[u]) for u in mine}
+    else:
+        raise ValueError("schedule must be 'static' or 'dynamic'")
     results = gather_results(local, len(unique), group, device)
     return [results[b] for b in back]
 
@@ -112,7 +159,8 @@ def make_evaluator(generator, grammar, min_level: int, max_level: int, evaluatio
     return evaluate
 
 
-def batched_map(generator, grammar, min_level, max_level, evaluation_samples=1, group=None, infinity=1e100):
+def batched_map(generator, grammar, min_level, max_level, evaluation_samples=1, group=None, infinity=1e100,
+                schedule="static"):
     """A `toolbox.map` replacement (the reference's extension point, program.py:491, 577):
     `toolbox.register("map", batched_map(...))` makes one generation's evaluations run sharded.
     The mapped function is ignored for individuals given as grammar strings / PrimitiveTrees:
@@ -123,7 +171,7 @@ def batched_map(generator, grammar, min_level, max_level, evaluation_samples=1, 
     def _map(_function, individuals):
         strings = [str(ind) for ind in individuals]
         out = []
-        for t, rho, n in evaluate_population(evaluator, strings, group):
+        for t, rho, n in evaluate_population(evaluator, strings, group, schedule=schedule):
             if n >= infinity:                            # program.py:447-448
                 out.append((rho, infinity))
             else:

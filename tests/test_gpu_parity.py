@@ -453,3 +453,30 @@ def test_fast_3d_stages_bit_identical(hi):
     run_both(ws, h, [lowering.Op("prolong_add", hi, omega=0.55, src="sol", dst="sol")], problem)
     compare(ws, h, "sol", hi, True, "fast 3D prolong_add")
     ws.close()
+
+
+@pytest.mark.parametrize("omega", [1.15, 0.8])
+def test_one_pass_3d_rbgs_bit_identical_to_generic_at_257(omega):
+    """k_rbgs3d (TMA-staged planes, red half-sweep in shared memory) at 257^3 -- 5 x 33 x 9 tiles with
+    clipped tiles on every side and random Dirichlet values -- against the generic colour passes."""
+    from evostencils_b200.engine import Workspace
+    problem, hi = problems.POISSON_3D, 8
+    n = 2 ** hi + 1
+    rng = np.random.default_rng(5)
+    u0, f0 = rng.standard_normal((n, n, n)), rng.standard_normal((n, n, n))
+    stmts = smoother_statements(problem, hi, "collective", ir.RedBlack, omega=omega)
+    out = []
+    for fast in (True, False):
+        ws = Workspace(3, hi - 1, hi, 1, "f64", 0)
+        for level in (hi - 1, hi):
+            ws.set_operator(level, lowering.operator_table(problem.system_operator(level, 0)))
+        ws.set_fast_kernels(fast)
+        ws.upload("sol", hi, 0, u0)
+        ws.upload("rhs", hi, 0, f0)
+        for sweep in range(2):
+            ws.exec_ops(stmts)
+        out.append(ws.download("sol", hi, 0))
+        ws.close()
+    bad = np.argwhere(out[0] != out[1])
+    assert bad.size == 0, f"{len(bad)} mismatching nodes, first {bad[:4].tolist()}"
+    assert not np.array_equal(out[0], u0)

@@ -48,7 +48,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, with_costs, queue):
+def _worker(rank, world, port, with_costs, queue, schedule="static"):
     sys.path.insert(0, REPO)
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -58,10 +58,15 @@ def _worker(rank, world, port, with_costs, queue):
 
     def evaluate(s):
         calls.append(s)
+        if schedule == "dynamic" and rank == 0:
+            import time
+            time.sleep(0.05)                  # a slow rank: the other one must take over its work
         return fake_evaluate(s)
 
     costs = [float((i * 7) % 5) for i in range(len(STRINGS))] if with_costs else None
-    out = population.evaluate_population(evaluate, STRINGS, costs=costs)
+    out = population.evaluate_population(evaluate, STRINGS, costs=costs, schedule=schedule)
+    if schedule == "dynamic":                 # a second batch uses a fresh counter
+        assert population.evaluate_population(fake_evaluate, STRINGS[:5], schedule=schedule) == out[:5]
     queue.put((rank, out, calls))
     dist.barrier()
     dist.destroy_process_group()
@@ -88,6 +93,37 @@ def test_world_size_2_gloo(with_costs):
     assert sorted(all_calls) == sorted(set(STRINGS))      # every unique individual exactly once
     sizes = sorted(len(c) for _, _, c in got)
     assert sizes[1] - sizes[0] <= 1                       # balanced
+
+
+def test_work_queue_single_process():
+    assert list(population.WorkQueue(5)) == [0, 1, 2, 3, 4]
+    assert list(population.WorkQueue(0)) == []
+    got = population.evaluate_population(fake_evaluate, STRINGS, schedule="dynamic")
+    assert got == [fake_evaluate(s) for s in STRINGS]
+    with pytest.raises(ValueError):
+        population.evaluate_population(fake_evaluate, STRINGS, schedule="guided")
+
+
+def test_world_size_2_gloo_dynamic_schedule():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    queue = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, True, queue, "dynamic")) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = [queue.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    want = [fake_evaluate(s) for s in STRINGS]
+    all_calls = []
+    for rank, out, calls in got:
+        assert out == want, rank
+        all_calls += calls
+    assert sorted(all_calls) == sorted(set(STRINGS))      # every unique individual exactly once
+    by_rank = {rank: len(calls) for rank, _, calls in got}
+    assert by_rank[1] > by_rank[0]                        # the fast rank took more of the queue
 
 
 def test_batched_map_fitness_conventions():
