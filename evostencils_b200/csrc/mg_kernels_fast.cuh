@@ -4,6 +4,9 @@
 // FMA contraction), which tests/test_gpu_parity.py checks against the oracle on both paths.
 #pragma once
 #include <cstdlib>
+#include <map>
+#include <mutex>
+#include <tuple>
 
 #include "mg_fast2d.cuh"
 #include "mg_fast3d.cuh"
@@ -145,26 +148,81 @@ inline dim3 launch_star3d(mg_workspace* ws, Level& lv, int nt, const double* u, 
     return grid;
 }
 
-// one-pass 3D RB-GS sweep (mg_rbgs3d.cuh): whole grids of at least 65^3 nodes
-inline bool launch_rbgs3d(mg_workspace* ws, Level& lv, const double* u, const double* f, double* out, double w) {
-    static const int enabled = tunable("MG_RBGS3D", 1), zc_env = tunable("MG_RBGS3D_ZCHUNK", 0);
-    if (!enabled || lv.g.z0 != 0 || lv.g.nz != lv.g.n || lv.g.n < 65) return false;
-    constexpr int RY = 8;
+// ---- TMA tensor maps of whole 3D field arrays (x fastest; box = 64 columns x `rows` rows x 1 plane) ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// descriptors are cached by (array, nodes per dimension, box rows): the sweeps of a solve reuse three of them
+inline const CUtensorMap* plane_tensor_map(const double* base, const Geom& g, int rows) {
+    static std::mutex lock;
+    static std::map<std::tuple<const void*, int, int>, CUtensorMap> cache;
+    std::lock_guard<std::mutex> guard(lock);
+    const auto key = std::make_tuple(static_cast<const void*>(base), g.n, rows);
+    auto it = cache.find(key);
+    if (it != cache.end()) return &it->second;
+    EncodeTiledFn encode = encode_tiled_fn();
+    if (!encode) return nullptr;
+    CUtensorMap tm;
+    const cuuint64_t dims[3] = {(cuuint64_t)g.n, (cuuint64_t)g.n, (cuuint64_t)g.nz};
+    const cuuint64_t strides[2] = {(cuuint64_t)g.pitch * sizeof(double), (cuuint64_t)g.plane * sizeof(double)};
+    const cuuint32_t box[3] = {(cuuint32_t)RB3_W, (cuuint32_t)rows, 1u};
+    const cuuint32_t elem[3] = {1u, 1u, 1u};
+    if (encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(base), dims, strides, box, elem,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return nullptr;
+    return &cache.emplace(key, tm).first->second;
+}
+
+// one-pass 3D RB-GS sweep (mg_rbgs3d.cuh): whole grids
+template <int RY, int NS, int NF, int RW>
+inline bool launch_rbgs3d_cfg(mg_workspace* ws, Level& lv, const double* u, const double* f, double* out, double w) {
+    static const int zc_env = tunable("MG_RBGS3D_ZCHUNK", 0);
     static bool opted_in[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !opted_in[dev]) {
-        if (cudaFuncSetAttribute(k_rbgs3d<RY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rbgs3d_smem_bytes<RY>()) != cudaSuccess)
+        if (cudaFuncSetAttribute(k_rbgs3d<RY, NS, NF, RW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)rbgs3d_smem_bytes<RY, NS, NF>()) != cudaSuccess)
             return false;
         opted_in[dev] = true;
     }
+    const CUtensorMap* tm_u = plane_tensor_map(u, lv.g, RY + 4);
+    const CUtensorMap* tm_f = plane_tensor_map(f, lv.g, RY + 2);
+    if (!tm_u || !tm_f) return false;
     const int n = lv.g.n;
     const int gx = (n + RB3_TW - 1) / RB3_TW, gy = (n + RY - 1) / RY;
-    int zchunk = zc_env >= 3 ? zc_env : 32;
+    int zchunk = zc_env >= 3 ? zc_env : 64;
     while (zc_env < 3 && zchunk > 4 && gx * gy * ((n + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
-    launch_k(ws, k_rbgs3d<RY>, dim3(gx, gy, (n + zchunk - 1) / zchunk), 32 * (RY + 2), rbgs3d_smem_bytes<RY>(), lv.g, star3d(lv), u, f,
-             out, w, zchunk);
+    launch_k(ws, k_rbgs3d<RY, NS, NF, RW>, dim3(gx, gy, (n + zchunk - 1) / zchunk), 32 * (RY + 2) / RW,
+             rbgs3d_smem_bytes<RY, NS, NF>(), lv.g, star3d(lv), *tm_u, *tm_f, out, w, zchunk);
     return true;
+}
+
+inline bool launch_rbgs3d(mg_workspace* ws, Level& lv, const double* u, const double* f, double* out, double w) {
+    static const int enabled = tunable("MG_RBGS3D", 1), cfg = tunable("MG_RBGS3D_CFG", 0);
+    const int min_n = tunable("MG_RBGS3D_MIN_N", 257);      // not cached: the tests lower it to 65
+    if (!enabled || lv.g.z0 != 0 || lv.g.nz != lv.g.n || lv.g.n < 65 || lv.g.n < min_n) return false;
+    switch (cfg) {
+        case 1: return launch_rbgs3d_cfg<8, 6, 5, 2>(ws, lv, u, f, out, w);
+        case 2: return launch_rbgs3d_cfg<16, 6, 5, 1>(ws, lv, u, f, out, w);
+        case 3: return launch_rbgs3d_cfg<16, 6, 5, 2>(ws, lv, u, f, out, w);
+        case 4: return launch_rbgs3d_cfg<8, 5, 4, 1>(ws, lv, u, f, out, w);
+        default: return launch_rbgs3d_cfg<8, 6, 5, 1>(ws, lv, u, f, out, w);
+    }
 }
 
 template <typename T, int D, int F>

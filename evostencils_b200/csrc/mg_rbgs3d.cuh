@@ -22,6 +22,8 @@
 //     recomputed by this CTA from the same inputs as their owner uses: bit-identical to two
 //     sequential colour passes (operand order of star3_at, separate multiply and add).
 #pragma once
+#include <cuda.h>
+
 #include "mg_fast3d.cuh"
 
 namespace mg {
@@ -33,10 +35,12 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"(src), "r"(bytes), "r"(bar)
-                 : "memory");
+// one box of a 3D tensor map (x fastest) -> shared memory; out-of-range coordinates are filled with zeros
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* tm, int x, int y, int z, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+        "l"(tm), "r"(x), "r"(y), "r"(z), "r"(bar)
+        : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok;
@@ -52,26 +56,49 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 
 constexpr int RB3_TW = 60;     // output columns per tile
 constexpr int RB3_W = 64;      // staged columns per row (xb-2 .. xb+61): 512 B, one bulk copy
-constexpr int RB3_NS = 6;      // ring of u planes
-constexpr int RB3_NF = 5;      // ring of f planes
 
-template <int RY>
+template <int RY, int RB3_NS, int RB3_NF>      // RB3_NS / RB3_NF: ring sizes of u / f planes
 constexpr size_t rbgs3d_smem_bytes() {
-    return (size_t)(RB3_NS * (RY + 4) + RB3_NF * (RY + 2)) * RB3_W * sizeof(double) + 16 * sizeof(unsigned long long);
+    return (size_t)(RB3_NS * (RY + 4) + RB3_NF * (RY + 2)) * RB3_W * sizeof(double) + 16 * sizeof(unsigned long long) + 128;
+}
+
+// u + w (f - A u) at component C of a lane's column pair c2; o = element offset of the pair in a ring
+// slot (um / uq / up: the staged planes below, at and above the node; fq: the right-hand side, whose tile
+// starts one row later).  The parity of a row is warp-uniform, so the two components are two code paths:
+// one shuffle each, no selects.
+template <int C>
+__device__ __forceinline__ double rb3_relax(const Star3D& st, double w, const double* um, const double* uq, const double* up,
+                                            const double* fq, int o, const double2 c2) {
+    double cen, wv, ev;
+    if (C == 0) {
+        cen = c2.x; ev = c2.y;
+        wv = __shfl_up_sync(0xffffffffu, c2.y, 1);
+    } else {
+        cen = c2.y; wv = c2.x;
+        ev = __shfl_down_sync(0xffffffffu, c2.x, 1);
+    }
+    const double sv = uq[o + C - RB3_W], nv = uq[o + C + RB3_W];
+    const double zm = um[o + C], zp = up[o + C];
+    const double fv = fq[o + C - RB3_W];
+    const double r = fv - star3_at(st, zm, sv, wv, cen, ev, nv, zp);
+    return cen + w * r;
 }
 
 // out = RB-GS sweep of u (red = (x+y+z) even first, then black), whole grid (g.nz == g.n, g.z0 == 0).
-// grid = (ceil(n / 60), ceil(n / RY), ceil(n / zchunk)), block = 32 * (RY + 2).
-template <int RY>
-__global__ void __launch_bounds__(32 * (RY + 2), 3) k_rbgs3d(Geom g, Star3D st, const double* __restrict__ u,
-                                                          const double* __restrict__ f, double* __restrict__ out, double w,
-                                                          int zchunk) {
-    constexpr int UR = RY + 4, FR = RY + 2;
+// grid = (ceil(n / 60), ceil(n / RY), ceil(n / zchunk)), block = 32 * (RY + 2) / RW (RW tile rows per warp).
+template <int RY, int RB3_NS, int RB3_NF, int RW>
+__global__ void __launch_bounds__(32 * (RY + 2) / RW) k_rbgs3d(Geom g, Star3D st, const __grid_constant__ CUtensorMap tm_u,
+                                                               const __grid_constant__ CUtensorMap tm_f,
+                                                               double* __restrict__ out, double w, int zchunk) {
+    constexpr int UR = RY + 4, FR = RY + 2, NW = (RY + 2) / RW;
+    static_assert((RY + 2) % RW == 0 && RY % RW == 0 && RY % 2 == 0, "rows per warp must divide the red and the black rows");
     constexpr uint32_t U_BYTES = UR * RB3_W * 8, F_BYTES = FR * RB3_W * 8;
+    constexpr int U_SLOT = UR * RB3_W, F_SLOT = FR * RB3_W;                  // doubles per ring slot
     extern __shared__ __align__(128) unsigned char rb3_smem[];
-    double* su = reinterpret_cast<double*>(rb3_smem);                       // [NS][UR][64]
-    double* sf = su + RB3_NS * UR * RB3_W;                                  // [NF][FR][64]
-    unsigned long long* bars = reinterpret_cast<unsigned long long*>(sf + RB3_NF * FR * RB3_W);   // [NS] u, [NF] f
+    // TMA destinations must be 128-byte aligned
+    double* su = reinterpret_cast<double*>(rb3_smem + ((128u - (smem_u32(rb3_smem) & 127u)) & 127u));   // [NS][UR][64]
+    double* sf = su + RB3_NS * U_SLOT;                                      // [NF][FR][64]
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(sf + RB3_NF * F_SLOT);   // [NS] u, [NF] f
     pdl_sync();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n = g.n;
@@ -81,104 +108,134 @@ __global__ void __launch_bounds__(32 * (RY + 2), 3) k_rbgs3d(Geom g, Star3D st, 
     const int p0 = zb - 2, fp0 = zb - 1;                                    // first staged plane of u / f
     const uint32_t su_a = smem_u32(su), sf_a = smem_u32(sf), bar_a = smem_u32(bars);
 
-    // stage plane p of u (rows yb-2 .. yb+RY+1) / of f (rows yb-1 .. yb+RY); plane and row indices are
-    // clamped into the grid (clamped copies are only ever read for nodes that are not updated)
-    auto stage_u = [&](int p) {
-        const int slot = (p - p0) % RB3_NS;
-        const uint32_t bar = bar_a + 8 * slot;
-        if (lane == 0) mbar_arrive_expect_tx(bar, U_BYTES);
-        __syncwarp();
-        if (lane < UR) {
-            const int y = imin(imax(yb - 2 + lane, 0), n - 1);
-            bulk_g2s(su_a + (uint32_t)((slot * UR + lane) * RB3_W * 8),
-                     u + (long long)imin(imax(p, 0), n - 1) * plane + (long long)y * pitch + (xb - 2), RB3_W * 8, bar);
+    // stage plane p of u (rows yb-2 .. yb+RY+1, columns xb-2 .. xb+61) into ring slot `slot` / of f (rows
+    // yb-1 .. yb+RY): one TMA box each; rows, columns and planes outside the grid arrive as zeros and are
+    // only read for nodes that are not updated
+    auto stage_u = [&](int p, int slot) {
+        if (lane == 0) {
+            const uint32_t bar = bar_a + 8 * slot;
+            mbar_arrive_expect_tx(bar, U_BYTES);
+            tma_load_3d(su_a + (uint32_t)(slot * U_SLOT * 8), &tm_u, xb - 2, yb - 2, p, bar);
         }
     };
-    auto stage_f = [&](int p) {
-        const int slot = (p - fp0) % RB3_NF;
-        const uint32_t bar = bar_a + 8 * (RB3_NS + slot);
-        if (lane == 0) mbar_arrive_expect_tx(bar, F_BYTES);
-        __syncwarp();
-        if (lane < FR) {
-            const int y = imin(imax(yb - 1 + lane, 0), n - 1);
-            bulk_g2s(sf_a + (uint32_t)((slot * FR + lane) * RB3_W * 8),
-                     f + (long long)imin(imax(p, 0), n - 1) * plane + (long long)y * pitch + (xb - 2), RB3_W * 8, bar);
+    auto stage_f = [&](int p, int slot) {
+        if (lane == 0) {
+            const uint32_t bar = bar_a + 8 * (RB3_NS + slot);
+            mbar_arrive_expect_tx(bar, F_BYTES);
+            tma_load_3d(sf_a + (uint32_t)(slot * F_SLOT * 8), &tm_f, xb - 2, yb - 1, p, bar);
         }
     };
-    auto wait_u = [&](int p) { mbar_wait(bar_a + 8 * ((p - p0) % RB3_NS), ((p - p0) / RB3_NS) & 1); };
-    auto wait_f = [&](int p) { mbar_wait(bar_a + 8 * (RB3_NS + (p - fp0) % RB3_NF), ((p - fp0) / RB3_NF) & 1); };
-    auto uslot = [&](int p) { return su + ((p - p0) % RB3_NS) * (UR * RB3_W); };
-    auto fslot = [&](int p) { return sf + ((p - fp0) % RB3_NF) * (FR * RB3_W); };
+    auto back = [](int slot, int k, int ring) { const int v = slot - k; return v < 0 ? v + ring : v; };
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < RB3_NS + RB3_NF; ++i) mbar_init(bar_a + 8 * i, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    if (warp == RY + 1) {
+    if (warp == NW - 1) {
         for (int i = 0; i < RB3_NS; ++i)
-            if (p0 + i <= ze + 1) stage_u(p0 + i);
+            if (p0 + i <= ze + 1) stage_u(p0 + i, i);
         for (int i = 0; i < RB3_NF; ++i)
-            if (fp0 + i <= ze) stage_f(fp0 + i);
+            if (fp0 + i <= ze) stage_f(fp0 + i, i);
     }
-    wait_u(p0);
-    wait_u(p0 + 1);
+    mbar_wait(bar_a, 0);            // planes p0 and p0+1 of u
+    mbar_wait(bar_a + 8, 0);
 
-    // u + w (f - A u) at component c of this lane's pair in tile row `lr` of a plane (um / uq / up: the
-    // staged planes below, at and above it; fq: its right-hand side)
-    auto relax = [&](const double* um, const double* uq, const double* up, const double* fq, int lr, int c,
-                     const double2 c2) -> double {
-        const double left = __shfl_up_sync(0xffffffffu, c2.y, 1), right = __shfl_down_sync(0xffffffffu, c2.x, 1);
-        const double cen = c ? c2.y : c2.x;
-        const double wv = c ? c2.x : left, ev = c ? right : c2.y;
-        const int o = lr * RB3_W + 2 * lane + c;
-        const double sv = uq[o - RB3_W], nv = uq[o + RB3_W];
-        const double zm = um[o], zp = up[o];
-        const double fv = fq[o - RB3_W];
-        const double r = fv - star3_at(st, zm, sv, wv, cen, ev, nv, zp);
-        return cen + w * r;
-    };
-
-    for (int s = zb - 1; s <= ze; ++s) {
-        wait_u(s + 1);
-        wait_f(s);
-        // ---- red(s): tile rows 1 .. RY+2 (y = yb-1 .. yb+RY), one warp each ----
-        if (s >= 1 && s <= n - 2) {
-            const int lr = warp + 1, y = yb - 2 + lr;
-            const int c = (y + s) & 1;                                       // xb is even: red = (col + y + s) even
-            double* us = uslot(s);
-            double2* row = reinterpret_cast<double2*>(us + lr * RB3_W) + lane;
-            const double2 c2 = *row;
-            const double v = relax(uslot(s - 1), us, uslot(s + 1), fslot(s), lr, c, c2);
-            const int x = xb - 2 + 2 * lane + c;
-            if (y >= 1 && y <= n - 2 && x >= imax(1, xb - 1) && x <= imin(n - 2, xb + RB3_TW))
-                reinterpret_cast<double*>(row)[c] = v;
+    // ---- per-thread constants of the march ----
+    const int x0 = xb - 2 + 2 * lane;                                       // first column of the lane's pair
+    const int o_red = (warp * RW + 1) * RB3_W + 2 * lane;                    // pair of the first red row in a slot
+    const int o_blk = o_red + RB3_W;                                         // ... of the first black row
+    // bit 2i+c: the red update of component c in red row i is kept (interior node inside the red region);
+    // bit 8+2i+c: component c of black row i is an interior node (in x and y)
+    unsigned ok = 0;
+#pragma unroll
+    for (int i = 0; i < RW; ++i)
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int x = x0 + c, yr = yb - 1 + warp * RW + i, yk = yr + 1;
+            if (yr >= 1 && yr <= n - 2 && x >= imax(1, xb - 1) && x <= imin(n - 2, xb + RB3_TW)) ok |= 1u << (2 * i + c);
+            if (yk >= 1 && yk <= n - 2 && x >= 1 && x <= n - 2) ok |= 1u << (8 + 2 * i + c);
         }
-        fence_proxy_async();
+    // store of black row i: bit 16+i a whole pair, bit 20+i only its first column (x0 == n-1)
+    const int y_blk = yb + warp * RW;
+#pragma unroll
+    for (int i = 0; i < RW; ++i)
+        if (lane >= 1 && lane <= RB3_TW / 2 && y_blk + i <= n - 1) {
+            if (x0 + 1 <= n - 1) ok |= 1u << (16 + i);
+            else if (x0 <= n - 1) ok |= 1u << (20 + i);
+        }
+    const bool black_warp = warp * RW < RY;
+    const int par_red = (yb - 1 + warp * RW) & 1;                            // + s: component of the red node in red row 0
+    double* optr = out + (long long)(zb - 2) * plane + (long long)y_blk * pitch + x0;   // plane s-1 at s = zb-1
+
+    // ring state of step s = zb-1: element offsets of the slots of planes s-2, s-1, s, s+1 of u and of
+    // planes s-1, s of f; barrier address and phase parity of plane s+1 of u and of plane s of f
+    int e_m2 = 0, e_m = 0, e_s = U_SLOT, e_p = 2 * U_SLOT, e_f1 = 0, e_f = 0;
+    uint32_t b_u = bar_a + 16, b_f = bar_a + 8 * RB3_NS;
+    uint32_t par_u = 0, par_f = 0;
+    for (int s = zb - 1; s <= ze; ++s) {
+        mbar_wait(b_u, par_u);
+        mbar_wait(b_f, par_f);
+        double* const us = su + e_s;
+        const double* const um = su + e_m;
+        const double* const up = su + e_p;
+        // ---- red(s): tile rows 1 .. RY+2 (y = yb-1 .. yb+RY) ----
+        if (s >= 1 && s <= n - 2) {
+            const double* const fs = sf + e_f;
+            const int c0 = (par_red + s) & 1;
+#pragma unroll
+            for (int i = 0; i < RW; ++i) {
+                const int o = o_red + i * RB3_W;
+                const double2 c2 = *reinterpret_cast<const double2*>(us + o);
+                if ((c0 ^ (i & 1)) == 0) {
+                    const double v = rb3_relax<0>(st, w, um, us, up, fs, o, c2);
+                    if (ok & (1u << (2 * i))) us[o] = v;
+                } else {
+                    const double v = rb3_relax<1>(st, w, um, us, up, fs, o, c2);
+                    if (ok & (1u << (2 * i + 1))) us[o + 1] = v;
+                }
+            }
+        }
         __syncthreads();
-        // planes <= s-3 of u and <= s-2 of f are dead now: refill their slots
-        if (warp == RY + 1) {
-            if (s - 3 >= p0 && s - 3 + RB3_NS <= ze + 1) stage_u(s - 3 + RB3_NS);
-            if (s - 2 >= fp0 && s - 2 + RB3_NF <= ze) stage_f(s - 2 + RB3_NF);
+        if (warp == NW - 1) {
+            // planes <= s-3 of u and <= s-2 of f are dead now: refill their slots (the proxy fence orders
+            // the red stores other warps made into them, visible here through the barrier, before the
+            // asynchronous writes)
+            fence_proxy_async();
+            if (s - 3 >= p0 && s - 3 + RB3_NS <= ze + 1) stage_u(s - 3 + RB3_NS, back(e_m2 / U_SLOT, 1, RB3_NS));
+            if (s - 2 >= fp0 && s - 2 + RB3_NF <= ze) stage_f(s - 2 + RB3_NF, back(e_f1 / F_SLOT, 1, RB3_NF));
         }
         // ---- black(s-1) + store of the finished plane: tile rows 2 .. RY+1 (y = yb .. yb+RY-1) ----
         const int q = s - 1;
-        if (q >= zb && q < ze && warp < RY) {
-            const int lr = warp + 2, y = yb + warp;
-            const int c = (y + q + 1) & 1;
-            const double* uq = uslot(q);
-            double2 c2 = *(reinterpret_cast<const double2*>(uq + lr * RB3_W) + lane);
-            const double v = relax(uslot(q - 1), uq, uslot(q + 1), fslot(q), lr, c, c2);
-            const int x0 = xb - 2 + 2 * lane, x = x0 + c;
-            if (q >= 1 && q <= n - 2 && y >= 1 && y <= n - 2 && x >= 1 && x <= n - 2) {
-                if (c) c2.y = v; else c2.x = v;
-            }
-            if (lane >= 1 && lane <= RB3_TW / 2 && y <= n - 1) {
-                double* o = out + (long long)q * plane + (long long)y * pitch + x0;
-                if (x0 + 1 <= n - 1) st2(o, c2);
-                else if (x0 <= n - 1) *o = c2.x;
+        if (q >= zb && q < ze && black_warp) {
+            const double* const uqm = su + e_m2;
+            const double* const fq = sf + e_f1;
+            const bool q_in = q >= 1 && q <= n - 2;
+            const int c0 = (par_red + s + 1) & 1;       // black row i lies one row above red row i, in plane s-1: its
+                                                        // black node has the other component
+#pragma unroll
+            for (int i = 0; i < RW; ++i) {
+                const int o = o_blk + i * RB3_W;
+                double2 c2 = *reinterpret_cast<const double2*>(um + o);
+                if ((c0 ^ (i & 1)) == 0) {
+                    const double v = rb3_relax<0>(st, w, uqm, um, us, fq, o, c2);
+                    if (q_in && (ok & (1u << (8 + 2 * i)))) c2.x = v;
+                } else {
+                    const double v = rb3_relax<1>(st, w, uqm, um, us, fq, o, c2);
+                    if (q_in && (ok & (1u << (9 + 2 * i)))) c2.y = v;
+                }
+                double* o_g = optr + i * pitch;
+                if (ok & (1u << (16 + i))) st2(o_g, c2);
+                else if (ok & (1u << (20 + i))) *o_g = c2.x;
             }
         }
+        optr += plane;
+        e_m2 = e_m; e_m = e_s; e_s = e_p;
+        e_p += U_SLOT; b_u += 8;
+        if (e_p == RB3_NS * U_SLOT) { e_p = 0; b_u = bar_a; par_u ^= 1; }
+        e_f1 = e_f;
+        e_f += F_SLOT; b_f += 8;
+        if (e_f == RB3_NF * F_SLOT) { e_f = 0; b_f = bar_a + 8 * RB3_NS; par_f ^= 1; }
     }
 }
 

@@ -431,10 +431,12 @@ def test_helmholtz_reference_wave_number_converges():
     gen.close()
 
 
-@pytest.mark.parametrize("hi", [6, 7])
-def test_fast_3d_stages_bit_identical(hi):
-    """2.5-D blocked 7-point kernels (levels >= 6 of 3D Poisson) against the oracle and the generic kernels."""
+@pytest.mark.parametrize("hi,one_pass", [(6, False), (7, False), (6, True), (7, True)])
+def test_fast_3d_stages_bit_identical(hi, one_pass, monkeypatch):
+    """2.5-D blocked 7-point kernels (levels >= 6 of 3D Poisson) against the oracle and the generic kernels;
+    `one_pass`: RB-GS through k_rbgs3d (by default only from 257^3 up) instead of two colour passes."""
     from oracle import driver, mg_oracle
+    monkeypatch.setenv("MG_RBGS3D_MIN_N", "65" if one_pass else "100000")
     problem, lo = problems.POISSON_3D, hi - 1
     ws, h = make_pair(problem, lo, hi, seed=13)
     run_both(ws, h, [lowering.Op("residual", hi, dst="res")], problem)
