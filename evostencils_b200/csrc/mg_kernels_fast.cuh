@@ -188,14 +188,14 @@ inline const CUtensorMap* plane_tensor_map(const double* base, const Geom& g, in
 }
 
 // one-pass 3D RB-GS sweep (mg_rbgs3d.cuh): whole grids
-template <int RY, int NS, int NF, int RW>
+template <int RY, int NS, int NF>
 inline bool launch_rbgs3d_cfg(mg_workspace* ws, Level& lv, const double* u, const double* f, double* out, double w) {
-    static const int zc_env = tunable("MG_RBGS3D_ZCHUNK", 0);
+    static const int zc_env = tunable("MG_RBGS3D_ZCHUNK", 0), pf_env = tunable("MG_RBGS3D_PF", 0);
     static bool opted_in[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !opted_in[dev]) {
-        if (cudaFuncSetAttribute(k_rbgs3d<RY, NS, NF, RW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        if (cudaFuncSetAttribute(k_rbgs3d<RY, NS, NF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)rbgs3d_smem_bytes<RY, NS, NF>()) != cudaSuccess)
             return false;
         opted_in[dev] = true;
@@ -207,8 +207,8 @@ inline bool launch_rbgs3d_cfg(mg_workspace* ws, Level& lv, const double* u, cons
     const int gx = (n + RB3_TW - 1) / RB3_TW, gy = (n + RY - 1) / RY;
     int zchunk = zc_env >= 3 ? zc_env : 64;
     while (zc_env < 3 && zchunk > 4 && gx * gy * ((n + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
-    launch_k(ws, k_rbgs3d<RY, NS, NF, RW>, dim3(gx, gy, (n + zchunk - 1) / zchunk), 32 * (RY + 2) / RW,
-             rbgs3d_smem_bytes<RY, NS, NF>(), lv.g, star3d(lv), *tm_u, *tm_f, out, w, zchunk);
+    launch_k(ws, k_rbgs3d<RY, NS, NF>, dim3(gx, gy, (n + zchunk - 1) / zchunk), 32 * (RY + 2),
+             rbgs3d_smem_bytes<RY, NS, NF>(), lv.g, star3d(lv), *tm_u, *tm_f, out, w, zchunk, pf_env);
     return true;
 }
 
@@ -217,11 +217,12 @@ inline bool launch_rbgs3d(mg_workspace* ws, Level& lv, const double* u, const do
     const int min_n = tunable("MG_RBGS3D_MIN_N", 257);      // not cached: the tests lower it to 65
     if (!enabled || lv.g.z0 != 0 || lv.g.nz != lv.g.n || lv.g.n < 65 || lv.g.n < min_n) return false;
     switch (cfg) {
-        case 1: return launch_rbgs3d_cfg<8, 6, 5, 2>(ws, lv, u, f, out, w);
-        case 2: return launch_rbgs3d_cfg<16, 6, 5, 1>(ws, lv, u, f, out, w);
-        case 3: return launch_rbgs3d_cfg<16, 6, 5, 2>(ws, lv, u, f, out, w);
-        case 4: return launch_rbgs3d_cfg<8, 5, 4, 1>(ws, lv, u, f, out, w);
-        default: return launch_rbgs3d_cfg<8, 6, 5, 1>(ws, lv, u, f, out, w);
+        // rows per tile, ring sizes of u / f (measured at 513^3, profiles/README.md): the default keeps
+        // 3 CTAs per SM (74 KB each) with 3 planes in flight
+        case 1: return launch_rbgs3d_cfg<8, 6, 5>(ws, lv, u, f, out, w);
+        case 2: return launch_rbgs3d_cfg<16, 6, 5>(ws, lv, u, f, out, w);
+        case 3: return launch_rbgs3d_cfg<12, 6, 5>(ws, lv, u, f, out, w);
+        default: return launch_rbgs3d_cfg<8, 7, 6>(ws, lv, u, f, out, w);
     }
 }
 

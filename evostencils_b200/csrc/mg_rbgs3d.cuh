@@ -24,6 +24,8 @@
 #pragma once
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "mg_fast3d.cuh"
 
 namespace mg {
@@ -42,9 +44,14 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* tm,
         "l"(tm), "r"(x), "r"(y), "r"(z), "r"(bar)
         : "memory");
 }
+__device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* tm, int x, int y, int z) {
+    asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(tm), "r"(x), "r"(y), "r"(z)
+                 : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
+    uint32_t ok, tries = 0;
     do {
+        if (++tries == (1u << 24)) __trap();        // a transfer that never completes: fail, do not hang
         asm volatile(
             "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
             : "=r"(ok)
@@ -62,36 +69,25 @@ constexpr size_t rbgs3d_smem_bytes() {
     return (size_t)(RB3_NS * (RY + 4) + RB3_NF * (RY + 2)) * RB3_W * sizeof(double) + 16 * sizeof(unsigned long long) + 128;
 }
 
-// u + w (f - A u) at component C of a lane's column pair c2; o = element offset of the pair in a ring
-// slot (um / uq / up: the staged planes below, at and above the node; fq: the right-hand side, whose tile
-// starts one row later).  The parity of a row is warp-uniform, so the two components are two code paths:
-// one shuffle each, no selects.
 template <int C>
-__device__ __forceinline__ double rb3_relax(const Star3D& st, double w, const double* um, const double* uq, const double* up,
-                                            const double* fq, int o, const double2 c2) {
-    double cen, wv, ev;
-    if (C == 0) {
-        cen = c2.x; ev = c2.y;
-        wv = __shfl_up_sync(0xffffffffu, c2.y, 1);
-    } else {
-        cen = c2.y; wv = c2.x;
-        ev = __shfl_down_sync(0xffffffffu, c2.x, 1);
-    }
-    const double sv = uq[o + C - RB3_W], nv = uq[o + C + RB3_W];
-    const double zm = um[o + C], zp = up[o + C];
-    const double fv = fq[o + C - RB3_W];
-    const double r = fv - star3_at(st, zm, sv, wv, cen, ev, nv, zp);
-    return cen + w * r;
-}
+__device__ __forceinline__ double rb3_get(const double2 v) { return C ? v.y : v.x; }
 
 // out = RB-GS sweep of u (red = (x+y+z) even first, then black), whole grid (g.nz == g.n, g.z0 == 0).
-// grid = (ceil(n / 60), ceil(n / RY), ceil(n / zchunk)), block = 32 * (RY + 2) / RW (RW tile rows per warp).
-template <int RY, int RB3_NS, int RB3_NF, int RW>
-__global__ void __launch_bounds__(32 * (RY + 2) / RW) k_rbgs3d(Geom g, Star3D st, const __grid_constant__ CUtensorMap tm_u,
-                                                               const __grid_constant__ CUtensorMap tm_f,
-                                                               double* __restrict__ out, double w, int zchunk) {
-    constexpr int UR = RY + 4, FR = RY + 2, NW = (RY + 2) / RW;
-    static_assert((RY + 2) % RW == 0 && RY % RW == 0 && RY % 2 == 0, "rows per warp must divide the red and the black rows");
+// grid = (ceil(n / 60), ceil(n / RY), ceil(n / zchunk)), block = 32 * (RY + 2): warp k owns tile row k+1
+// (y = yb-1+k) in both half-sweeps and carries its column pairs along z in registers:
+//   rzm, rc, rn   the row in the original planes s-1, s, s+1 (rn is read one step ahead: it is the z+
+//                 neighbour now and the centre of the next step; rzm is the z- neighbour),
+//   bzm, bc, pr   the row after the red half-sweep in planes s-2, s-1, s (pr is formed by this thread in
+//                 red(s), so the black half-sweep never re-reads its own row),
+//   fp, fq        the right-hand side of the row in planes s and s-1.
+// Per step a thread reads two 16-byte pairs (rn, fp) and four 8-byte values (the y neighbours of the red
+// and of the black node, which other warps own) from shared memory.
+template <int RY, int RB3_NS, int RB3_NF>
+__global__ void __launch_bounds__(32 * (RY + 2)) k_rbgs3d(Geom g, Star3D st, const __grid_constant__ CUtensorMap tm_u,
+                                                          const __grid_constant__ CUtensorMap tm_f,
+                                                          double* __restrict__ out, double w, int zchunk, int pf) {
+    constexpr int UR = RY + 4, FR = RY + 2, NW = RY + 2;
+    static_assert(RY % 2 == 0, "tile rows start on even y");
     constexpr uint32_t U_BYTES = UR * RB3_W * 8, F_BYTES = FR * RB3_W * 8;
     constexpr int U_SLOT = UR * RB3_W, F_SLOT = FR * RB3_W;                  // doubles per ring slot
     extern __shared__ __align__(128) unsigned char rb3_smem[];
@@ -143,30 +139,31 @@ __global__ void __launch_bounds__(32 * (RY + 2) / RW) k_rbgs3d(Geom g, Star3D st
 
     // ---- per-thread constants of the march ----
     const int x0 = xb - 2 + 2 * lane;                                       // first column of the lane's pair
-    const int o_red = (warp * RW + 1) * RB3_W + 2 * lane;                    // pair of the first red row in a slot
-    const int o_blk = o_red + RB3_W;                                         // ... of the first black row
-    // bit 2i+c: the red update of component c in red row i is kept (interior node inside the red region);
-    // bit 8+2i+c: component c of black row i is an interior node (in x and y)
+    const int y = yb - 1 + warp;                                             // the warp's row
+    const int o_row = (warp + 1) * RB3_W + 2 * lane;                         // its pair inside a slot of u
+    const int o_f = warp * RB3_W + 2 * lane;                                 // ... of f (the f tile starts one row later)
+    // bit c: the red update of component c is kept (interior node inside the red region); bit 2+c:
+    // component c is an interior node in x and y (black update); bit 4: the row is stored as whole pairs,
+    // bit 5: only its first column (x0 == n-1)
     unsigned ok = 0;
 #pragma unroll
-    for (int i = 0; i < RW; ++i)
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-            const int x = x0 + c, yr = yb - 1 + warp * RW + i, yk = yr + 1;
-            if (yr >= 1 && yr <= n - 2 && x >= imax(1, xb - 1) && x <= imin(n - 2, xb + RB3_TW)) ok |= 1u << (2 * i + c);
-            if (yk >= 1 && yk <= n - 2 && x >= 1 && x <= n - 2) ok |= 1u << (8 + 2 * i + c);
-        }
-    // store of black row i: bit 16+i a whole pair, bit 20+i only its first column (x0 == n-1)
-    const int y_blk = yb + warp * RW;
-#pragma unroll
-    for (int i = 0; i < RW; ++i)
-        if (lane >= 1 && lane <= RB3_TW / 2 && y_blk + i <= n - 1) {
-            if (x0 + 1 <= n - 1) ok |= 1u << (16 + i);
-            else if (x0 <= n - 1) ok |= 1u << (20 + i);
-        }
-    const bool black_warp = warp * RW < RY;
-    const int par_red = (yb - 1 + warp * RW) & 1;                            // + s: component of the red node in red row 0
-    double* optr = out + (long long)(zb - 2) * plane + (long long)y_blk * pitch + x0;   // plane s-1 at s = zb-1
+    for (int c = 0; c < 2; ++c) {
+        const int x = x0 + c;
+        if (y >= 1 && y <= n - 2 && x >= imax(1, xb - 1) && x <= imin(n - 2, xb + RB3_TW)) ok |= 1u << c;
+        if (y >= 1 && y <= n - 2 && x >= 1 && x <= n - 2) ok |= 4u << c;
+    }
+    if (warp >= 1 && warp <= RY && lane >= 1 && lane <= RB3_TW / 2 && y <= n - 1) {
+        if (x0 + 1 <= n - 1) ok |= 16u;
+        else if (x0 <= n - 1) ok |= 32u;
+    }
+    const bool black_warp = warp >= 1 && warp <= RY;
+    const int par_row = y & 1;                                               // + s: component of the red node (plane s)
+                                                                             //      = of the black node (plane s-1)
+    double* optr = out + (long long)(zb - 2) * plane + (long long)y * pitch + x0;   // plane s-1 at s = zb-1
+
+    double2 rzm = *reinterpret_cast<const double2*>(su + o_row);            // plane zb-2 (slot 0)
+    double2 rc = *reinterpret_cast<const double2*>(su + U_SLOT + o_row);    // plane zb-1 (slot 1)
+    double2 bzm = make_double2(0.0, 0.0), bc = bzm, fq = bzm;
 
     // ring state of step s = zb-1: element offsets of the slots of planes s-2, s-1, s, s+1 of u and of
     // planes s-1, s of f; barrier address and phase parity of plane s+1 of u and of plane s of f
@@ -178,57 +175,64 @@ __global__ void __launch_bounds__(32 * (RY + 2) / RW) k_rbgs3d(Geom g, Star3D st
         mbar_wait(b_f, par_f);
         double* const us = su + e_s;
         const double* const um = su + e_m;
-        const double* const up = su + e_p;
-        // ---- red(s): tile rows 1 .. RY+2 (y = yb-1 .. yb+RY) ----
-        if (s >= 1 && s <= n - 2) {
-            const double* const fs = sf + e_f;
-            const int c0 = (par_red + s) & 1;
-#pragma unroll
-            for (int i = 0; i < RW; ++i) {
-                const int o = o_red + i * RB3_W;
-                const double2 c2 = *reinterpret_cast<const double2*>(us + o);
-                if ((c0 ^ (i & 1)) == 0) {
-                    const double v = rb3_relax<0>(st, w, um, us, up, fs, o, c2);
-                    if (ok & (1u << (2 * i))) us[o] = v;
-                } else {
-                    const double v = rb3_relax<1>(st, w, um, us, up, fs, o, c2);
-                    if (ok & (1u << (2 * i + 1))) us[o + 1] = v;
-                }
-            }
-        }
-        __syncthreads();
-        if (warp == NW - 1) {
-            // planes <= s-3 of u and <= s-2 of f are dead now: refill their slots (the proxy fence orders
-            // the red stores other warps made into them, visible here through the barrier, before the
-            // asynchronous writes)
-            fence_proxy_async();
-            if (s - 3 >= p0 && s - 3 + RB3_NS <= ze + 1) stage_u(s - 3 + RB3_NS, back(e_m2 / U_SLOT, 1, RB3_NS));
-            if (s - 2 >= fp0 && s - 2 + RB3_NF <= ze) stage_f(s - 2 + RB3_NF, back(e_f1 / F_SLOT, 1, RB3_NF));
-        }
-        // ---- black(s-1) + store of the finished plane: tile rows 2 .. RY+1 (y = yb .. yb+RY-1) ----
+        const double2 rn = *reinterpret_cast<const double2*>(su + e_p + o_row);
+        const double2 fp = *reinterpret_cast<const double2*>(sf + e_f + o_f);
+        const bool red_plane = s >= 1 && s <= n - 2;
         const int q = s - 1;
-        if (q >= zb && q < ze && black_warp) {
-            const double* const uqm = su + e_m2;
-            const double* const fq = sf + e_f1;
-            const bool q_in = q >= 1 && q <= n - 2;
-            const int c0 = (par_red + s + 1) & 1;       // black row i lies one row above red row i, in plane s-1: its
-                                                        // black node has the other component
-#pragma unroll
-            for (int i = 0; i < RW; ++i) {
-                const int o = o_blk + i * RB3_W;
-                double2 c2 = *reinterpret_cast<const double2*>(um + o);
-                if ((c0 ^ (i & 1)) == 0) {
-                    const double v = rb3_relax<0>(st, w, uqm, um, us, fq, o, c2);
-                    if (q_in && (ok & (1u << (8 + 2 * i)))) c2.x = v;
-                } else {
-                    const double v = rb3_relax<1>(st, w, uqm, um, us, fq, o, c2);
-                    if (q_in && (ok & (1u << (9 + 2 * i)))) c2.y = v;
+        const bool black_plane = q >= zb && q < ze && black_warp;
+        const bool q_in = q >= 1 && q <= n - 2;
+        double2 pr = rc;                                                     // the row of plane s after red(s)
+
+        auto step = [&](auto tag) {
+            constexpr int C = decltype(tag)::value;
+            // ---- red(s): component C of the pair ----
+            if (red_plane) {
+                const double wv = C ? rc.x : __shfl_up_sync(0xffffffffu, rc.y, 1);
+                const double ev = C ? __shfl_down_sync(0xffffffffu, rc.x, 1) : rc.y;
+                const double sv = us[o_row + C - RB3_W], nv = us[o_row + C + RB3_W];
+                const double cen = rb3_get<C>(rc);
+                const double r = rb3_get<C>(fp) - star3_at(st, rb3_get<C>(rzm), sv, wv, cen, ev, nv, rb3_get<C>(rn));
+                const double v = cen + w * r;
+                if (ok & (1u << C)) {
+                    us[o_row + C] = v;
+                    if (C) pr.y = v; else pr.x = v;
                 }
-                double* o_g = optr + i * pitch;
-                if (ok & (1u << (16 + i))) st2(o_g, c2);
-                else if (ok & (1u << (20 + i))) *o_g = c2.x;
             }
-        }
+            __syncthreads();
+            if (warp == NW - 1) {
+                // planes <= s-3 of u and <= s-2 of f are dead now: refill their slots (the proxy fence orders
+                // the red stores other warps made into them, visible here through the barrier, before the
+                // asynchronous writes)
+                fence_proxy_async();
+                if (s - 3 >= p0 && s - 3 + RB3_NS <= ze + 1) stage_u(s - 3 + RB3_NS, back(e_m2 / U_SLOT, 1, RB3_NS));
+                if (s - 2 >= fp0 && s - 2 + RB3_NF <= ze) stage_f(s - 2 + RB3_NF, back(e_f1 / F_SLOT, 1, RB3_NF));
+                if (pf > 0 && lane == 0 && s + pf <= imin(ze + 1, n - 1)) {     // the boxes of plane s+pf -> L2
+                    tma_prefetch_3d(&tm_u, xb - 2, yb - 2, s + pf);
+                    if (s + pf <= ze) tma_prefetch_3d(&tm_f, xb - 2, yb - 1, s + pf);
+                }
+            }
+            // ---- black(s-1): component C of the pair, then the finished row of plane s-1 is stored ----
+            if (black_plane) {
+                const double wv = C ? bc.x : __shfl_up_sync(0xffffffffu, bc.y, 1);
+                const double ev = C ? __shfl_down_sync(0xffffffffu, bc.x, 1) : bc.y;
+                const double sv = um[o_row + C - RB3_W], nv = um[o_row + C + RB3_W];
+                const double cen = rb3_get<C>(bc);
+                const double r = rb3_get<C>(fq) - star3_at(st, rb3_get<C>(bzm), sv, wv, cen, ev, nv, rb3_get<C>(pr));
+                const double v = cen + w * r;
+                double2 o2 = bc;
+                if (q_in && (ok & (4u << C))) {
+                    if (C) o2.y = v; else o2.x = v;
+                }
+                if (ok & 16u) st2(optr, o2);
+                else if (ok & 32u) *optr = o2.x;
+            }
+        };
+        if ((par_row + s) & 1) step(std::integral_constant<int, 1>{});
+        else step(std::integral_constant<int, 0>{});
+
+        rzm = rc; rc = rn;
+        bzm = bc; bc = pr;
+        fq = fp;
         optr += plane;
         e_m2 = e_m; e_m = e_s; e_s = e_p;
         e_p += U_SLOT; b_u += 8;

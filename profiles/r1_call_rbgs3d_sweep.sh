@@ -5,7 +5,9 @@ timeout -k 10 200 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "3d_
 echo "two colour passes: $(MG_RBGS3D=0 timeout -k 10 120 python profiles/time_rbgs3d.py 2>&1 | tail -1 | cut -c1-80)"
 for cfg in ${CFGS:-0 1 2 3}; do
   for zc in ${ZCS:-32 64}; do
-    echo "cfg $cfg zchunk $zc: $(MG_RBGS3D_CFG=$cfg MG_RBGS3D_ZCHUNK=$zc timeout -k 10 120 python profiles/time_rbgs3d.py 2>&1 | tail -1 | cut -c1-80)"
+    for pf in ${PFS:-0}; do
+      echo "cfg $cfg zchunk $zc pf $pf: $(MG_RBGS3D_CFG=$cfg MG_RBGS3D_ZCHUNK=$zc MG_RBGS3D_PF=$pf timeout -k 10 120 python profiles/time_rbgs3d.py --level ${LEVEL:-9} 2>&1 | tail -1 | cut -c1-80)"
+    done
   done
 done
 if [ -n "$NCU_CFG" ]; then
