@@ -11,6 +11,7 @@
 #include "mg_fast2d.cuh"
 #include "mg_fast3d.cuh"
 #include "mg_rbgs3d.cuh"
+#include "mg_restrict3d.cuh"
 #include "mg_workspace.cuh"
 
 namespace mg {
@@ -328,8 +329,52 @@ inline bool fast_norm(mg_workspace* ws, Level& lv) {
     return false;
 }
 
+// fused 3D residual + restriction (mg_restrict3d.cuh): whole grids, fine level of at least 129^3 nodes
+template <int RYC, int NS, int NF>
+inline bool launch_resrestrict3d_cfg(mg_workspace* ws, Level& lf, Level& lc, const double* u, const double* f, double* out) {
+    static const int zc_env = tunable("MG_RESTRICT3D_ZCHUNK", 0);
+    static bool opted_in[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !opted_in[dev]) {
+        if (cudaFuncSetAttribute(k_resrestrict3d<RYC, NS, NF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)resrestrict3d_smem_bytes<RYC, NS, NF>()) != cudaSuccess)
+            return false;
+        opted_in[dev] = true;
+    }
+    const CUtensorMap* tm_u = plane_tensor_map(u, lf.g, 2 * RYC + 3);
+    const CUtensorMap* tm_f = plane_tensor_map(f, lf.g, 2 * RYC + 1);
+    if (!tm_u || !tm_f) return false;
+    const int m = lc.g.n - 2;                                              // interior coarse nodes per dimension
+    const int gx = (m + RS3_TXC - 1) / RS3_TXC, gy = (m + RYC - 1) / RYC;
+    int zchunk = zc_env >= 2 ? zc_env : 32;
+    while (zc_env < 2 && zchunk > 2 && gx * gy * ((m + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
+    launch_k(ws, k_resrestrict3d<RYC, NS, NF>, dim3(gx, gy, (m + zchunk - 1) / zchunk), 32 * (2 * RYC + 1),
+             resrestrict3d_smem_bytes<RYC, NS, NF>(), lc.g, lf.g, star3d(lf), *tm_u, *tm_f, out, zchunk);
+    return true;
+}
+
 template <typename T, int D, int F>
 inline bool fast_residual_restrict(mg_workspace* ws, Level& lf, Level& lc) {
+    if constexpr (D == 3 && F == 1 && sizeof(T) == sizeof(double)) {
+        static const int enabled = tunable("MG_RESTRICT3D", 1), cfg = tunable("MG_RESTRICT3D_CFG", 0);
+        const int min_n = tunable("MG_RESTRICT3D_MIN_N", 129);     // not cached: the tests lower it to 65
+        if (!enabled || !star3d_nt(ws, lf) || lf.g.z0 != 0 || lf.g.nz != lf.g.n || lc.g.z0 != 0 || lc.g.nz != lc.g.n ||
+            lf.g.n < 65 || lf.g.n < min_n)
+            return false;
+        const double* u = static_cast<const double*>(lf.sol[lf.cur[0]][0]);
+        const double* f = static_cast<const double*>(lf.rhs[0]);
+        double* out = static_cast<double*>(lc.rhs[0]);
+        bool done;
+        switch (cfg) {
+            case 1: done = launch_resrestrict3d_cfg<4, 4, 3>(ws, lf, lc, u, f, out); break;
+            case 2: done = launch_resrestrict3d_cfg<8, 5, 3>(ws, lf, lc, u, f, out); break;
+            case 3: done = launch_resrestrict3d_cfg<2, 6, 4>(ws, lf, lc, u, f, out); break;
+            default: done = launch_resrestrict3d_cfg<4, 5, 4>(ws, lf, lc, u, f, out); break;
+        }
+        if (done) fast_count(ws);
+        return done;
+    }
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
         static const int tile_rc = tunable("MG_RESTRICT_RC", 3);     // 0: marching kernel
         // the tile kernel clamps its columns itself: any level the 2-column kernels accept (>= 257^2)

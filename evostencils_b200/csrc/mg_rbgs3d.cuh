@@ -51,7 +51,7 @@ __device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* tm, int x, in
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok, tries = 0;
     do {
-        if (++tries == (1u << 24)) __trap();        // a transfer that never completes: fail, do not hang
+        if (++tries == (1u << 20)) __trap();        // a transfer that never completes: fail, do not hang
         asm volatile(
             "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
             : "=r"(ok)

@@ -437,6 +437,7 @@ def test_fast_3d_stages_bit_identical(hi, one_pass, monkeypatch):
     `one_pass`: RB-GS through k_rbgs3d (by default only from 257^3 up) instead of two colour passes."""
     from oracle import driver, mg_oracle
     monkeypatch.setenv("MG_RBGS3D_MIN_N", "65" if one_pass else "100000")
+    monkeypatch.setenv("MG_RESTRICT3D_MIN_N", "65" if one_pass else "100000")     # k_resrestrict3d likewise
     problem, lo = problems.POISSON_3D, hi - 1
     ws, h = make_pair(problem, lo, hi, seed=13)
     run_both(ws, h, [lowering.Op("residual", hi, dst="res")], problem)
@@ -467,7 +468,7 @@ def test_one_pass_3d_rbgs_bit_identical_to_generic_at_257(omega):
     rng = np.random.default_rng(5)
     u0, f0 = rng.standard_normal((n, n, n)), rng.standard_normal((n, n, n))
     stmts = smoother_statements(problem, hi, "collective", ir.RedBlack, omega=omega)
-    out = []
+    out, coarse = [], []
     for fast in (True, False):
         ws = Workspace(3, hi - 1, hi, 1, "f64", 0)
         for level in (hi - 1, hi):
@@ -478,7 +479,13 @@ def test_one_pass_3d_rbgs_bit_identical_to_generic_at_257(omega):
         for sweep in range(2):
             ws.exec_ops(stmts)
         out.append(ws.download("sol", hi, 0))
+        # fused residual + restriction (k_resrestrict3d: 5 x 32 x 4 tiles of coarse nodes) on the smoothed field
+        ws.exec_ops([lowering.Op("residual", hi, dst="res"), lowering.Op("restrict", hi - 1, src="res", dst="rhs")], fused=True)
+        coarse.append(ws.download("rhs", hi - 1, 0))
         ws.close()
     bad = np.argwhere(out[0] != out[1])
     assert bad.size == 0, f"{len(bad)} mismatching nodes, first {bad[:4].tolist()}"
     assert not np.array_equal(out[0], u0)
+    bad = np.argwhere(coarse[0][1:-1, 1:-1, 1:-1] != coarse[1][1:-1, 1:-1, 1:-1])
+    assert bad.size == 0, f"restriction: {len(bad)} mismatching coarse nodes, first {bad[:4].tolist()}"
+    assert np.abs(coarse[0][1:-1, 1:-1, 1:-1]).max() > 0
