@@ -4,7 +4,8 @@
 
 Step  = the first N x `--individuals-per-gpu` individuals of the stored 256-individual population
         (weak scaling; 32 per GPU = the whole population on 8 GPUs) are evaluated once through
-        B200ProgramGenerator.generate_and_evaluate; ranks take individuals from a shared counter.
+        B200ProgramGenerator.generate_and_evaluate; ranks take individuals from a shared counter and
+        evaluate `--streams` (default 2) of them at a time, each on its own workspace and CUDA stream.
 value = fine-grid DoF updates per second = sum over individuals of (interior DoF x multigrid
         cycles executed) / step time, whole job, inputs resident in HBM.
 e2e   = same metric with the RHS and the initial guess copied from pinned host memory for every
@@ -42,6 +43,9 @@ def parse_args():
     ap.add_argument("--schedule", default="dynamic", choices=["dynamic", "static"],
                     help="dynamic: ranks take the next individual of the step from a shared counter "
                          "(population.WorkQueue); static: the reference's i %% nprocs striding")
+    ap.add_argument("--streams", type=int, default=2,
+                    help="engine workspaces (= CUDA streams, one host thread each) per GPU: individuals of a rank are "
+                         "evaluated concurrently, the coarse levels of one under the fine levels of another")
     ap.add_argument("--max-level", type=int, default=12)
     ap.add_argument("--grammar-depth", type=int, default=5)
     ap.add_argument("--engine-min-level", type=int, default=2)
@@ -214,28 +218,34 @@ def finest_stage_counts(program, hi):
     return counts
 
 
-def evaluate_shard(gen, grammar, jobs, lo, hi, stage_counts=None, schedule="dynamic"):
+def evaluate_shard(gens, grammar, jobs, lo, hi, stage_counts=None, schedule="dynamic"):
     """One step: this rank's part of the step's individuals `jobs` (self-scheduled over the ranks
-    through population.WorkQueue, or strided i % world).  -> (cycles executed, results)."""
+    through population.WorkQueue, or strided i % world), spread over the rank's generators (one host
+    thread, workspace and stream each).  -> (cycles executed, results)."""
     from evostencils_b200 import population
-    cycles = 0
-    results = []
     if schedule == "dynamic":
         mine = population.WorkQueue(len(jobs))
     else:
         rank, world, _ = population._world()
         mine = population.shard_indices(len(jobs), rank, world)
-    for k in mine:
-        string = jobs[k]
-        expression, _ = grammar.compile(string)
-        t, rho, n = gen.generate_and_evaluate(expression, None, lo, hi, "", evaluation_samples=1)
-        c = max(0, len(gen.last_residual_history) - 1)
-        cycles += c
-        if stage_counts is not None and gen.last_program is not None:
-            for name, k in finest_stage_counts(gen.last_program, hi).items():
-                stage_counts[name] = stage_counts.get(name, 0) + k * c
-        results.append((t, rho, n))
-    return cycles, results
+    cycles = [0] * len(gens)
+    lock = threading.Lock()
+
+    def evaluator(slot, gen):
+        def evaluate(string):
+            expression, _ = grammar.compile(string)
+            t, rho, n = gen.generate_and_evaluate(expression, None, lo, hi, "", evaluation_samples=1)
+            c = max(0, len(gen.last_residual_history) - 1)
+            cycles[slot] += c
+            if stage_counts is not None and gen.last_program is not None:
+                with lock:
+                    for name, k in finest_stage_counts(gen.last_program, hi).items():
+                        stage_counts[name] = stage_counts.get(name, 0) + k * c
+            return (t, rho, n)
+        return evaluate
+
+    local = population.run_concurrently([evaluator(i, g) for i, g in enumerate(gens)], mine, jobs)
+    return sum(cycles), [local[k] for k in sorted(local)]
 
 
 def run_b200(args):
@@ -260,36 +270,43 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     def timed_phase(resident):
-        gen, problem, lo, hi = make_generator(args, local, resident)
+        made = [make_generator(args, local, resident) for _ in range(max(1, args.streams))]
+        gens = [m[0] for m in made]
+        gen, problem, lo, hi = made[0]
         grammar = Grammar(problem, lo, hi, maximum_local_system_size=4)
         # longest-first by the static cost of one cycle (the number of cycles is not known beforehand)
         cost = [lowering.estimate_cycle_bytes(lowering.lower(grammar.compile(s)[0], lo, hi).ops, problem.dimension)
                 for s in jobs]
         ordered = [jobs[i] for i in sorted(range(len(jobs)), key=lambda i: (-cost[i], i))]
         us, fs = synthetic_inputs(problem, hi)
-        gen.set_inputs(rhs=fs, u0=us)
+        for g in gens:
+            g.set_inputs(rhs=fs, u0=us)
         for _ in range(args.warmup):
-            evaluate_shard(gen, grammar, ordered, lo, hi, schedule=args.schedule)
-        ws = gen._workspace
-        gen.h2d_bytes = gen.d2h_bytes = 0
-        launches0 = ws.launch_count()
+            evaluate_shard(gens, grammar, ordered, lo, hi, schedule=args.schedule)
+        wss = [g._workspace for g in gens]
+        for g in gens:
+            g.h2d_bytes = g.d2h_bytes = 0
+        launches0 = sum(w.launch_count() for w in wss)
         barrier()
-        ws.mark(0)
+        for w in wss:
+            w.mark(0)
         t0 = time.perf_counter()
         cycles = 0
         results = None
         counts = {}
         for _ in range(args.steps):
-            c, results = evaluate_shard(gen, grammar, ordered, lo, hi, counts, schedule=args.schedule)
+            c, results = evaluate_shard(gens, grammar, ordered, lo, hi, counts, schedule=args.schedule)
             cycles += c
-        ws.mark(1)
-        ws.synchronize()
+        for w in wss:
+            w.mark(1)
+        for w in wss:
+            w.synchronize()
         barrier()
         wall_ms = (time.perf_counter() - t0) * 1e3
-        dev_ms = ws.elapsed()
-        launches = ws.launch_count() - launches0
-        stats = torch.tensor([dev_ms, wall_ms, float(cycles), float(launches), float(gen.h2d_bytes),
-                              float(gen.d2h_bytes)], dtype=torch.float64, device="cuda")
+        dev_ms = max(w.elapsed() for w in wss)          # every stream is marked at the common start and end
+        launches = sum(w.launch_count() for w in wss) - launches0
+        stats = torch.tensor([dev_ms, wall_ms, float(cycles), float(launches), float(sum(g.h2d_bytes for g in gens)),
+                              float(sum(g.d2h_bytes for g in gens))], dtype=torch.float64, device="cuda")
         if world > 1:
             mx = stats.clone()
             dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -300,14 +317,16 @@ def run_b200(args):
             h2d, d2h = sm[4].item(), sm[5].item()
         else:
             h2d, d2h = stats[4].item(), stats[5].item()
-        return gen, problem, lo, hi, dev_ms, wall_ms, cycles, launches, h2d, d2h, results, counts
+        return gens, problem, lo, hi, dev_ms, wall_ms, cycles, launches, h2d, d2h, results, counts
 
     with ClockSampler(local) as clocks:
-        gen, problem, lo, hi, dev_ms, wall_ms, cycles, launches, _, _, results, counts = timed_phase(resident=True)
-        stages = stage_rooflines(gen, problem, hi, peak) if rank == 0 else None
-        gen.close()
-        gen2, _, _, _, dev2, wall2, cycles2, launches2, h2d, d2h, _, _ = timed_phase(resident=False)
-        gen2.close()
+        gens, problem, lo, hi, dev_ms, wall_ms, cycles, launches, _, _, results, counts = timed_phase(resident=True)
+        stages = stage_rooflines(gens[0], problem, hi, peak) if rank == 0 else None
+        for g in gens:
+            g.close()
+        gens2, _, _, _, dev2, wall2, cycles2, launches2, h2d, d2h, _, _ = timed_phase(resident=False)
+        for g in gens2:
+            g.close()
     dof = float((2 ** hi - 1) ** 2)
     value = dof * cycles / (dev_ms * 1e-3)
     e2e = dof * cycles2 / (max(dev2, wall2) * 1e-3)
@@ -330,7 +349,7 @@ def run_b200(args):
         "config": {"workload": "BASELINE.json configs[1]: 2D Poisson 5-point 4096^2 fp64, fitness evaluation of "
                                "evolved-cycle individuals (grammar levels %d..%d, default V(2,1) RB-GS cycle + CG "
                                "below, engine levels %d..%d)" % (lo, hi, args.engine_min_level, hi),
-                   "individuals_per_gpu": p, "individuals_per_step": world * p, "schedule": args.schedule, "population": os.path.relpath(POPULATION, ROOT),
+                   "individuals_per_gpu": p, "individuals_per_step": world * p, "schedule": args.schedule, "streams_per_gpu": max(1, args.streams), "population": os.path.relpath(POPULATION, ROOT),
                    "evaluation_samples": 1, "target_reduction": 1e-12, "max_iterations": 100,
                    "inputs": "u0=0, f~N(0,1) seed 1234 (SURVEY.md 8d)",
                    "l2_policy": "every field array is 134 MB > 126 MB L2; stage timings additionally flush L2",

@@ -61,10 +61,12 @@ class WorkQueue:
     _serial = 0
 
     def __init__(self, n_jobs: int, group=None, store=None):
+        import threading
         rank, world, dist = _world(group)
         self.n_jobs = n_jobs
         self.world = world
         self._next = 0
+        self._lock = threading.Lock()           # several evaluation threads of one rank may share a queue
         self._store = None
         if world > 1:
             if store is None:
@@ -78,11 +80,12 @@ class WorkQueue:
         return self
 
     def __next__(self) -> int:
-        if self._store is None:
-            k = self._next
-            self._next += 1
-        else:
-            k = self._store.add(self._key, 1) - 1
+        with self._lock:
+            if self._store is None:
+                k = self._next
+                self._next += 1
+            else:
+                k = self._store.add(self._key, 1) - 1
         if k >= self.n_jobs:
             raise StopIteration
         return k
@@ -115,9 +118,54 @@ def gather_results(local: dict, n_items: int, group=None, device=None) -> List[R
     return [(buf[i, 0].item(), buf[i, 1].item(), buf[i, 2].item()) for i in range(n_items)]
 
 
-def evaluate_population(evaluate: Callable[[str], Result], strings: Sequence[str], group=None, device=None,
+def run_concurrently(evaluators: Sequence[Callable[[str], Result]], jobs, unique: Sequence[str]) -> dict:
+    """Evaluate `unique[j]` for every j the iterator `jobs` yields, with one host thread per evaluator
+    (= per engine workspace and CUDA stream of this rank).  The engine calls release the GIL, so the
+    solves of the threads overlap on the GPU: the latency-bound coarse levels of one individual run
+    under the bandwidth-bound fine levels of another (`north_star`: one individual per stream).
+    Results per individual do not depend on the overlap; the measured solve *time* of an individual
+    does (it shares the GPU), like a reference run that shares a node's memory bandwidth with other
+    MPI ranks.  -> {j: result}"""
+    import threading
+    local: dict = {}
+    errors: list = []
+    lock = threading.Lock()
+    it = iter(jobs)
+
+    def take():
+        with lock:
+            return next(it, None)
+
+    def work(evaluate):
+        try:
+            while True:
+                j = take()
+                if j is None:
+                    return
+                r = evaluate(unique[j])
+                with lock:
+                    local[j] = r
+        except BaseException as exc:            # surfaced on the calling thread
+            errors.append(exc)
+
+    if len(evaluators) == 1:
+        work(evaluators[0])
+    else:
+        threads = [threading.Thread(target=work, args=(e,), daemon=True) for e in evaluators]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+    if errors:
+        raise errors[0]
+    return local
+
+
+def evaluate_population(evaluate, strings: Sequence[str], group=None, device=None,
                         costs: Optional[Sequence[float]] = None, schedule: str = "static") -> List[Result]:
     """Evaluate every individual once across the ranks of `group`; every rank gets all results.
+    `evaluate` may be a list of callables, one per engine workspace of this rank: they run in
+    parallel host threads and share the rank's part of the population (`run_concurrently`).
 
     `evaluate(grammar_string) -> (time_ms, rho, n)` runs on this rank's GPU.  With `costs`
     (e.g. op-list byte counts) the unique individuals are dealt longest-first so that the ranks
@@ -134,13 +182,14 @@ def evaluate_population(evaluate: Callable[[str], Result], strings: Sequence[str
         for i, b in enumerate(back):
             first.setdefault(b, costs[i])
         order.sort(key=lambda u: (-first[u], u))
+    evaluators = list(evaluate) if isinstance(evaluate, (list, tuple)) else [evaluate]
     if schedule == "dynamic":
-        local = {order[k]: evaluate(unique[order[k]]) for k in WorkQueue(len(order), group)}
+        jobs = (order[k] for k in WorkQueue(len(order), group))
     elif schedule == "static":
-        mine = [order[k] for k in shard_indices(len(order), rank, world)]
-        local = {u: evaluate(unique[u]) for u in mine}
+        jobs = [order[k] for k in shard_indices(len(order), rank, world)]
     else:
         raise ValueError("schedule must be 'static' or 'dynamic'")
+    local = run_concurrently(evaluators, jobs, unique)
     results = gather_results(local, len(unique), group, device)
     return [results[b] for b in back]
 
@@ -166,12 +215,14 @@ def batched_map(generator, grammar, min_level, max_level, evaluation_samples=1, 
     The mapped function is ignored for individuals given as grammar strings / PrimitiveTrees:
     they are evaluated through `generate_and_evaluate` and returned as (rho, t/n) fitness tuples
     like `evaluate_multiple_objectives` (program.py:419-453)."""
-    evaluator = make_evaluator(generator, grammar, min_level, max_level, evaluation_samples, infinity)
+    generators = list(generator) if isinstance(generator, (list, tuple)) else [generator]
+    # several generators (one workspace and stream each): their evaluations overlap on the GPU
+    evaluators = [make_evaluator(g, grammar, min_level, max_level, evaluation_samples, infinity) for g in generators]
 
     def _map(_function, individuals):
         strings = [str(ind) for ind in individuals]
         out = []
-        for t, rho, n in evaluate_population(evaluator, strings, group, schedule=schedule):
+        for t, rho, n in evaluate_population(evaluators, strings, group, schedule=schedule):
             if n >= infinity:                            # program.py:447-448
                 out.append((rho, infinity))
             else:

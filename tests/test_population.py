@@ -104,6 +104,34 @@ def test_work_queue_single_process():
         population.evaluate_population(fake_evaluate, STRINGS, schedule="guided")
 
 
+def test_concurrent_evaluators_share_the_jobs():
+    import threading
+    import time
+    seen = {0: [], 1: [], 2: []}
+
+    def make(k):
+        def evaluate(s):
+            seen[k].append((s, threading.get_ident()))
+            time.sleep(0.005)                   # long enough for the other threads to take jobs too
+            return fake_evaluate(s)
+        return evaluate
+
+    want = [fake_evaluate(s) for s in STRINGS]
+    for schedule in ("static", "dynamic"):
+        for k in seen:
+            seen[k].clear()
+        got = population.evaluate_population([make(0), make(1), make(2)], STRINGS, schedule=schedule)
+        assert got == want
+        calls = [s for k in seen for s, _ in seen[k]]
+        assert sorted(calls) == sorted(set(STRINGS))                 # every unique individual exactly once
+        assert len({t for k in seen for _, t in seen[k]}) >= 2       # on more than one thread
+
+    def broken(s):
+        raise RuntimeError("boom")
+    with pytest.raises(RuntimeError):
+        population.evaluate_population([broken, broken], STRINGS)
+
+
 def test_world_size_2_gloo_dynamic_schedule():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
