@@ -489,3 +489,37 @@ def test_one_pass_3d_rbgs_bit_identical_to_generic_at_257(omega):
     bad = np.argwhere(coarse[0][1:-1, 1:-1, 1:-1] != coarse[1][1:-1, 1:-1, 1:-1])
     assert bad.size == 0, f"restriction: {len(bad)} mismatching coarse nodes, first {bad[:4].tolist()}"
     assert np.abs(coarse[0][1:-1, 1:-1, 1:-1]).max() > 0
+
+
+def test_concurrent_evaluations_are_bitwise_those_of_sequential_ones():
+    """Two generators (workspace + stream + host thread each) sharing a list of individuals
+    (population.run_concurrently, the bench's `--streams 2`) give exactly the results and residual
+    histories of one generator evaluating them one after the other."""
+    from evostencils_b200 import population
+    from evostencils_b200.generator import B200ProgramGenerator
+    problem, lo, hi = problems.POISSON_2D, 5, 10
+    grammar = Grammar(problem, lo, hi)
+    strings = [v_cycle_string(hi - lo, 2, 1, 21, "red_black"), v_cycle_string(hi - lo, 2, 2, 14, "single"),
+               v_cycle_string(hi - lo, 1, 1, 23, "red_black"), v_cycle_string(hi - lo, 3, 3, 12, "single"),
+               v_cycle_string(hi - lo, 2, 0, 21, "red_black"), v_cycle_string(hi - lo, 1, 2, 16, "single")]
+
+    def evaluator(gen, histories):
+        def evaluate(string):
+            expression, _ = grammar.compile(string)
+            t, rho, n = gen.generate_and_evaluate(expression, None, lo, hi, "", evaluation_samples=1)
+            histories[string] = list(gen.last_residual_history)
+            return (rho, n)
+        return evaluate
+
+    runs = []
+    for n_gens in (1, 2):
+        gens = [B200ProgramGenerator(problem=problem, min_level=lo, max_level=hi, device=0, engine_min_level=2)
+                for _ in range(n_gens)]
+        histories = {}
+        got = population.run_concurrently([evaluator(g, histories) for g in gens], range(len(strings)), strings)
+        runs.append(([got[j] for j in range(len(strings))], histories))
+        for g in gens:
+            g.close()
+    assert runs[0][0] == runs[1][0]
+    assert runs[0][1] == runs[1][1]
+    assert all(len(h) > 3 for h in runs[0][1].values())
