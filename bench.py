@@ -15,6 +15,7 @@ The line also carries `roofline` (dominant kernel, timed live with CUDA events),
 `--impl reference` times the CPU port of the reference path instead (rank 0 only).
 """
 import argparse
+import contextlib
 import json
 import os
 import subprocess
@@ -97,7 +98,7 @@ class ClockSampler:
                     self.samples.append(parts)
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._stop.wait(0.5)
 
     def __enter__(self):
         self._thread = threading.Thread(target=self._run, daemon=True)
@@ -319,7 +320,9 @@ def run_b200(args):
             h2d, d2h = stats[4].item(), stats[5].item()
         return gens, problem, lo, hi, dev_ms, wall_ms, cycles, launches, h2d, d2h, results, counts
 
-    with ClockSampler(local) as clocks:
+    # clocks are sampled for rank 0's GPU only: one nvidia-smi process per rank every 0.2 s takes the
+    # driver's global locks often enough on an 8-GPU box to disturb the other ranks' launches
+    with (ClockSampler(local) if rank == 0 else contextlib.nullcontext()) as clocks:
         gens, problem, lo, hi, dev_ms, wall_ms, cycles, launches, _, _, results, counts = timed_phase(resident=True)
         stages = stage_rooflines(gens[0], problem, hi, peak) if rank == 0 else None
         for g in gens:

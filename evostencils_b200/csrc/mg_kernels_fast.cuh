@@ -414,13 +414,21 @@ inline bool fast_prolong_add(mg_workspace* ws, Level& lf, Level& lc, const Field
     if constexpr (D == 3 && F == 1 && sizeof(T) == sizeof(double)) {
         const int nt = star3d_nt(ws, lf);
         if (!nt || lf.g.nz < 3) return false;
-        constexpr int RY = 4;
-        dim3 grid((lf.g.n - 1) / (2 * nt), (lf.g.n - 2 + RY - 1) / RY, lf.g.nz - 2);
+        // rows per thread: 8 on large levels (513^3: 0.486 ms against 0.510 with 4 and 0.604 with 2), else 4
+        static const int ry_tuned = tunable("MG_PROLONG3D_RY", 0);
+        const int ry_env = ry_tuned ? ry_tuned : (lf.g.n >= 257 ? 8 : 4);
         const double* e = reinterpret_cast<const double*>(src.p[0]);
         double* u = static_cast<double*>(lf.sol[lf.cur[0]][0]);
-        if (nt == 128) launch_k(ws, k_prolong3d<128, RY>, grid, 128, 0, lf.g, lc.g, e, u, omega);
-        else if (nt == 64) launch_k(ws, k_prolong3d<64, RY>, grid, 64, 0, lf.g, lc.g, e, u, omega);
-        else launch_k(ws, k_prolong3d<32, RY>, grid, 32, 0, lf.g, lc.g, e, u, omega);
+        auto launch = [&](auto ry_tag) {
+            constexpr int RY = decltype(ry_tag)::value;
+            dim3 grid((lf.g.n - 1) / (2 * nt), (lf.g.n - 2 + RY - 1) / RY, lf.g.nz - 2);
+            if (nt == 128) launch_k(ws, k_prolong3d<128, RY>, grid, 128, 0, lf.g, lc.g, e, u, omega);
+            else if (nt == 64) launch_k(ws, k_prolong3d<64, RY>, grid, 64, 0, lf.g, lc.g, e, u, omega);
+            else launch_k(ws, k_prolong3d<32, RY>, grid, 32, 0, lf.g, lc.g, e, u, omega);
+        };
+        if (ry_env == 8) launch(std::integral_constant<int, 8>{});
+        else if (ry_env == 2) launch(std::integral_constant<int, 2>{});
+        else launch(std::integral_constant<int, 4>{});
         fast_count(ws);
         return true;
     }
