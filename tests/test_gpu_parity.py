@@ -468,7 +468,10 @@ def test_one_pass_3d_rbgs_bit_identical_to_generic_at_257(omega):
     rng = np.random.default_rng(5)
     u0, f0 = rng.standard_normal((n, n, n)), rng.standard_normal((n, n, n))
     stmts = smoother_statements(problem, hi, "collective", ir.RedBlack, omega=omega)
-    out, coarse = [], []
+    nc = 2 ** (hi - 1) + 1
+    e0 = np.zeros((nc, nc, nc))
+    e0[1:-1, 1:-1, 1:-1] = rng.standard_normal((nc - 2, nc - 2, nc - 2))
+    out, coarse, corrected = [], [], []
     for fast in (True, False):
         ws = Workspace(3, hi - 1, hi, 1, "f64", 0)
         for level in (hi - 1, hi):
@@ -482,6 +485,10 @@ def test_one_pass_3d_rbgs_bit_identical_to_generic_at_257(omega):
         # fused residual + restriction (k_resrestrict3d: 5 x 32 x 4 tiles of coarse nodes) on the smoothed field
         ws.exec_ops([lowering.Op("residual", hi, dst="res"), lowering.Op("restrict", hi - 1, src="res", dst="rhs")], fused=True)
         coarse.append(ws.download("rhs", hi - 1, 0))
+        # prolongation + correction with 8 rows per thread (the variant used from 257^3 up)
+        ws.upload("sol", hi - 1, 0, e0)
+        ws.exec_ops([lowering.Op("prolong_add", hi, omega=0.7, src="sol", dst="sol")])
+        corrected.append(ws.download("sol", hi, 0))
         ws.close()
     bad = np.argwhere(out[0] != out[1])
     assert bad.size == 0, f"{len(bad)} mismatching nodes, first {bad[:4].tolist()}"
@@ -489,6 +496,9 @@ def test_one_pass_3d_rbgs_bit_identical_to_generic_at_257(omega):
     bad = np.argwhere(coarse[0][1:-1, 1:-1, 1:-1] != coarse[1][1:-1, 1:-1, 1:-1])
     assert bad.size == 0, f"restriction: {len(bad)} mismatching coarse nodes, first {bad[:4].tolist()}"
     assert np.abs(coarse[0][1:-1, 1:-1, 1:-1]).max() > 0
+    bad = np.argwhere(corrected[0] != corrected[1])
+    assert bad.size == 0, f"prolongation: {len(bad)} mismatching nodes, first {bad[:4].tolist()}"
+    assert not np.array_equal(corrected[0], out[0])
 
 
 def test_concurrent_evaluations_are_bitwise_those_of_sequential_ones():
