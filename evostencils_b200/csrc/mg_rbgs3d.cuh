@@ -170,69 +170,62 @@ __global__ void __launch_bounds__(32 * (RY + 2)) k_rbgs3d(Geom g, Star3D st, con
     int e_m2 = 0, e_m = 0, e_s = U_SLOT, e_p = 2 * U_SLOT, e_f1 = 0, e_f = 0;
     uint32_t b_u = bar_a + 16, b_f = bar_a + 8 * RB3_NS;
     uint32_t par_u = 0, par_f = 0;
-    for (int s = zb - 1; s <= ze; ++s) {
+    // one step of the march with the red / black node in component C of the pair; the carried rows are
+    // explicit operands so that the loop below can be unrolled by two without moving them:
+    // (zm, c) original planes s-1, s -> nxt = plane s+1; (bz, b) red planes s-2, s-1 -> pr = red plane s;
+    // fq = f(s-1) -> fp = f(s)
+    auto step = [&](auto tag, const int s, const double2& zm, const double2& c, double2& nxt, const double2& bz,
+                    const double2& b, double2& pr, const double2& fq, double2& fp) {
+        constexpr int C = decltype(tag)::value;
         mbar_wait(b_u, par_u);
         mbar_wait(b_f, par_f);
         double* const us = su + e_s;
         const double* const um = su + e_m;
-        const double2 rn = *reinterpret_cast<const double2*>(su + e_p + o_row);
-        const double2 fp = *reinterpret_cast<const double2*>(sf + e_f + o_f);
-        const bool red_plane = s >= 1 && s <= n - 2;
+        nxt = *reinterpret_cast<const double2*>(su + e_p + o_row);
+        fp = *reinterpret_cast<const double2*>(sf + e_f + o_f);
         const int q = s - 1;
-        const bool black_plane = q >= zb && q < ze && black_warp;
-        const bool q_in = q >= 1 && q <= n - 2;
-        double2 pr = rc;                                                     // the row of plane s after red(s)
-
-        auto step = [&](auto tag) {
-            constexpr int C = decltype(tag)::value;
-            // ---- red(s): component C of the pair ----
-            if (red_plane) {
-                const double wv = C ? rc.x : __shfl_up_sync(0xffffffffu, rc.y, 1);
-                const double ev = C ? __shfl_down_sync(0xffffffffu, rc.x, 1) : rc.y;
-                const double sv = us[o_row + C - RB3_W], nv = us[o_row + C + RB3_W];
-                const double cen = rb3_get<C>(rc);
-                const double r = rb3_get<C>(fp) - star3_at(st, rb3_get<C>(rzm), sv, wv, cen, ev, nv, rb3_get<C>(rn));
-                const double v = cen + w * r;
-                if (ok & (1u << C)) {
-                    us[o_row + C] = v;
-                    if (C) pr.y = v; else pr.x = v;
-                }
+        pr = c;
+        // ---- red(s) ----
+        if (s >= 1 && s <= n - 2) {
+            const double wv = C ? c.x : __shfl_up_sync(0xffffffffu, c.y, 1);
+            const double ev = C ? __shfl_down_sync(0xffffffffu, c.x, 1) : c.y;
+            const double sv = us[o_row + C - RB3_W], nv = us[o_row + C + RB3_W];
+            const double cen = rb3_get<C>(c);
+            const double r = rb3_get<C>(fp) - star3_at(st, rb3_get<C>(zm), sv, wv, cen, ev, nv, rb3_get<C>(nxt));
+            const double v = cen + w * r;
+            if (ok & (1u << C)) {
+                us[o_row + C] = v;
+                if (C) pr.y = v; else pr.x = v;
             }
-            __syncthreads();
-            if (warp == NW - 1) {
-                // planes <= s-3 of u and <= s-2 of f are dead now: refill their slots (the proxy fence orders
-                // the red stores other warps made into them, visible here through the barrier, before the
-                // asynchronous writes)
-                fence_proxy_async();
-                if (s - 3 >= p0 && s - 3 + RB3_NS <= ze + 1) stage_u(s - 3 + RB3_NS, back(e_m2 / U_SLOT, 1, RB3_NS));
-                if (s - 2 >= fp0 && s - 2 + RB3_NF <= ze) stage_f(s - 2 + RB3_NF, back(e_f1 / F_SLOT, 1, RB3_NF));
-                if (pf > 0 && lane == 0 && s + pf <= imin(ze + 1, n - 1)) {     // the boxes of plane s+pf -> L2
-                    tma_prefetch_3d(&tm_u, xb - 2, yb - 2, s + pf);
-                    if (s + pf <= ze) tma_prefetch_3d(&tm_f, xb - 2, yb - 1, s + pf);
-                }
+        }
+        __syncthreads();
+        if (warp == NW - 1) {
+            // planes <= s-3 of u and <= s-2 of f are dead now: refill their slots (the proxy fence orders
+            // the red stores other warps made into them, visible here through the barrier, before the
+            // asynchronous writes)
+            fence_proxy_async();
+            if (s - 3 >= p0 && s - 3 + RB3_NS <= ze + 1) stage_u(s - 3 + RB3_NS, back(e_m2 / U_SLOT, 1, RB3_NS));
+            if (s - 2 >= fp0 && s - 2 + RB3_NF <= ze) stage_f(s - 2 + RB3_NF, back(e_f1 / F_SLOT, 1, RB3_NF));
+            if (pf > 0 && lane == 0 && s + pf <= imin(ze + 1, n - 1)) {     // the boxes of plane s+pf -> L2
+                tma_prefetch_3d(&tm_u, xb - 2, yb - 2, s + pf);
+                if (s + pf <= ze) tma_prefetch_3d(&tm_f, xb - 2, yb - 1, s + pf);
             }
-            // ---- black(s-1): component C of the pair, then the finished row of plane s-1 is stored ----
-            if (black_plane) {
-                const double wv = C ? bc.x : __shfl_up_sync(0xffffffffu, bc.y, 1);
-                const double ev = C ? __shfl_down_sync(0xffffffffu, bc.x, 1) : bc.y;
-                const double sv = um[o_row + C - RB3_W], nv = um[o_row + C + RB3_W];
-                const double cen = rb3_get<C>(bc);
-                const double r = rb3_get<C>(fq) - star3_at(st, rb3_get<C>(bzm), sv, wv, cen, ev, nv, rb3_get<C>(pr));
-                const double v = cen + w * r;
-                double2 o2 = bc;
-                if (q_in && (ok & (4u << C))) {
-                    if (C) o2.y = v; else o2.x = v;
-                }
-                if (ok & 16u) st2(optr, o2);
-                else if (ok & 32u) *optr = o2.x;
+        }
+        // ---- black(s-1), then the finished row of plane s-1 is stored ----
+        if (q >= zb && q < ze && black_warp) {
+            const double wv = C ? b.x : __shfl_up_sync(0xffffffffu, b.y, 1);
+            const double ev = C ? __shfl_down_sync(0xffffffffu, b.x, 1) : b.y;
+            const double sv = um[o_row + C - RB3_W], nv = um[o_row + C + RB3_W];
+            const double cen = rb3_get<C>(b);
+            const double r = rb3_get<C>(fq) - star3_at(st, rb3_get<C>(bz), sv, wv, cen, ev, nv, rb3_get<C>(pr));
+            const double v = cen + w * r;
+            double2 o2 = b;
+            if (q >= 1 && q <= n - 2 && (ok & (4u << C))) {
+                if (C) o2.y = v; else o2.x = v;
             }
-        };
-        if ((par_row + s) & 1) step(std::integral_constant<int, 1>{});
-        else step(std::integral_constant<int, 0>{});
-
-        rzm = rc; rc = rn;
-        bzm = bc; bc = pr;
-        fq = fp;
+            if (ok & 16u) st2(optr, o2);
+            else if (ok & 32u) *optr = o2.x;
+        }
         optr += plane;
         e_m2 = e_m; e_m = e_s; e_s = e_p;
         e_p += U_SLOT; b_u += 8;
@@ -240,7 +233,22 @@ __global__ void __launch_bounds__(32 * (RY + 2)) k_rbgs3d(Geom g, Star3D st, con
         e_f1 = e_f;
         e_f += F_SLOT; b_f += 8;
         if (e_f == RB3_NF * F_SLOT) { e_f = 0; b_f = bar_a + 8 * RB3_NS; par_f ^= 1; }
+    };
+    const std::integral_constant<int, 0> even;
+    const std::integral_constant<int, 1> odd;
+    double2 n1, n2, p1, p2, f1, f2;
+    int s = zb - 1;
+    if ((par_row + s) & 1) {                                                 // peel: the loop starts on component 0
+        step(odd, s, rzm, rc, n1, bzm, bc, p1, fq, f1);
+        rzm = rc; rc = n1; bzm = bc; bc = p1; fq = f1;
+        ++s;
     }
+    for (; s + 1 <= ze; s += 2) {
+        step(even, s, rzm, rc, n1, bzm, bc, p1, fq, f1);
+        step(odd, s + 1, rc, n1, n2, bc, p1, p2, f1, f2);
+        rzm = n1; rc = n2; bzm = p1; bc = p2; fq = f2;
+    }
+    if (s <= ze) step(even, s, rzm, rc, n1, bzm, bc, p1, fq, f1);
 }
 
 }  // namespace mg
