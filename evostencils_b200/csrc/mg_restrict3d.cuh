@@ -111,19 +111,23 @@ __global__ void __launch_bounds__(32 * (2 * RYC + 1)) k_resrestrict3d(Geom gc, G
     int u_slot = 0, f_slot = 0;                                             // slot numbers of plane z-1 of u / plane z of f
     uint32_t b_u = bar_a + 16, b_f = bar_a + 8 * NS;
     uint32_t par_u = 0, par_f = 0;
-    for (int z = z0; z <= z1; ++z) {
+    // one fine plane z of parity ODD (compile time: z0 is odd, the planes alternate); the carried rows are
+    // explicit operands so that the loop below can be unrolled by two without moving them:
+    // (zm, c) = the row in planes z-1, z -> nxt = plane z+1
+    auto step = [&](auto tag, const int z, const double2& zm, const double2& c, double2& nxt) {
+        constexpr bool ODD = decltype(tag)::value != 0;
         mbar_wait(b_u, par_u);
         mbar_wait(b_f, par_f);
         // ---- residual of the warp's row in plane z ----
-        const double2 rn = *reinterpret_cast<const double2*>(su + e_p + o_row);
+        nxt = *reinterpret_cast<const double2*>(su + e_p + o_row);
         const double2 s2 = *reinterpret_cast<const double2*>(su + e_c + o_row - RB3_W);
         const double2 n2 = *reinterpret_cast<const double2*>(su + e_c + o_row + RB3_W);
         const double2 f2 = *reinterpret_cast<const double2*>(sf + e_f + o_f);
-        const double left = __shfl_up_sync(0xffffffffu, rc.y, 1), right = __shfl_down_sync(0xffffffffu, rc.x, 1);
+        const double left = __shfl_up_sync(0xffffffffu, c.y, 1), right = __shfl_down_sync(0xffffffffu, c.x, 1);
         double2 r2;
-        r2.x = f2.x - star3_at(st, rzm.x, s2.x, left, rc.x, rc.y, n2.x, rn.x);
-        r2.y = f2.y - star3_at(st, rzm.y, s2.y, rc.x, rc.y, right, n2.y, rn.y);
-        double* const rb = sr + (z & 1) * F_SLOT;
+        r2.x = f2.x - star3_at(st, zm.x, s2.x, left, c.x, c.y, n2.x, nxt.x);
+        r2.y = f2.y - star3_at(st, zm.y, s2.y, c.x, c.y, right, n2.y, nxt.y);
+        double* const rb = sr + (ODD ? F_SLOT : 0);
         *reinterpret_cast<double2*>(rb + o_f) = r2;
         __syncthreads();
         if (warp == NW - 1) {
@@ -138,7 +142,7 @@ __global__ void __launch_bounds__(32 * (2 * RYC + 1)) k_resrestrict3d(Geom gc, G
             const double2 yp = *reinterpret_cast<const double2*>(rb + o_f + RB3_W);
             const double lm = __shfl_up_sync(0xffffffffu, ym.y, 1), l0 = __shfl_up_sync(0xffffffffu, r2.y, 1),
                          lp = __shfl_up_sync(0xffffffffu, yp.y, 1);
-            if (z & 1) {
+            if (ODD) {
                 const int Zdone = (z - 1) >> 1;                              // oz = +1 finishes the coarse plane below
                 if (Zdone >= Zb) {
                     const double v = rs3_plane_terms(acc, false, 0.25, lm, ym, l0, r2, lp, yp);
@@ -149,7 +153,6 @@ __global__ void __launch_bounds__(32 * (2 * RYC + 1)) k_resrestrict3d(Geom gc, G
                 acc = rs3_plane_terms(acc, false, 0.5, lm, ym, l0, r2, lp, yp);
             }
         }
-        rzm = rc; rc = rn;
         e_c = e_p;
         e_p += U_SLOT; b_u += 8;
         if (e_p == NS * U_SLOT) { e_p = 0; b_u = bar_a; par_u ^= 1; }
@@ -157,6 +160,15 @@ __global__ void __launch_bounds__(32 * (2 * RYC + 1)) k_resrestrict3d(Geom gc, G
         if (e_f == NF * F_SLOT) { e_f = 0; b_f = bar_a + 8 * NS; par_f ^= 1; }
         if (++u_slot == NS) u_slot = 0;
         if (++f_slot == NF) f_slot = 0;
+    };
+    const std::integral_constant<int, 0> even;
+    const std::integral_constant<int, 1> odd;
+    double2 n1, n2;
+    step(odd, z0, rzm, rc, n1);                                             // z0 and z1 are odd
+    for (int z = z0 + 1; z < z1; z += 2) {
+        step(even, z, rc, n1, n2);
+        step(odd, z + 1, n1, n2, rzm);
+        rc = n2; n1 = rzm;
     }
 }
 
