@@ -50,7 +50,8 @@ def parse_args():
     ap.add_argument("--max-level", type=int, default=12)
     ap.add_argument("--grammar-depth", type=int, default=5)
     ap.add_argument("--engine-min-level", type=int, default=2)
-    ap.add_argument("--cpu-sample-cycles", type=int, default=2)
+    ap.add_argument("--cpu-sample-cycles", type=int, default=40,
+                    help="CPU legs: cycles per sample (40 cycles = ~25 core-seconds on 16 cores)")
     ap.add_argument("--generic-kernels", action="store_true", help="disable the specialised kernels")
     ap.add_argument("--no-prefetch", action="store_true",
                     help="e2e leg: upload the inputs synchronously instead of one evaluation ahead on a copy stream")
@@ -394,55 +395,71 @@ def run_stages(args):
     print(json.dumps({"stages": stages, "peak": peak, "peak_source": peak_src, "level": hi, "reps": args.stage_reps}))
 
 
+class CpuPort:
+    """C/OpenMP oracle port on the host cores (all of them): cycles of the reference V(2,1) RB-GS
+    individual (population[0]) at the bench size, one loop nest per unfused statement -- the
+    granularity of the code ExaStencils generates.  Set up once, timed per call of `run`."""
+
+    def __init__(self, args):
+        from evostencils_b200 import engine, lowering, problems
+        from evostencils_b200.grammar import Grammar
+        oracle_dir = os.path.join(ROOT, "oracle")
+        lib_path = os.path.join(oracle_dir, "_build", "libmgoracle.so")
+        try:
+            subprocess.run(["make", "-s", "-B", "-C", oracle_dir, "MARCH=native"], check=True, capture_output=True, timeout=120)
+        except Exception:
+            if not os.path.exists(lib_path):
+                raise
+        self.cores = len(os.sched_getaffinity(0))
+        os.environ.setdefault("OMP_NUM_THREADS", str(self.cores))
+        clib = engine.load_library(lib_path)
+        problem = problems.POISSON_2D
+        self.hi = hi = args.max_level
+        lo = hi - args.grammar_depth
+        elo = args.engine_min_level
+        grammar = Grammar(problem, lo, hi, maximum_local_system_size=4)
+        program = lowering.lower(grammar.compile(load_population()[0])[0], lo, hi)
+        self.ws = ws = engine.Workspace(2, elo, hi, 1, "f64", 0, lib=clib)
+        for level in range(elo, hi + 1):
+            ws.set_operator(level, lowering.operator_table(problem.system_operator(level, 0)))
+        ws.set_coarse_solver("CG", 1000, 1e-12)
+        us, fs = synthetic_inputs(problem, hi, pinned=False)
+        ws.upload("sol", hi, 0, us[0])
+        ws.upload("rhs", hi, 0, fs[0])
+        self.cycle = ws.build_cycle(program.ops, lambda level: lowering.default_cycle_ops(problem, level, elo), fused=False)
+        ws.run_cycles(self.cycle, 1)                      # warm-up (page faults)
+
+    def run(self, n):
+        ms = self.ws.run_cycles(self.cycle, n)
+        dof = float((2 ** self.hi - 1) ** 2)
+        return {"value": dof * n / (ms * 1e-3), "unit": UNIT, "cores": self.cores, "kind": "port",
+                "sample": "%d cycles (+ residual norm) of population[0] = V(2,1) RB-GS w=1.15 at %d^2, "
+                          "C/OpenMP oracle port, unfused statements" % (n, 2 ** self.hi),
+                "ms_per_cycle": ms / n}
+
+    def close(self):
+        self.ws.close()
+
+
 def cpu_baseline(args, sample_only=False):
-    """C/OpenMP oracle port on the host cores: `cpu_sample_cycles` cycles of the reference V(2,1)
-    RB-GS individual (population[0]) at the bench size."""
-    from evostencils_b200 import engine, lowering, problems
-    from evostencils_b200.grammar import Grammar
-    oracle_dir = os.path.join(ROOT, "oracle")
-    lib_path = os.path.join(oracle_dir, "_build", "libmgoracle.so")
+    port = CpuPort(args)
     try:
-        subprocess.run(["make", "-s", "-B", "-C", oracle_dir, "MARCH=native"], check=True, capture_output=True, timeout=120)
-    except Exception:
-        if not os.path.exists(lib_path):
-            raise
-    cores = len(os.sched_getaffinity(0))
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
-    clib = engine.load_library(lib_path)
-    problem = problems.POISSON_2D
-    hi = args.max_level
-    lo = hi - args.grammar_depth
-    elo = args.engine_min_level
-    grammar = Grammar(problem, lo, hi, maximum_local_system_size=4)
-    program = lowering.lower(grammar.compile(load_population()[0])[0], lo, hi)
-    ws = engine.Workspace(2, elo, hi, 1, "f64", 0, lib=clib)
-    for level in range(elo, hi + 1):
-        ws.set_operator(level, lowering.operator_table(problem.system_operator(level, 0)))
-    ws.set_coarse_solver("CG", 1000, 1e-12)
-    us, fs = synthetic_inputs(problem, hi, pinned=False)
-    ws.upload("sol", hi, 0, us[0])
-    ws.upload("rhs", hi, 0, fs[0])
-    cycle = ws.build_cycle(program.ops, lambda level: lowering.default_cycle_ops(problem, level, elo), fused=False)
-    ws.run_cycles(cycle, 1)                      # warm-up (page faults)
-    n = args.cpu_sample_cycles
-    ms = ws.run_cycles(cycle, n)
-    ws.close()
-    dof = float((2 ** hi - 1) ** 2)
-    return {"value": dof * n / (ms * 1e-3), "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "%d cycles (+ residual norm) of population[0] = V(2,1) RB-GS w=1.15 at %d^2, "
-                      "C/OpenMP oracle port, unfused statements" % (n, 2 ** hi),
-            "ms_per_cycle": ms / n}
+        return port.run(args.cpu_sample_cycles)
+    finally:
+        port.close()
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    port = CpuPort(args)
     for _ in range(args.warmup):
-        cpu_baseline(args)
+        port.run(args.cpu_sample_cycles)
     t0 = time.perf_counter()
-    vals = [cpu_baseline(args) for _ in range(args.steps)]
+    vals = [port.run(args.cpu_sample_cycles) for _ in range(args.steps)]
     wall = (time.perf_counter() - t0) * 1e3
+    port.close()
     value = float(np.mean([v["value"] for v in vals]))
     cpu = dict(vals[-1])
     cpu["value"] = value
