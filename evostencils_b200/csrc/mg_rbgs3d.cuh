@@ -7,17 +7,23 @@
 //   * A CTA owns a tile of TW = 60 columns x RY rows and marches over a chunk of z planes.  Per plane
 //     it keeps RY+4 rows x 64 columns of u (halo of 2: the black update of a node needs the red
 //     values at distance 1, which need the original values at distance 2) and RY+2 rows of f.
-//   * Planes are staged by TMA: every row of a plane tile is one `cp.async.bulk` (512 B, global ->
-//     shared) that completes on the plane's mbarrier; NS = 6 planes of u and NF = 5 of f form rings,
-//     a slot is refilled as soon as its plane is dead, so 2-3 planes are always in flight while
-//     the warps compute.  No thread ever waits on a global load.
+//   * Planes are staged by TMA through a tensor map of the whole array (host: cuTensorMapEncodeTiled,
+//     mg_kernels_fast.cuh): one `cp.async.bulk.tensor.3d` box per plane tile of u and one of f, issued by
+//     one lane, completing on the ring slot's mbarrier; rows, columns and planes outside the grid arrive
+//     as zeros.  Rings of NS planes of u and NF of f; a slot is re-armed right after the barrier that
+//     retires its plane, so about 3 planes are in flight while the warps compute.  No thread ever
+//     waits on a global load.  (One 512-byte `cp.async.bulk` per row -- 22 copies per plane, serialised
+//     lane by lane through the uniform datapath -- cost 1.03 ms per sweep at 513^3 against 0.66.)
 //   * Step s of the march: red(s) updates the red nodes of plane s in place in shared memory (red
 //     nodes read only black nodes, which the red half-sweep leaves alone, so planes s-1, s, s+1 may be
 //     in any red state); after one __syncthreads, black(s-1) reads the red nodes of planes s-2, s-1, s
 //     around every black node of plane s-1 and writes the finished plane s-1 (both colours, boundary
 //     nodes copied) to `out`.  Black results never go back to shared memory: nothing reads them.
-//   * One warp per tile row: lane j holds the aligned column pair (xb-2+2j, xb-1+2j); x neighbours come
-//     from the adjacent lane by shuffle, y and z neighbours from shared memory.
+//   * One warp per tile row, in both half-sweeps: lane j holds the aligned column pair (xb-2+2j,
+//     xb-1+2j) of its row in the planes around s in registers (see k_rbgs3d); x neighbours come from the
+//     adjacent lane by shuffle, only the y neighbours (rows of other warps) from shared memory.  The
+//     component of the pair that is red in plane s (= black in plane s-1) alternates from plane to
+//     plane: the plane loop is unrolled by two with the component as a template argument.
 //   * Red values in the halo (rows yb-1 and yb+RY, columns xb-1 and xb+60, planes zb-1 and ze) are
 //     recomputed by this CTA from the same inputs as their owner uses: bit-identical to two
 //     sequential colour passes (operand order of star3_at, separate multiply and add).
@@ -62,7 +68,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 constexpr int RB3_TW = 60;     // output columns per tile
-constexpr int RB3_W = 64;      // staged columns per row (xb-2 .. xb+61): 512 B, one bulk copy
+constexpr int RB3_W = 64;      // staged columns per row (xb-2 .. xb+61)
 
 template <int RY, int RB3_NS, int RB3_NF>      // RB3_NS / RB3_NF: ring sizes of u / f planes
 constexpr size_t rbgs3d_smem_bytes() {
