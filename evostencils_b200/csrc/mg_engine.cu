@@ -180,6 +180,7 @@ extern "C" int mg_destroy(mg_workspace* ws) {
         if (lv.partial) cudaFree(lv.partial);
     }
     if (ws->cgs_work) cudaFree(ws->cgs_work);
+    for (void* p : ws->fas_raw) cudaFree(p);
     delete ws->tail;
     if (ws->tail_pool) cudaFree(ws->tail_pool);
     if (ws->tail_stage) cudaFreeHost(ws->tail_stage);
@@ -331,3 +332,4 @@ extern "C" int mg_clear_smoothers(mg_workspace* ws) {
 }
 
 #include "mg_engine_run.inc"
+#include "mg_engine_fas.inc"

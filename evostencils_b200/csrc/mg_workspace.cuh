@@ -137,6 +137,9 @@ struct mg_workspace {
     int outer_graph_cycle = -1;
     long long outer_graph_kernels = 0;
     size_t cgs_smem_bytes = 0;                  // dynamic shared memory of the coarse solver (0: global scratch)
+    // nonlinear FAS stages (mg_fas.cuh): Approximation field per level, allocated on first use
+    std::vector<void*> fas_approx;              // index = level - min_level (points past the guard rows)
+    std::vector<void*> fas_raw;                 // the allocations behind them
 
     mg::Level& L(int level) { return levels[level - min_level]; }
     bool has_level(int level) const { return level >= min_level && level <= max_level; }

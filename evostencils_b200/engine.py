@@ -35,6 +35,7 @@ EXPORTED_SYMBOLS = [
     "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_set_outer_operator",
     "mg_solve_bicgstab", "mg_synchronize",
     "mg_time_ops", "mg_profile_ops", "mg_mark", "mg_elapsed", "mg_flush_l2", "mg_set_fast_kernels",
+    "mg_fas_smooth", "mg_fas_residual", "mg_fas_restrict", "mg_fas_subtract_approximation", "mg_fas_residual_norm",
 ]
 
 
@@ -99,6 +100,12 @@ def load_library(path: Optional[str] = None):
     lib.mg_elapsed.argtypes = [vp, C.POINTER(C.c_float)]
     lib.mg_flush_l2.argtypes = [vp, C.c_size_t]
     lib.mg_set_fast_kernels.argtypes = [vp, i32]
+    if path == LIB_PATH or hasattr(lib, "mg_fas_smooth"):       # nonlinear FAS stages: CUDA engine only
+        lib.mg_fas_smooth.argtypes = [vp, i32, dbl, dbl, i32]
+        lib.mg_fas_residual.argtypes = [vp, i32, dbl]
+        lib.mg_fas_restrict.argtypes = [vp, i32, dbl]
+        lib.mg_fas_subtract_approximation.argtypes = [vp, i32]
+        lib.mg_fas_residual_norm.argtypes = [vp, i32, dbl, C.POINTER(dbl)]
     if path == LIB_PATH:
         _lib = lib
     return lib
@@ -435,6 +442,24 @@ class Workspace:
 
     def flush_l2(self, nbytes=256 << 20):
         self._check(self.lib.mg_flush_l2(self._h, nbytes))
+
+    # -- nonlinear FAS stages (mg_fas.cuh; FAS_2D_Basic.exa4) ------------------------------------
+    def fas_smooth(self, level, omega, gamma, sweeps=1):
+        self._check(self.lib.mg_fas_smooth(self._h, level, omega, gamma, sweeps))
+
+    def fas_residual(self, level, gamma):
+        self._check(self.lib.mg_fas_residual(self._h, level, gamma))
+
+    def fas_restrict(self, coarse_level, gamma):
+        self._check(self.lib.mg_fas_restrict(self._h, coarse_level, gamma))
+
+    def fas_subtract_approximation(self, level):
+        self._check(self.lib.mg_fas_subtract_approximation(self._h, level))
+
+    def fas_residual_norm(self, level, gamma) -> float:
+        out = C.c_double()
+        self._check(self.lib.mg_fas_residual_norm(self._h, level, gamma, C.byref(out)))
+        return out.value
 
     def set_fast_kernels(self, enabled: bool, tail=None):
         """Specialised kernels on/off; `tail` (default: same as `enabled`) selects the single-CTA

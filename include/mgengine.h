@@ -170,6 +170,25 @@ int mg_flush_l2(mg_workspace* ws, size_t bytes);
  * (default 3 = both; 0 = generic grid kernels only) */
 int mg_set_fast_kernels(mg_workspace* ws, int enabled);
 
+/* ---- nonlinear FAS stages ------------------------------------------ */
+/* -Laplace(u) + gamma u e^u = f: the statements of example_problems/FAS_2D_Basic/FAS_2D_Basic.exa4
+ * (replaces the Layer-4 text ProgramGeneratorFAS.traverse_graph emits, code_generation/
+ * exastencils_FAS.py:99-319, and the ExaStencils compile behind it).  2D scalar MG_F64 workspaces whose
+ * operator on the level is the 5-point Laplace star; direct launches on the workspace stream. */
+/* `sweeps` damped Jacobi-Newton sweeps (.exa4:65-75; 30 of them = CGS@coarsest, :58-63) */
+int mg_fas_smooth(mg_workspace* ws, int level, double omega, double gamma, int sweeps);
+/* Residual@level = RHS - (L u + gamma e^u u), boundary 0 (.exa4:77-82) */
+int mg_fas_residual(mg_workspace* ws, int level, double gamma);
+/* `level` = the coarse level: Approximation = R Solution@(level+1); Solution@level = Approximation;
+ * RHS@level = R Residual@(level+1) + (L Approximation + gamma e^Approximation Approximation)
+ * (.exa4:219-227; exastencils_FAS.py:120-149) */
+int mg_fas_restrict(mg_workspace* ws, int level, double gamma);
+/* Solution@level -= Approximation@level (.exa4:247-249; exastencils_FAS.py:174-184); the correction is
+ * then prolongated with an MG_OP_PROLONG_ADD op */
+int mg_fas_subtract_approximation(mg_workspace* ws, int level);
+/* sqrt(sum over interior nodes of (RHS - (L u + gamma e^u u))^2) (.exa4:83-89); synchronises */
+int mg_fas_residual_norm(mg_workspace* ws, int level, double gamma, double* out);
+
 #ifdef __cplusplus
 }
 #endif
