@@ -1,0 +1,49 @@
+#!/usr/bin/env python
+"""The reference's nonlinear example `example_problems/FAS_2D_Basic` on the GPU engine: FAS V(pre, post)
+cycle with the damped Jacobi-Newton smoother of `FAS_2D_Basic.exa4`, solved until the `.exa4`'s
+stopping rule holds; prints the two lines the generated binary prints (:185-186), which
+`ProgramGeneratorFAS.generate_and_evaluate` parses (exastencils_FAS.py:369-426).  Levels default to
+the `.knowledge` file's (minLevel 6, maxLevel 10).  `--cpu` also times the numpy restatement
+(oracle/fas_oracle.py) of the same solve on the host, as the CPU figure beside the GPU one."""
+import argparse
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__.split("\n")[0])
+    ap.add_argument("--min-level", type=int, default=6)
+    ap.add_argument("--max-level", type=int, default=10)
+    ap.add_argument("--pre", type=int, default=2)
+    ap.add_argument("--post", type=int, default=2)
+    ap.add_argument("--nruns", type=int, default=5)
+    ap.add_argument("--cpu", action="store_true", help="time the numpy restatement too (test infrastructure, one run)")
+    ap.add_argument("--device", type=int, default=0)
+    a = ap.parse_args(argv)
+    from evostencils_b200 import fas
+    solver = fas.FasSolver(a.min_level, a.max_level, device=a.device)
+    ops = fas.v_cycle_ops(a.max_level, a.min_level, a.pre, a.post)
+    solver.solve(ops)                                   # warm-up
+    best = None
+    for _ in range(a.nruns):
+        solver.reset()
+        history, ms = solver.solve(ops)
+        best = ms if best is None else min(best, ms)
+    error = float(abs(solver.solution() - fas.exact_solution(a.max_level)).max())
+    solver.close()
+    print("total no of iterations", len(history) - 1)
+    print("time to solution (in ms) is", best)
+    print(f"residual reduction {history[-1] / history[0]:.3e}, max error against solFct {error:.3e}")
+    if a.cpu:
+        from oracle import fas_oracle
+        t0 = time.perf_counter()
+        _, want = fas_oracle.solve(a.max_level, a.min_level, a.pre, a.post)
+        print(f"numpy restatement on the host: {len(want) - 1} iterations, {(time.perf_counter() - t0) * 1e3:.1f} ms")
+    return len(history) - 1, best
+
+
+if __name__ == "__main__":
+    main()
