@@ -61,9 +61,12 @@ def exact_solution(level: int) -> np.ndarray:
 
 
 def v_cycle_ops(max_level: int, min_level: int, pre: int = 2, post: int = 2, omega: float = SMOOTHER_WEIGHT,
-                cgs_sweeps: int = CGS_SWEEPS) -> List[FasOp]:
+                cgs_sweeps: int = CGS_SWEEPS, cgc_omega: float = 1.0) -> List[FasOp]:
     """The statement sequence of `gen_mgCycle@finest` for a FAS V(pre, post) cycle, in the order
-    `traverse_graph` emits it (.exa4:210-269 for max_level 5, min_level 3, pre = post = 2)."""
+    `traverse_graph` emits it (.exa4:210-269 for max_level 5, min_level 3, pre = post = 2; pinned on
+    listings emitted by the unmodified reference for FAS grammar strings, tests/golden/fas_golden.json).
+    `cgc_omega` = relaxation factor of the coarse-grid correction (`Solution += w * (P * Solution_c)`,
+    exastencils_FAS.py:104-118; the hand-written sample has none)."""
     ops: List[FasOp] = []
 
     def visit(level):
@@ -75,7 +78,7 @@ def v_cycle_ops(max_level: int, min_level: int, pre: int = 2, post: int = 2, ome
         ops.append(FasOp("restrict", level - 1))                             # approximation, solution and rhs of level-1
         visit(level - 1)
         ops.append(FasOp("subtract", level - 1))
-        ops.append(FasOp("prolong_add", level))
+        ops.append(FasOp("prolong_add", level, cgc_omega))
         ops.append(FasOp("smooth", level, omega, post))
 
     visit(max_level)
@@ -111,7 +114,7 @@ class FasSolver:
             elif op.kind == "subtract":
                 ws.fas_subtract_approximation(op.level)
             elif op.kind == "prolong_add":
-                ws.exec_ops([lowering.Op("prolong_add", op.level, omega=1.0, src="sol", dst="sol")])
+                ws.exec_ops([lowering.Op("prolong_add", op.level, omega=op.omega, src="sol", dst="sol")])
             else:
                 raise ValueError(f"unknown FAS op '{op.kind}'")
 

@@ -93,15 +93,16 @@ def restrict(fine):
     return out
 
 
-def prolong_add(u, coarse):
-    """u += P coarse on the interior fine nodes: 2^-k * (sum of the enclosing coarse nodes in memory order)."""
+def prolong_add(u, coarse, omega=1.0):
+    """u += omega * (P coarse) on the interior fine nodes: P = 2^-k * (sum of the enclosing coarse nodes in
+    memory order)."""
     n = u.shape[0]
     out = u.copy()
     e = coarse
-    out[2:n - 1:2, 2:n - 1:2] += e[1:-1, 1:-1]                                         # even, even
-    out[2:n - 1:2, 1:n - 1:2] += 0.5 * (e[1:-1, :-1] + e[1:-1, 1:])                    # odd x
-    out[1:n - 1:2, 2:n - 1:2] += 0.5 * (e[:-1, 1:-1] + e[1:, 1:-1])                    # odd y
-    out[1:n - 1:2, 1:n - 1:2] += 0.25 * (((e[:-1, :-1] + e[:-1, 1:]) + e[1:, :-1]) + e[1:, 1:])
+    out[2:n - 1:2, 2:n - 1:2] += omega * e[1:-1, 1:-1]                                 # even, even
+    out[2:n - 1:2, 1:n - 1:2] += omega * (0.5 * (e[1:-1, :-1] + e[1:-1, 1:]))          # odd x
+    out[1:n - 1:2, 2:n - 1:2] += omega * (0.5 * (e[:-1, 1:-1] + e[1:, 1:-1]))          # odd y
+    out[1:n - 1:2, 1:n - 1:2] += omega * (0.25 * (((e[:-1, :-1] + e[:-1, 1:]) + e[1:, :-1]) + e[1:, 1:]))
     return out
 
 
@@ -109,7 +110,8 @@ def norm(r):
     return float(np.sqrt(np.sum(r[1:-1, 1:-1] * r[1:-1, 1:-1])))
 
 
-def cycle(u, f, level, min_level, pre, post, gamma=GAMMA, weight=SMOOTHER_WEIGHT, cgs_sweeps=CGS_SWEEPS):
+def cycle(u, f, level, min_level, pre, post, gamma=GAMMA, weight=SMOOTHER_WEIGHT, cgs_sweeps=CGS_SWEEPS,
+          cgc_omega=1.0):
     """One FAS V(pre, post) cycle (gen_mgCycle of the .exa4, any depth)."""
     if level == min_level:
         for _ in range(cgs_sweeps):
@@ -121,21 +123,21 @@ def cycle(u, f, level, min_level, pre, post, gamma=GAMMA, weight=SMOOTHER_WEIGHT
     approx = restrict(u)
     f_c = restrict(r)
     f_c[1:-1, 1:-1] = f_c[1:-1, 1:-1] + apply_operator(approx, level - 1, gamma)[1:-1, 1:-1]
-    u_c = cycle(approx.copy(), f_c, level - 1, min_level, pre, post, gamma, weight, cgs_sweeps)
+    u_c = cycle(approx.copy(), f_c, level - 1, min_level, pre, post, gamma, weight, cgs_sweeps, cgc_omega)
     u_c = u_c - approx
-    u = prolong_add(u, u_c)
+    u = prolong_add(u, u_c, cgc_omega)
     for _ in range(post):
         u = smooth(u, f, level, gamma, weight)
     return u
 
 
 def solve(level, min_level, pre=2, post=2, gamma=GAMMA, weight=SMOOTHER_WEIGHT, cgs_sweeps=CGS_SWEEPS,
-          target=1e-10, max_iterations=100):
+          target=1e-10, max_iterations=100, cgc_omega=1.0):
     """-> (solution, residual history); the Solve function of the .exa4 (:118-187)."""
     f = right_hand_side(level, gamma)
     u = np.zeros_like(f)
     history = [norm(residual(u, f, level, gamma))]
     while not (history[-1] < target * history[0] or len(history) - 1 >= max_iterations):
-        u = cycle(u, f, level, min_level, pre, post, gamma, weight, cgs_sweeps)
+        u = cycle(u, f, level, min_level, pre, post, gamma, weight, cgs_sweeps, cgc_omega)
         history.append(norm(residual(u, f, level, gamma)))
     return u, history

@@ -17,6 +17,79 @@ def test_cycle_statement_order_is_that_of_the_generated_listing():
                    ("subtract", 4, 1), ("prolong_add", 5, 1), ("smooth", 5, 2)]
 
 
+def parse_layer4(text):
+    """Statement sequence of a cycle function emitted by the reference's ProgramGeneratorFAS:
+    (kind, level of the field written, count or factor)."""
+    import re
+    out = []
+    for line in text.splitlines():
+        line = line.strip()
+        m = re.match(r"Smoother@(\d+) \(", line)
+        if m:
+            level = int(m.group(1))
+            if out and out[-1][0] == "smooth" and out[-1][1] == level:
+                out[-1] = ("smooth", level, out[-1][2] + 1)
+            else:
+                out.append(("smooth", level, 1))
+            continue
+        m = re.match(r"CGS@(\d+) \(", line)
+        if m:
+            out.append(("cgs", int(m.group(1)), 1))
+            continue
+        m = re.match(r"Residual@(\d+) = \( RHS@\1 - \( \( Laplace@\1 \* Solution@\1 \) \+ \( gamSten@\1 \* Solution@\1 \) \) \)", line)
+        if m:
+            out.append(("residual", int(m.group(1)), 1))
+            continue
+        m = re.match(r"Approximation@(\d+) = \( RestrictionNode@(\d+) \* Solution@\d+ \)", line)
+        if m:
+            assert int(m.group(2)) == int(m.group(1)) + 1
+            out.append(("restrict_solution", int(m.group(1)), 1))
+            continue
+        m = re.match(r"RHS@(\d+) = \( \( RestrictionNode@(\d+) \* Residual@\2 \) \+ \( \( Laplace@\1 \* Approximation@\1 \) "
+                     r"\+ \( gamSten@\1 \* Approximation@\1 \) \) \)", line)
+        if m:
+            assert out[-1] == ("restrict_solution", int(m.group(1)), 1)      # the two loops of one `restrict` op
+            out[-1] = ("restrict", int(m.group(1)), 1)
+            continue
+        m = re.match(r"Solution@(\d+) -= Approximation@\1", line)
+        if m:
+            out.append(("subtract", int(m.group(1)), 1))
+            continue
+        m = re.match(r"Solution@(\d+) \+= \( ([0-9.e-]+) \* \( CorrectionNode@(\d+) \* Solution@\3 \) \)", line)
+        if m:
+            assert int(m.group(3)) == int(m.group(1)) - 1
+            out.append(("prolong_add", int(m.group(1)), float(m.group(2))))
+            continue
+        assert line == "" or line == "}" or line.startswith(("Function", "loop over", "apply bc", "communicate",
+                                                             "Solution@")), line
+    return out
+
+
+def test_cycle_statement_order_is_that_of_the_reference_emitter():
+    """tests/golden/fas_golden.json: Layer-4 text emitted by the unmodified reference
+    (`ProgramGeneratorFAS.generate_cycle_function`) for FAS V-cycles written in its FAS grammar."""
+    import json
+    import os
+    golden = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "fas_golden.json")))
+    assert len(golden) >= 4
+    for name, case in golden.items():
+        want = parse_layer4(case["layer4"])
+        factors = {w for kind, _, w in want if kind == "prolong_add"}
+        assert len(factors) == 1, name
+        ops = fas.v_cycle_ops(case["max_level"], case["min_level"], case["pre"], case["post"], cgc_omega=factors.pop())
+        got = []
+        for op in ops:
+            if op.kind == "smooth" and op.level == case["min_level"]:
+                got.append(("cgs", op.level, 1))                    # CGS@coarsest = 30 sweeps of the smoother
+            elif op.kind == "smooth":
+                got.append(("smooth", op.level, op.sweeps))
+            elif op.kind == "prolong_add":
+                got.append(("prolong_add", op.level, op.omega))
+            else:
+                got.append((op.kind, op.level, 1))
+        assert got == want, name
+
+
 def test_oracle_converges_to_the_discretisation_error():
     from oracle import fas_oracle as fo
     errors = []
@@ -94,12 +167,12 @@ def test_fas_stages_match_the_oracle(level):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("lo,hi,pre,post", [(3, 5, 2, 2), (3, 7, 2, 2), (4, 8, 1, 1)])
-def test_fas_solve_matches_the_oracle(lo, hi, pre, post):
+@pytest.mark.parametrize("lo,hi,pre,post,cgc", [(3, 5, 2, 2, 1.0), (3, 7, 2, 2, 1.0), (4, 8, 1, 1, 1.0), (3, 6, 1, 2, 0.7)])
+def test_fas_solve_matches_the_oracle(lo, hi, pre, post, cgc):
     from oracle import fas_oracle as fo
     solver = fas.FasSolver(lo, hi)
-    history, ms = solver.solve(fas.v_cycle_ops(hi, lo, pre, post))
-    u_ref, want = fo.solve(hi, lo, pre, post)
+    history, ms = solver.solve(fas.v_cycle_ops(hi, lo, pre, post, cgc_omega=cgc))
+    u_ref, want = fo.solve(hi, lo, pre, post, cgc_omega=cgc)
     assert len(history) == len(want)                                # identical iteration count
     assert np.all(np.abs(np.array(history) - np.array(want)) <= 1e-10 * np.array(want) + 1e-13 * want[0])
     assert close(solver.solution(), u_ref, 1e-11)
