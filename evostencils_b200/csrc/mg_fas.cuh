@@ -26,17 +26,36 @@ __device__ __forceinline__ double fas_apply(const FasStar& s, const double* __re
     return a + (s.gam * exp(c)) * c;
 }
 
-// Solution<next> = u + w (f - (L u + gam e^u u)) / (diag(L) + gam (1 + u) e^u)   (.exa4:68-75); boundary copied
-__global__ void k_fas_smooth(Geom g, FasStar s, const double* __restrict__ u, const double* __restrict__ f,
-                             double* __restrict__ out, double w) {
+// One sweep of the smoother `traverse_graph` emits (exastencils_FAS.py:186-246) or the template's
+// Smoother function (.exa4:65-75 = one Newton step, colour < 0):
+//   newton_steps >= 1: Jacobi-Newton, that many in-place updates of the centre value per node
+//                      u += w (f - (L u + gam e^u u)) / (diag(L) + gam (u + 1) e^u), neighbours fixed;
+//   newton_steps == 0: Jacobi-Picard, one update with the denominator diag(L);
+//   colour < 0: Jacobi (reads u, writes out, boundary copied); colour 0 / 1: in-place pass (out == u) over
+//   the interior nodes with (x + y) % 2 == colour, whose neighbours all have the other colour.
+__global__ void k_fas_smooth(Geom g, FasStar s, const double* u, const double* __restrict__ f, double* out, double w,
+                             int newton_steps, int colour) {
     int x, y, z;
     if (!node_coords<2>(g, x, y, z)) return;
     const long long i = node_index<2>(g, x, y, 0);
+    const bool interior = is_interior<2>(g, x, y, 0);
+    if (colour >= 0 && (!interior || ((x + y) & 1) != colour)) return;
     double v = u[i];
-    if (is_interior<2>(g, x, y, 0)) {
-        const double num = f[i] - fas_apply(s, u, i, g.pitch);
-        const double den = s.cc + s.gam * (1.0 + v) * exp(v);
-        v = v + w * (num / den);
+    if (interior) {
+        const double e = s.cx * u[i + 1], wt = s.cx * u[i - 1], nt = s.cy * u[i + g.pitch], st = s.cy * u[i - g.pitch];
+        const double fi = f[i];
+        const int steps = newton_steps > 0 ? newton_steps : 1;
+        for (int k = 0; k < steps; ++k) {
+            double a = s.cc * v;
+            a = a + e;
+            a = a + wt;
+            a = a + nt;
+            a = a + st;
+            const double ev = exp(v);
+            const double num = fi - (a + (s.gam * ev) * v);
+            const double den = newton_steps > 0 ? s.cc + s.gam * (v + 1.0) * ev : s.cc;
+            v = v + w * (num / den);
+        }
     }
     out[i] = v;
 }

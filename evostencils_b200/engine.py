@@ -101,7 +101,7 @@ def load_library(path: Optional[str] = None):
     lib.mg_flush_l2.argtypes = [vp, C.c_size_t]
     lib.mg_set_fast_kernels.argtypes = [vp, i32]
     if path == LIB_PATH or hasattr(lib, "mg_fas_smooth"):       # nonlinear FAS stages: CUDA engine only
-        lib.mg_fas_smooth.argtypes = [vp, i32, dbl, dbl, i32]
+        lib.mg_fas_smooth.argtypes = [vp, i32, dbl, dbl, i32, i32, i32]
         lib.mg_fas_residual.argtypes = [vp, i32, dbl]
         lib.mg_fas_restrict.argtypes = [vp, i32, dbl]
         lib.mg_fas_subtract_approximation.argtypes = [vp, i32]
@@ -444,8 +444,8 @@ class Workspace:
         self._check(self.lib.mg_flush_l2(self._h, nbytes))
 
     # -- nonlinear FAS stages (mg_fas.cuh; FAS_2D_Basic.exa4) ------------------------------------
-    def fas_smooth(self, level, omega, gamma, sweeps=1):
-        self._check(self.lib.mg_fas_smooth(self._h, level, omega, gamma, sweeps))
+    def fas_smooth(self, level, omega, gamma, sweeps=1, newton_steps=1, colored=False):
+        self._check(self.lib.mg_fas_smooth(self._h, level, omega, gamma, sweeps, newton_steps, 1 if colored else 0))
 
     def fas_residual(self, level, gamma):
         self._check(self.lib.mg_fas_residual(self._h, level, gamma))

@@ -35,6 +35,9 @@ class FasOp:
     level: int                # level of the field that is written
     omega: float = 1.0
     sweeps: int = 1
+    newton_steps: int = 1     # smooth: local Newton updates per node; 0 = Jacobi-Picard
+    colored: bool = False     # smooth: red-black in place instead of Jacobi
+    cgs: bool = False         # smooth: this is the call of CGS@coarsest
 
 
 def laplace_table(level: int) -> list:
@@ -71,7 +74,7 @@ def v_cycle_ops(max_level: int, min_level: int, pre: int = 2, post: int = 2, ome
 
     def visit(level):
         if level == min_level:
-            ops.append(FasOp("smooth", level, omega, cgs_sweeps))            # CGS@coarsest
+            ops.append(FasOp("smooth", level, omega, cgs_sweeps, cgs=True))  # CGS@coarsest
             return
         ops.append(FasOp("smooth", level, omega, pre))
         ops.append(FasOp("residual", level))
@@ -83,6 +86,119 @@ def v_cycle_ops(max_level: int, min_level: int, pre: int = 2, post: int = 2, ome
 
     visit(max_level)
     return ops
+
+
+# ----------------------------------------------------------------------------------------
+# IR graph -> statement list
+# ----------------------------------------------------------------------------------------
+
+class _Lowerer:
+    """Walks a FAS `Cycle` graph the way `ProgramGeneratorFAS.traverse_graph` does
+    (exastencils_FAS.py:99-319) and records a `FasOp` where that function appends a Layer-4
+    statement.  The graph may consist of `evostencils_b200.ir` objects or of the reference's own
+    `evostencils.ir` objects: nodes are recognised by class name, like there."""
+
+    def __init__(self, template_smoother: bool, cgs_sweeps: int):
+        self.ops: List[FasOp] = []
+        self.template_smoother = template_smoother
+        self.cgs_sweeps = cgs_sweeps
+        self.rhs_pending = {}                # level -> the coarse right-hand side must be (re)computed (:40, 138-146)
+        self.relaxation_factors: list = []   # pushed per Cycle, popped by its smoother / correction (:249-253)
+        self.partitionings: list = []
+
+    @staticmethod
+    def _name(obj):
+        name = type(obj).__name__
+        return "Operator" if name == "SystemOperator" else name
+
+    @staticmethod
+    def _level(obj):
+        return obj.grid[0].level
+
+    def _update_rhs(self, rhs, level):
+        if self._name(rhs) == "RightHandSide":
+            return
+        if self.rhs_pending.get(level, True):
+            self.visit(rhs)                  # emits the fine residual, then the restriction statements
+            self.rhs_pending[level] = False
+
+    def visit(self, e):
+        """-> None for a smoothing step, a marker of what the expression denotes otherwise."""
+        name, level = self._name(e), self._level(e)
+        if name == "Cycle":
+            self.relaxation_factors.append(e.relaxation_factor)
+            self.partitionings.append(e.partitioning)
+            self.visit(e.approximation)
+            correction = self.visit(e.correction)
+            if correction is not None:       # coarse-grid correction: Solution += w * (P * Solution_coarse)  (:104-118)
+                omega = self.relaxation_factors.pop()
+                self.partitionings.pop()
+                self.ops.append(FasOp("prolong_add", level, float(omega)))
+            return "solution"
+        if name == "Multiplication":
+            kind = self._name(e.operand1)
+            if kind == "CoarseGridSolver":   # (:186-195)
+                self._update_rhs(e.operand2, level)
+                self.ops.append(FasOp("smooth", level, SMOOTHER_WEIGHT, self.cgs_sweeps, cgs=True))
+                return "solution"
+            if kind == "Inverse":            # (:197-247)
+                self._smooth(e, level)
+                return None
+            if kind == "Operator":           # A_c * (R * u): inside a coarse right-hand side (:266-273)
+                self.visit(e.operand2)
+                return "expression"
+            if kind == "Restriction" and ("Approximation" in self._name(e.operand2) or self._name(e.operand2) == "Cycle"):
+                return "approximation"       # (:120-136): its two loops are part of the `restrict` op below
+            self.visit(e.operand1)
+            self.visit(e.operand2)
+            return "expression"
+        if name == "Addition":               # R * residual + A_c * (R * u): the coarse right-hand side
+            self.visit(e.operand1)
+            self.visit(e.operand2)
+            self.ops.append(FasOp("restrict", level))
+            return "expression"
+        if name == "Subtraction":            # (:174-184)
+            self.visit(e.operand1)
+            self.ops.append(FasOp("subtract", level))
+            return "solution"
+        if "Residual" in name:               # (:149-172)
+            self._update_rhs(e.rhs, level)
+            self.ops.append(FasOp("residual", level))
+            return "residual"
+        if name == "Prolongation":
+            self.rhs_pending[level - 1] = True          # (:301-303)
+            return "stencil"
+        return "field"                       # approximations, right-hand sides, stencils: no statement
+
+    def _smooth(self, e, level):
+        residual = e.operand2
+        self._update_rhs(residual.rhs, level)
+        omega = self.relaxation_factors.pop()
+        partitioning = self.partitionings.pop()
+        if self.template_smoother:           # FunctionCall(fct_smoother): Smoother@level of the template (:246-247)
+            self.ops.append(FasOp("smooth", level, SMOOTHER_WEIGHT, 1))
+            return
+        smoother = e.operand1.operand
+        newton_steps = smoother.operand2.n_newton_steps if self._name(smoother) == "Addition" else 0
+        colored = partitioning.get_name() == "red_black"
+        self.ops.append(FasOp("smooth", level, float(omega), 1, newton_steps, colored))
+
+
+def lower(expression, template_smoother: bool = False, cgs_sweeps: int = CGS_SWEEPS) -> List[FasOp]:
+    """IR graph of a FAS solver (built by the FAS productions of the grammar) -> statement list.
+    `template_smoother`: every smoothing step is a call of the template's `Smoother` function
+    (`ProgramGeneratorFAS(fct_smoother="Smoother")`), else the smoother the individual describes."""
+    lw = _Lowerer(template_smoother, cgs_sweeps)
+    lw.visit(expression)
+    merged: List[FasOp] = []
+    for op in lw.ops:                        # consecutive identical sweeps become one op with a count
+        last = merged[-1] if merged else None
+        if (last is not None and op.kind == "smooth" and last.kind == "smooth" and not op.cgs and not last.cgs
+                and (last.level, last.omega, last.newton_steps, last.colored) == (op.level, op.omega, op.newton_steps, op.colored)):
+            last.sweeps += op.sweeps
+        else:
+            merged.append(FasOp(**vars(op)))
+    return merged
 
 
 class FasSolver:
@@ -106,7 +222,7 @@ class FasSolver:
         for op in ops:
             if op.kind == "smooth":
                 if op.sweeps > 0:
-                    ws.fas_smooth(op.level, op.omega, gamma, op.sweeps)
+                    ws.fas_smooth(op.level, op.omega, gamma, op.sweeps, op.newton_steps, op.colored)
             elif op.kind == "residual":
                 ws.fas_residual(op.level, gamma)
             elif op.kind == "restrict":
@@ -135,3 +251,121 @@ class FasSolver:
 
     def close(self):
         self.ws.close()
+
+
+# ----------------------------------------------------------------------------------------
+# the reference's generator interface for this path
+# ----------------------------------------------------------------------------------------
+
+class B200ProgramGeneratorFAS:
+    """Drop-in for `ProgramGeneratorFAS` (exastencils_FAS.py:11-446) behind the optimizer: same
+    constructor arguments (field / stencil names are accepted and ignored: the problem is the
+    `FAS_2D_Basic` definition of `problems.py`), `uses_FAS`, the front-end records
+    (`equations`, `operators`, `fields`, `finest_grid`, `coarsening_factor`, levels of the `.knowledge`
+    file), the dummy `generate_storage` / `initialize_code_generation`, and `generate_and_evaluate`
+    which lowers the `Cycle` among its arguments and solves on the GPU instead of emitting Layer 4,
+    running ExaStencils, make and `likwid-pin ./exastencils` (:369-426).
+    `fct_smoother` given: every smoothing step calls the template's `Smoother` (:246-247)."""
+
+    def __init__(self, problem_name="FAS_2D_Basic", solution="Solution", rhs="RHS", residual="Residual",
+                 FASApproximation="Approximation", restriction="RestrictionNode", prolongation="CorrectionNode",
+                 op_linear="Laplace", op_nonlinear="gamSten", fct_name_mgcycle="gen_mgCycle", fct_cgs="CGS",
+                 fct_smoother=None, mpi_rank=0, min_level=None, max_level=None, device=None):
+        from . import ir, problems
+        self.problem_name = problem_name
+        self._problem = problems.get_problem(problem_name)
+        self.min_level = self._problem.min_level if min_level is None else min_level
+        self.max_level = self._problem.max_level if max_level is None else max_level
+        self.dimension = self._problem.dimension
+        self.mpi_rank = mpi_rank
+        self.fct_smoother = fct_smoother
+        self.fct_CGS = fct_cgs
+        self.fct_name = fct_name_mgcycle + f"@{self.max_level}"
+        self.gamma = float(self._problem.parameters["gam"])
+        self._device = device
+        self._solver = None
+        self._front_end = None
+        self.last_residual_history: List[float] = []
+        size, h = 2 ** self.max_level, 1 / (2 ** self.max_level)
+        self.coarsening_factor = [tuple([2] * self.dimension)]
+        self.finest_grid = [ir.Grid(tuple([size] * self.dimension), tuple([h] * self.dimension), self.max_level)]
+
+    @property
+    def uses_FAS(self):
+        return True
+
+    def _records(self):
+        if self._front_end is None:
+            from .front_end import build_front_end
+            self._front_end = build_front_end(self._problem, self.min_level, self.max_level)
+        return self._front_end
+
+    @property
+    def equations(self):
+        return self._records()[0]
+
+    @property
+    def operators(self):
+        return self._records()[1]
+
+    @property
+    def fields(self):
+        return self._records()[2]
+
+    def generate_storage(self, *args):
+        return []
+
+    def initialize_code_generation(self, *args, **kwargs):
+        pass
+
+    def _ensure_solver(self, min_level):
+        import os
+        if self._solver is None or self._solver.min_level != min_level:
+            if self._solver is not None:
+                self._solver.close()
+            device = self._device if self._device is not None else int(os.environ.get("LOCAL_RANK", "0"))
+            self._solver = FasSolver(min_level, self.max_level, self.gamma, device)
+        return self._solver
+
+    def lower(self, expression) -> List[FasOp]:
+        return lower(expression, template_smoother=self.fct_smoother is not None)
+
+    def generate_and_evaluate(self, *args, **kwargs):
+        """-> (time to solution in ms, convergence factor, iterations), averaged over
+        `evaluation_samples` runs; the convergence factor is (res_final / res_initial)^(1/n) like the
+        reference's `parse_output` (:370-393)."""
+        expression = next((a for a in args if type(a).__name__ == "Cycle"), None)
+        if expression is None:
+            raise ValueError("no Cycle among the arguments")
+        samples = kwargs.get("evaluation_samples", 1)
+        infinity = 1e100
+        ops = self.lower(expression)
+        solver = self._ensure_solver(min(op.level for op in ops))
+        times, factors, iterations = [], [], []
+        for _ in range(samples):
+            solver.reset()
+            history, ms = solver.solve(ops)
+            self.last_residual_history = history
+            n = len(history) - 1
+            c = (history[-1] / history[0]) ** (1.0 / n) if n > 0 and history[0] > 0 else float("nan")
+            if math.isinf(c) or math.isnan(c):
+                return infinity, infinity, infinity
+            times.append(ms)
+            factors.append(c)
+            iterations.append(n)
+        return sum(times) / samples, sum(factors) / samples, sum(iterations) / samples
+
+    def generate_cycle_function(self, *args):
+        """The statement list as text, one statement per line (the reference returns Layer-4 ExaSlang,
+        :428-437; the listings under tests/golden/fas_golden.json are the reference's)."""
+        expression = next((a for a in args if type(a).__name__ == "Cycle"), None)
+        lines = [f"Function {self.fct_name} (  ) {{"]
+        for op in self.lower(expression):
+            lines.append(f"  {op.kind}@{op.level} omega={op.omega!r} sweeps={op.sweeps} newton_steps={op.newton_steps} "
+                         f"colored={op.colored}")
+        return "\n".join(lines + ["}"])
+
+    def close(self):
+        if self._solver is not None:
+            self._solver.close()
+            self._solver = None

@@ -56,7 +56,10 @@ class Grammar:
     def __init__(self, problem: ProblemSpec, min_level: int, max_level: int,
                  maximum_local_system_size: int = 8, relaxation_factor_samples: int = 37,
                  enable_partitioning: bool = True, parameters: Optional[Dict] = None,
-                 coarse_grid_solver_expression=None):
+                 coarse_grid_solver_expression=None, FAS: bool = False):
+        """`FAS` selects the productions of the full approximation scheme (multigrid.py:275-299,
+        323-341, 360-375): Jacobi-Picard / Jacobi-Newton smoothers, the restricted fine solution
+        carried into the coarse right-hand side and subtracted again before the prolongation."""
         depth = max_level - min_level
         assert depth >= 1, "The maximum number of levels must be greater zero"
         self.problem = problem
@@ -69,6 +72,7 @@ class Grammar:
         self.primitives: Dict[str, List[Production]] = {}
         self.terminals: Dict[str, List[Production]] = {}
         self.ret = "S_0"
+        self.FAS = FAS
 
         dim = problem.dimension
         nf = problem.n_fields
@@ -85,7 +89,11 @@ class Grammar:
             self._term("red_black", "Partitioning", ir.RedBlack)
         for i in range(relaxation_factor_samples):
             self._term(repr(i), "RelaxationFactorIndex", i, named=False)
-        self._add_block_shapes(nf, dim, maximum_local_system_size)
+        if not FAS:
+            self._add_block_shapes(nf, dim, maximum_local_system_size)
+        else:
+            for k in (1, 2, 3, 4):                                        # multigrid.py:446-449
+                self._term(repr(k), "NewtonSteps", k, named=False)
 
         self.operators = []
         for d in range(depth + 1):
@@ -165,20 +173,50 @@ class Grammar:
             return smoothing(relaxation_factor_index, ir.Single,
                              lambda op: ir.generate_collective_block_jacobi(op, block_shape), cycle)
 
+        def jacobi_picard(relaxation_factor_index, partitioning, cycle):
+            return smoothing(relaxation_factor_index, partitioning, ir.generate_jacobi_picard, cycle)
+
+        def jacobi_newton(relaxation_factor_index, partitioning, n_newton_steps, cycle):
+            return smoothing(relaxation_factor_index, partitioning,
+                             lambda op: ir.generate_jacobi_newton(op, n_newton_steps), cycle)
+
+        def fas_restrict(restriction_operator, cycle):
+            # rhs of the coarse problem: R r + A_c (R u)                  (multigrid.py:285-294)
+            residual_c = ir.Multiplication(restriction_operator, cycle.correction)
+            residual_fas = ir.Multiplication(coarse_operator, ir.Multiplication(restriction_operator, cycle.approximation))
+            cycle.correction = ir.Addition(residual_c, residual_fas)
+            return cycle
+
         def coarsening(coarse_operator_, coarse_approximation, restriction_operator, cycle):
-            cycle.correction = ir.Multiplication(restriction_operator, cycle.correction)
+            if self.FAS:
+                cycle = fas_restrict(restriction_operator, cycle)
+            else:
+                cycle.correction = ir.Multiplication(restriction_operator, cycle.correction)
             coarse_residual = ir.Residual(coarse_operator_, coarse_approximation, cycle.correction)
             new_cycle = ir.Cycle(coarse_approximation, cycle.correction, coarse_residual)
             new_cycle.predecessor = cycle
             return new_cycle
 
-        def update_with_coarse_grid_correction(relaxation_factor_index, prolongation_operator, state):
+        def update_with_coarse_grid_correction(relaxation_factor_index, prolongation_operator, state,
+                                               restriction_operator=None):
             cycle = state[0]
-            cycle.predecessor.correction = ir.Multiplication(prolongation_operator, cycle)
+            if self.FAS:                                                  # multigrid.py:275-283
+                correction_fas = ir.Multiplication(restriction_operator, cycle.predecessor.approximation)
+                cycle.predecessor.correction = ir.Multiplication(prolongation_operator,
+                                                                 ir.Subtraction(cycle, correction_fas))
+            else:
+                cycle.predecessor.correction = ir.Multiplication(prolongation_operator, cycle)
             return update(relaxation_factor_index, ir.Single, cycle.predecessor)
 
         def correct_with_coarse_grid_solver(relaxation_factor_index, prolongation_operator, coarse_grid_solver,
                                             restriction_operator, cycle):
+            if self.FAS:                                                  # multigrid.py:332-341
+                cycle = fas_restrict(restriction_operator, cycle)
+                approximation_c = ir.Multiplication(coarse_grid_solver, cycle.correction)
+                restricted_solution = ir.Multiplication(restriction_operator, cycle.approximation)
+                cycle.correction = ir.Multiplication(prolongation_operator,
+                                                     ir.Subtraction(approximation_c, restricted_solution))
+                return update(relaxation_factor_index, ir.Single, cycle)
             restricted = ir.Multiplication(restriction_operator, cycle.correction)
             cycle.correction = ir.Multiplication(prolongation_operator,
                                                  ir.Multiplication(coarse_grid_solver, restricted))
@@ -191,9 +229,19 @@ class Grammar:
         both(f"residual_{d}", residual, [], [S, Sg], [C, Cg])
         if not scalar_equation:
             both(f"decoupled_jacobi_{d}", decoupled_jacobi, ["RelaxationFactorIndex", "Partitioning"], [C, Cg], [S, Sg])
-        both(f"collective_jacobi_{d}", collective_jacobi, ["RelaxationFactorIndex", "Partitioning"], [C, Cg], [S, Sg])
-        both(f"collective_block_jacobi_{d}", collective_block_jacobi, ["RelaxationFactorIndex", "BlockShape"], [C, Cg], [S, Sg])
-        if not coarsest:
+        if not self.FAS:
+            both(f"collective_jacobi_{d}", collective_jacobi, ["RelaxationFactorIndex", "Partitioning"], [C, Cg], [S, Sg])
+            both(f"collective_block_jacobi_{d}", collective_block_jacobi, ["RelaxationFactorIndex", "BlockShape"], [C, Cg], [S, Sg])
+        else:                                                             # multigrid.py:360-364 (argument order as there)
+            for i, o in zip([C, Cg], [S, Sg]):
+                self._prim(f"jacobi_picard_{d}", ["RelaxationFactorIndex", "Partitioning", i], o, jacobi_picard)
+                self._prim(f"jacobi_newton_{d}", ["RelaxationFactorIndex", "Partitioning", "NewtonSteps", i], o, jacobi_newton)
+        if not coarsest and self.FAS:                                     # multigrid.py:366-375: the restriction comes last
+            for i, o in zip([S2, Sg2], [S, Sg]):
+                self._prim(f"update_with_coarse_grid_correction_{d}", ["RelaxationFactorIndex", f"P_{d + 1}", i, f"R_{d}"], o,
+                           update_with_coarse_grid_correction)
+            both(f"coarsening_{d}", coarsening, [f"A_{d + 1}", f"x_{d + 1}", f"R_{d}"], [C, Cg], [C2, Cg2])
+        elif not coarsest:
             both(f"update_with_coarse_grid_correction_{d}", update_with_coarse_grid_correction,
                  ["RelaxationFactorIndex", f"P_{d + 1}"], [S2, Sg2], [S, Sg])
             both(f"coarsening_{d}", coarsening, [f"A_{d + 1}", f"x_{d + 1}", f"R_{d}"], [C, Cg], [C2, Cg2])

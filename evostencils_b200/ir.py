@@ -142,6 +142,20 @@ class Addition(Expression):
         return self.operand1.generate_stencil() + self.operand2.generate_stencil()
 
 
+class Subtraction(Expression):
+    """operand1 - operand2 (base.py `sub`); in FAS cycles: coarse solution minus the restricted fine
+    solution (grammar/multigrid.py:276-281, 337-341)."""
+
+    def __init__(self, operand1, operand2):
+        super().__init__()
+        self.operand1 = operand1
+        self.operand2 = operand2
+
+    @property
+    def grid(self):
+        return self.operand1.grid
+
+
 class Multiplication(Expression):
     """Binary product node (base.py:385-405).  Used both for operator entries
     (stencil * stencil) and for the cycle-level products `R * residual`,
@@ -302,6 +316,30 @@ class BlockDiagonalOperator(SystemOperator):
                 entries[-1].append(Operator(f"{operator.name}_{i}{j}_block_diag", entry.grid,
                                             ConstantStencilGenerator(periodic)))
         super().__init__(f"{operator.name}_block_diag", entries)
+
+
+class Jacobian(Expression):
+    """Derivative of the nonlinear term, used with `n_newton_steps` local Newton updates (system.Jacobian;
+    smoother.py:45-46)."""
+
+    def __init__(self, operand, n_newton_steps=1):
+        super().__init__()
+        self.operand = operand
+        self.n_newton_steps = n_newton_steps
+
+    @property
+    def grid(self):
+        return self.operand.grid
+
+
+def generate_jacobi_picard(operator):
+    """smoother.py:41-42"""
+    return ElementwiseDiagonal(operator)
+
+
+def generate_jacobi_newton(operator, n_newton_steps):
+    """smoother.py:45-46"""
+    return Addition(ElementwiseDiagonal(operator), Jacobian(operator, n_newton_steps))
 
 
 def generate_decoupled_jacobi(operator):

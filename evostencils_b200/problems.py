@@ -182,6 +182,34 @@ POISSON_3D = ProblemSpec(
 
 
 # ----------------------------------------------------------------------------------------
+# Nonlinear FAS example: -Laplace(u) + gam u e^u = f   (example_problems/FAS_2D_Basic)
+# ----------------------------------------------------------------------------------------
+
+def _fas_solution(x, y):
+    return (x ** 2 - x ** 3) * np.sin(3.0 * np.pi * y)                  # solFct, FAS_2D_Basic.exa4:54-56
+
+
+def _fas_rhs(x, y, h=None, gam=10.0, **_):
+    # rhsFct of the enhanced test problem (.exa4:46-53)
+    return [((9.0 * np.pi ** 2 + gam * np.exp(_fas_solution(x, y))) * (x ** 2 - x ** 3) + 6.0 * x - 2.0)
+            * np.sin(3.0 * np.pi * y)]
+
+
+def _fas_bc(x, y, h=None, **_):
+    return [np.zeros(np.broadcast(x, y).shape)]                         # Field Solution< global, BasicComm, 0.0 >
+
+
+# the linear part only: the term gam e^u u is applied by the FAS stage kernels (csrc/mg_fas.cuh); names as
+# ProgramGeneratorFAS registers them (exastencils_FAS.py:77-85); levels of the .knowledge file
+FAS_2D_BASIC = ProblemSpec(
+    name="FAS_2D_Basic", dimension=2, field_names=["u"], rhs_names=["RHS_u"],
+    equation_names=["solEq"], min_level=6, max_level=10, dtype="f64",
+    entry_terms=_poisson_terms, rhs_function=_fas_rhs, boundary_function=_fas_bc,
+    solver=SolverDefaults(target_reduction=1e-10, max_iterations=100, damping=0.8, coloring="single"),
+    parameters={"gam": 10.0}, restriction_names=["RestrictionNode"], prolongation_names=["ProlongationNode"])
+
+
+# ----------------------------------------------------------------------------------------
 # Linear elasticity 2D (two coupled fields)
 # ----------------------------------------------------------------------------------------
 
@@ -249,7 +277,7 @@ HELMHOLTZ_2D = ProblemSpec(
     solver_iteration_limit=10000)
 
 
-REGISTRY = {p.name: p for p in (POISSON_2D, POISSON_3D, LINEAR_ELASTICITY_2D, HELMHOLTZ_2D)}
+REGISTRY = {p.name: p for p in (POISSON_2D, POISSON_3D, LINEAR_ELASTICITY_2D, HELMHOLTZ_2D, FAS_2D_BASIC)}
 
 
 def get_problem(name: str) -> ProblemSpec:

@@ -175,8 +175,13 @@ int mg_set_fast_kernels(mg_workspace* ws, int enabled);
  * (replaces the Layer-4 text ProgramGeneratorFAS.traverse_graph emits, code_generation/
  * exastencils_FAS.py:99-319, and the ExaStencils compile behind it).  2D scalar MG_F64 workspaces whose
  * operator on the level is the 5-point Laplace star; direct launches on the workspace stream. */
-/* `sweeps` damped Jacobi-Newton sweeps (.exa4:65-75; 30 of them = CGS@coarsest, :58-63) */
-int mg_fas_smooth(mg_workspace* ws, int level, double omega, double gamma, int sweeps);
+/* `sweeps` smoother sweeps.  newton_steps >= 1: Jacobi-Newton with that many local Newton updates per
+ * node, newton_steps == 0: Jacobi-Picard (exastencils_FAS.py:206-223); colored != 0: red-black in place,
+ * colour (i0 + i1) % 2 == 0 first (:236-246), else Jacobi into the other solution slot.
+ * (omega 0.8, newton_steps 1, colored 0 = Smoother@all of the template, .exa4:65-75; 30 of those =
+ * CGS@coarsest, :58-63) */
+int mg_fas_smooth(mg_workspace* ws, int level, double omega, double gamma, int sweeps, int newton_steps,
+                  int colored);
 /* Residual@level = RHS - (L u + gamma e^u u), boundary 0 (.exa4:77-82) */
 int mg_fas_residual(mg_workspace* ws, int level, double gamma);
 /* `level` = the coarse level: Approximation = R Solution@(level+1); Solution@level = Approximation;

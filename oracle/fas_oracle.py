@@ -69,13 +69,40 @@ def residual(u, f, level, gamma):
     return r
 
 
-def smooth(u, f, level, gamma, weight=SMOOTHER_WEIGHT):
+def _local_steps(c, nb, f_int, h2, gamma, weight, newton_steps):
+    """`newton_steps` in-place updates of the centre values c with the neighbour sum terms fixed
+    (exastencils_FAS.py:206-231): c += w (f - (L u + gam e^c c)) / (diag [+ gam (c + 1) e^c]);
+    newton_steps = 0: Jacobi-Picard (one step, denominator diag(L) only)."""
+    diag = 2.0 * h2 + 2.0 * h2
+    for _ in range(max(1, newton_steps)):
+        a = diag * c
+        for term in nb:
+            a = a + term
+        num = f_int - (a + (gamma * np.exp(c)) * c)
+        den = diag + gamma * (c + 1.0) * np.exp(c) if newton_steps > 0 else diag
+        c = c + weight * (num / den)
+    return c
+
+
+def smooth(u, f, level, gamma, weight=SMOOTHER_WEIGHT, newton_steps=1, colored=False):
+    """One sweep of the smoother `traverse_graph` emits (exastencils_FAS.py:186-246): Jacobi (the old
+    values of the neighbours, `Solution<next>`) or red-black in place, colour (i0 + i1) % 2 == 0 first."""
     h2 = float(4 ** level)
-    c = u[1:-1, 1:-1]
+
+    def neighbours(v):
+        return [(-h2) * v[1:-1, 2:], (-h2) * v[1:-1, :-2], (-h2) * v[2:, 1:-1], (-h2) * v[:-2, 1:-1]]
+
+    if not colored:
+        new = u.copy()
+        new[1:-1, 1:-1] = _local_steps(u[1:-1, 1:-1], neighbours(u), f[1:-1, 1:-1], h2, gamma, weight, newton_steps)
+        return new
     new = u.copy()
-    num = f[1:-1, 1:-1] - apply_operator(u, level, gamma)[1:-1, 1:-1]
-    den = (2.0 * h2 + 2.0 * h2) + gamma * (1.0 + c) * np.exp(c)
-    new[1:-1, 1:-1] = c + weight * (num / den)
+    n = u.shape[0]
+    yy, xx = np.meshgrid(np.arange(1, n - 1), np.arange(1, n - 1), indexing="ij")
+    for colour in (0, 1):
+        mask = ((xx + yy) % 2) == colour
+        upd = _local_steps(new[1:-1, 1:-1], neighbours(new), f[1:-1, 1:-1], h2, gamma, weight, newton_steps)
+        new[1:-1, 1:-1] = np.where(mask, upd, new[1:-1, 1:-1])
     return new
 
 
@@ -141,3 +168,39 @@ def solve(level, min_level, pre=2, post=2, gamma=GAMMA, weight=SMOOTHER_WEIGHT, 
         u = cycle(u, f, level, min_level, pre, post, gamma, weight, cgs_sweeps, cgc_omega)
         history.append(norm(residual(u, f, level, gamma)))
     return u, history
+
+
+def solve_ops(ops, max_level, min_level, gamma=GAMMA, target=1e-10, max_iterations=100):
+    """Execute a statement list (`evostencils_b200.fas.FasOp` records: kind, level, omega, sweeps,
+    newton_steps, colored) as the cycle of the `.exa4`'s Solve loop.  -> (solution, residual history)."""
+    f = {max_level: right_hand_side(max_level, gamma)}
+    u = {max_level: np.zeros_like(f[max_level])}
+    r, approx = {}, {}
+
+    def run_cycle():
+        for op in ops:
+            lv = op.level
+            if op.kind == "smooth":
+                for _ in range(op.sweeps):
+                    u[lv] = smooth(u[lv], f[lv], lv, gamma, op.omega, op.newton_steps, op.colored)
+            elif op.kind == "residual":
+                r[lv] = residual(u[lv], f[lv], lv, gamma)
+            elif op.kind == "restrict":
+                approx[lv] = restrict(u[lv + 1])
+                u[lv] = approx[lv].copy()
+                f[lv] = restrict(r[lv + 1])
+                f[lv][1:-1, 1:-1] = f[lv][1:-1, 1:-1] + apply_operator(approx[lv], lv, gamma)[1:-1, 1:-1]
+            elif op.kind == "subtract":
+                u[lv] = u[lv] - approx[lv]
+            elif op.kind == "prolong_add":
+                u[lv] = prolong_add(u[lv], u[lv - 1], op.omega)
+            else:
+                raise ValueError(op.kind)
+
+    history = [norm(residual(u[max_level], f[max_level], max_level, gamma))]
+    while not (history[-1] < target * history[0] or len(history) - 1 >= max_iterations):
+        run_cycle()
+        history.append(norm(residual(u[max_level], f[max_level], max_level, gamma)))
+        if not np.isfinite(history[-1]):
+            break
+    return u[max_level], history

@@ -53,6 +53,46 @@ def fas_v_cycle_string(depth, num_pre, num_post, relax_index, newton_steps=1, pa
     return expr
 
 
+def fas_w_like_string():
+    """Level 2 of the grammar is visited twice from level 1; Picard and Newton smoothers, both partitionings."""
+    e = "residual_0(u_and_f)"
+    e = f"residual_0(jacobi_newton_0(21, red_black, 2, {e}))"
+    e = f"coarsening_0(A_1, zero_1, R_0, {e})"
+    e = f"coarsening_1(A_2, zero_2, R_1, {e})"
+    e = f"correct_with_coarse_grid_solver_2(18, P_3, CGS_3, R_2, {e})"
+    e = f"jacobi_picard_2(14, single, residual_2({e}))"
+    e = f"update_with_coarse_grid_correction_1(16, P_2, {e}, R_1)"
+    e = f"residual_1(jacobi_newton_1(12, single, 3, residual_1({e})))"
+    e = f"coarsening_1(A_2, zero_2, R_1, {e})"
+    e = f"correct_with_coarse_grid_solver_2(18, P_3, CGS_3, R_2, {e})"
+    e = f"update_with_coarse_grid_correction_1(18, P_2, {e}, R_1)"
+    e = f"update_with_coarse_grid_correction_0(20, P_1, {e}, R_0)"
+    return f"jacobi_picard_0(22, red_black, residual_0(jacobi_newton_0(9, single, 1, residual_0({e}))))"
+
+
+INLINE_CASES = [
+    # (name, depth, grammar string): smoothers emitted inline (fct_smoother=None)
+    ("fas_inline_picard_newton", 1,
+     "jacobi_picard_0(20, red_black, residual_0(correct_with_coarse_grid_solver_0(18, P_1, CGS_1, R_0, "
+     "residual_0(jacobi_newton_0(14, single, 2, residual_0(u_and_f))))))"),
+    ("fas_inline_v_two_coarsenings", 2,
+     "jacobi_picard_0(20, red_black, residual_0(update_with_coarse_grid_correction_0(18, P_1, "
+     "correct_with_coarse_grid_solver_1(18, P_2, CGS_2, R_1, residual_1(jacobi_newton_1(14, single, 2, "
+     "coarsening_0(A_1, zero_1, R_0, residual_0(jacobi_newton_0(14, single, 1, residual_0(jacobi_newton_0(14, single, 1, "
+     "residual_0(u_and_f))))))))), R_0)))"),
+    ("fas_inline_w_like", 3, None),
+]
+
+
+def front_end(pg, depth):
+    hi = pg.max_level
+    approx = system.Approximation("x", [base.Approximation("u", pg.finest_grid[0])])
+    rhs = system.RightHandSide("b", [base.RightHandSide("RHS_u", pg.finest_grid[0])])
+    pset, _ = mg.generate_primitive_set(approx, rhs, pg.dimension, pg.coarsening_factor, hi, pg.equations,
+                                        pg.operators, pg.fields, depth=depth, FAS=True)
+    return pset
+
+
 def main():
     # fct_smoother = "Smoother": the smoother is the function of the template (.exa4:65-75), as in the
     # generated sample FAS_2D_Basic.exa4:210-269
@@ -63,14 +103,22 @@ def main():
     for name, depth, pre, post, cgc in (("fas_v22_two_coarsenings", 2, 2, 2, 18), ("fas_v21_three_coarsenings", 3, 2, 1, 18),
                                         ("fas_v11_one_coarsening", 1, 1, 1, 18), ("fas_v12_damped_correction", 2, 1, 2, 12)):
         lo, hi = pg.max_level - depth, pg.max_level
-        approx = system.Approximation("x", [base.Approximation("u", pg.finest_grid[0])])
-        rhs = system.RightHandSide("b", [base.RightHandSide("RHS_u", pg.finest_grid[0])])
-        pset, _ = mg.generate_primitive_set(approx, rhs, pg.dimension, pg.coarsening_factor, hi, pg.equations,
-                                            pg.operators, pg.fields, depth=depth, FAS=True)
+        pset = front_end(pg, depth)
         string = fas_v_cycle_string(depth, pre, post, 14, cgc_relax_index=cgc)
         expression, _ = eval(string, pset.context, {})
         text = pg.generate_cycle_function(expression)
         out[name] = {"min_level": lo, "max_level": hi, "pre": pre, "post": post, "cgc_relax_index": cgc,
+                     "template_smoother": True, "grammar": string, "layer4": text}
+        print(name, len(text.splitlines()), "lines")
+    inline = ProgramGeneratorFAS("FAS_2D_Basic", "Solution", "RHS", "Residual", "Approximation", "RestrictionNode",
+                                 "CorrectionNode", "Laplace", "gamSten", "gen_mgCycle", "CGS", None)
+    for name, depth, string in INLINE_CASES:
+        if string is None:
+            string = fas_w_like_string()
+        pset = front_end(inline, depth)
+        expression, _ = eval(string, pset.context, {})
+        text = inline.generate_cycle_function(expression)
+        out[name] = {"min_level": inline.max_level - depth, "max_level": inline.max_level, "template_smoother": False,
                      "grammar": string, "layer4": text}
         print(name, len(text.splitlines()), "lines")
     path = os.path.join(REPO, "tests", "golden", "fas_golden.json")

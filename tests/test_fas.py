@@ -19,22 +19,55 @@ def test_cycle_statement_order_is_that_of_the_generated_listing():
 
 def parse_layer4(text):
     """Statement sequence of a cycle function emitted by the reference's ProgramGeneratorFAS:
-    (kind, level of the field written, count or factor)."""
+    smooth -> ("smooth", level, sweeps, omega, newton_steps, colored) with omega None for calls of the
+    template's Smoother function; the others (kind, level, factor or 1)."""
     import re
     out = []
+    updates, in_colour = None, False
+
+    def add_smooth(level, omega, newton_steps, colored):
+        last = out[-1] if out else None
+        if last and last[0] == "smooth" and (last[1], last[3], last[4], last[5]) == (level, omega, newton_steps, colored):
+            out[-1] = ("smooth", level, last[2] + 1, omega, newton_steps, colored)
+        else:
+            out.append(("smooth", level, 1, omega, newton_steps, colored))
+
     for line in text.splitlines():
         line = line.strip()
         m = re.match(r"Smoother@(\d+) \(", line)
         if m:
-            level = int(m.group(1))
-            if out and out[-1][0] == "smooth" and out[-1][1] == level:
-                out[-1] = ("smooth", level, out[-1][2] + 1)
-            else:
-                out.append(("smooth", level, 1))
+            add_smooth(int(m.group(1)), None, 1, False)
             continue
         m = re.match(r"CGS@(\d+) \(", line)
         if m:
             out.append(("cgs", int(m.group(1)), 1))
+            continue
+        if line.startswith("color with"):
+            in_colour = True
+            continue
+        m = re.match(r"loop over Solution@(\d+) \{", line)
+        if m:
+            updates = []
+            continue
+        m = re.match(r"Solution@(\d+) \+= ([0-9.e-]+) \* \( \( RHS@\1 - \( \( Laplace@\1 \* Solution@\1 \) \+ "
+                     r"\( gamSten@\1 \* Solution@\1 \) \) \) / (.*) \)$", line)
+        if m:
+            den = m.group(3)
+            assert den in (f"Laplace@{m.group(1)}:[0,0]",
+                           f"( Laplace@{m.group(1)}:[0,0] + gam*(Solution@{m.group(1)} + 1)*exp(Solution@{m.group(1)}) )"), den
+            updates.append((int(m.group(1)), float(m.group(2)), "gam" in den))
+            continue
+        if line == "}" and updates:
+            level, omega, newton = updates[0]
+            assert all(u == updates[0] for u in updates)
+            add_smooth(level, omega, len(updates) if newton else 0, in_colour)
+            updates = None
+            continue
+        if line == "}" and in_colour and updates is None:
+            in_colour = False                                       # end of the colour block (after `apply bc`)
+            continue
+        if line == "}":
+            updates = None
             continue
         m = re.match(r"Residual@(\d+) = \( RHS@\1 - \( \( Laplace@\1 \* Solution@\1 \) \+ \( gamSten@\1 \* Solution@\1 \) \) \)", line)
         if m:
@@ -60,34 +93,112 @@ def parse_layer4(text):
             assert int(m.group(3)) == int(m.group(1)) - 1
             out.append(("prolong_add", int(m.group(1)), float(m.group(2))))
             continue
-        assert line == "" or line == "}" or line.startswith(("Function", "loop over", "apply bc", "communicate",
-                                                             "Solution@")), line
+        assert line == "" or line.startswith(("Function", "loop over", "apply bc", "communicate", "advance", "Variable",
+                                              "Solution<next>@", "Solution@", "( i0 + i1 ) % 2")), line
     return out
+
+
+def as_statements(ops, template_smoother):
+    got = []
+    for op in ops:
+        if op.kind == "smooth" and op.cgs:
+            got.append(("cgs", op.level, 1))                        # CGS@coarsest = 30 sweeps of the smoother
+        elif op.kind == "smooth":
+            got.append(("smooth", op.level, op.sweeps, None if template_smoother else op.omega,
+                        1 if template_smoother else op.newton_steps, False if template_smoother else op.colored))
+        elif op.kind == "prolong_add":
+            got.append(("prolong_add", op.level, op.omega))
+        else:
+            got.append((op.kind, op.level, 1))
+    return got
+
+
+def load_golden():
+    import json
+    import os
+    return json.load(open(os.path.join(os.path.dirname(__file__), "golden", "fas_golden.json")))
 
 
 def test_cycle_statement_order_is_that_of_the_reference_emitter():
     """tests/golden/fas_golden.json: Layer-4 text emitted by the unmodified reference
     (`ProgramGeneratorFAS.generate_cycle_function`) for FAS V-cycles written in its FAS grammar."""
-    import json
-    import os
-    golden = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "fas_golden.json")))
-    assert len(golden) >= 4
-    for name, case in golden.items():
+    golden = load_golden()
+    cases = {k: v for k, v in golden.items() if "pre" in v}
+    assert len(cases) >= 4
+    for name, case in cases.items():
         want = parse_layer4(case["layer4"])
-        factors = {w for kind, _, w in want if kind == "prolong_add"}
+        factors = {s[2] for s in want if s[0] == "prolong_add"}
         assert len(factors) == 1, name
         ops = fas.v_cycle_ops(case["max_level"], case["min_level"], case["pre"], case["post"], cgc_omega=factors.pop())
-        got = []
-        for op in ops:
-            if op.kind == "smooth" and op.level == case["min_level"]:
-                got.append(("cgs", op.level, 1))                    # CGS@coarsest = 30 sweeps of the smoother
-            elif op.kind == "smooth":
-                got.append(("smooth", op.level, op.sweeps))
-            elif op.kind == "prolong_add":
-                got.append(("prolong_add", op.level, op.omega))
-            else:
-                got.append((op.kind, op.level, 1))
-        assert got == want, name
+        assert as_statements(ops, True) == want, name
+
+
+def test_lowering_of_fas_grammar_strings_matches_the_reference_emitter():
+    """Grammar string -> (our FAS productions) -> IR graph -> `fas.lower` against the statements of the
+    listing the reference emits for the same string: template smoother calls and inline Jacobi-Picard /
+    Jacobi-Newton / red-black smoothers, V and W-like shapes."""
+    from evostencils_b200 import problems
+    from evostencils_b200.grammar import Grammar
+    golden = load_golden()
+    assert sum(1 for c in golden.values() if not c["template_smoother"]) >= 3
+    for name, case in golden.items():
+        grammar = Grammar(problems.FAS_2D_BASIC, case["min_level"], case["max_level"], FAS=True)
+        expression, _ = grammar.compile(case["grammar"])
+        ops = fas.lower(expression, template_smoother=case["template_smoother"])
+        assert as_statements(ops, case["template_smoother"]) == parse_layer4(case["layer4"]), name
+        assert fas.lower(grammar.compile(case["grammar"])[0], case["template_smoother"]) == ops      # graph not consumed
+
+
+def test_lowering_accepts_the_reference_ir():
+    """The drop-in boundary: graphs built by the reference's own grammar layer lower to the same
+    statements (container only: needs /root/reference)."""
+    import os
+    import sys
+    if not os.path.isdir("/root/reference/evostencils"):
+        pytest.skip("reference checkout not present")
+    make = os.path.join(os.path.dirname(__file__), "golden", "_make")
+    sys.path[:0] = [make, "/root/reference"]
+    cwd = os.getcwd()
+    try:
+        os.chdir("/root/reference")
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("make_fas_golden", os.path.join(make, "make_fas_golden.py"))
+        gen = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(gen)
+        pg = gen.ProgramGeneratorFAS("FAS_2D_Basic", "Solution", "RHS", "Residual", "Approximation", "RestrictionNode",
+                                     "CorrectionNode", "Laplace", "gamSten", "gen_mgCycle", "CGS", None)
+        for name, case in load_golden().items():
+            pset = gen.front_end(pg, case["max_level"] - case["min_level"])
+            expression, _ = eval(case["grammar"], pset.context, {})
+            ops = fas.lower(expression, template_smoother=case["template_smoother"])
+            assert as_statements(ops, case["template_smoother"]) == parse_layer4(case["layer4"]), name
+    finally:
+        os.chdir(cwd)
+        sys.path.remove(make)
+        sys.path.remove("/root/reference")
+
+
+def test_generator_mirror_has_the_reference_interface():
+    """Attributes the optimizer reads from a ProgramGeneratorFAS (optimization/program.py:806-842;
+    scripts that construct it) exist without touching the GPU."""
+    from evostencils_b200 import problems
+    from evostencils_b200.grammar import Grammar
+    gen = fas.B200ProgramGeneratorFAS("FAS_2D_Basic", "Solution", "RHS", "Residual", "Approximation", "RestrictionNode",
+                                      "CorrectionNode", "Laplace", "gamSten", "gen_mgCycle", "CGS", "Smoother")
+    assert gen.uses_FAS and (gen.dimension, gen.min_level, gen.max_level) == (2, 6, 10)       # .knowledge file
+    assert gen.generate_storage(6, 10, gen.finest_grid) == [] and gen.initialize_code_generation(6, 10) is None
+    assert gen.finest_grid[0].level == 10 and gen.coarsening_factor == [(2, 2)]
+    assert len(gen.equations) == 5 and len(gen.operators) == 15 and len(gen.fields) == 1
+    assert {o.name for o in gen.operators} == {"Laplace", "RestrictionNode", "ProlongationNode"}   # exastencils_FAS.py:77-85
+    expression, _ = Grammar(problems.FAS_2D_BASIC, 8, 10, FAS=True).compile(load_golden()["fas_v22_two_coarsenings"]["grammar"])
+    text = gen.generate_cycle_function(expression)
+    assert text.splitlines()[0] == "Function gen_mgCycle@10 (  ) {" and "restrict@9" in text and "prolong_add@10" in text
+    assert gen.lower(expression) == fas.v_cycle_ops(10, 8, 2, 2, cgc_omega=gen.lower(expression)[-2].omega)
+    import torch
+    if not torch.cuda.is_available():
+        from evostencils_b200.engine import EngineError
+        with pytest.raises(EngineError, match="no CPU fallback"):
+            gen.generate_and_evaluate(expression, evaluation_samples=1)
 
 
 def test_oracle_converges_to_the_discretisation_error():
@@ -178,3 +289,63 @@ def test_fas_solve_matches_the_oracle(lo, hi, pre, post, cgc):
     assert close(solver.solution(), u_ref, 1e-11)
     assert np.abs(solver.solution() - fas.exact_solution(hi)).max() < 2.0 * 4.0 ** (5 - hi) * 1e-3
     solver.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("newton_steps,colored,omega", [(2, False, 0.8), (0, False, 0.7), (1, True, 1.1), (0, True, 1.1), (3, True, 0.9)])
+def test_fas_smoother_variants_match_the_oracle(newton_steps, colored, omega):
+    """Jacobi-Picard, several local Newton steps and the red-black passes (exastencils_FAS.py:206-246)."""
+    from oracle import fas_oracle as fo
+    level = 7
+    rng = np.random.default_rng(17)
+    n = fo.nodes(level)
+    u = np.zeros((n, n))
+    u[1:-1, 1:-1] = 0.3 * rng.standard_normal((n - 2, n - 2))
+    f = rng.standard_normal((n, n)) * float(4 ** level) * 0.1
+    solver = fas.FasSolver(level - 1, level)
+    solver.ws.upload("sol", level, 0, u)
+    solver.ws.upload("rhs", level, 0, f)
+    solver.ws.fas_smooth(level, omega, fo.GAMMA, 3, newton_steps, colored)
+    want = u
+    for _ in range(3):
+        want = fo.smooth(want, f, level, fo.GAMMA, omega, newton_steps, colored)
+    assert close(solver.ws.download("sol", level, 0), want)
+    solver.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["fas_inline_picard_newton", "fas_inline_v_two_coarsenings", "fas_inline_w_like",
+                                  "fas_v12_damped_correction"])
+def test_lowered_fas_individuals_solve_like_the_oracle(case):
+    """Grammar string -> IR -> statement list -> GPU solve, against the numpy execution of the same list."""
+    from evostencils_b200 import problems
+    from evostencils_b200.grammar import Grammar
+    from oracle import fas_oracle as fo
+    golden = load_golden()[case]
+    depth = golden["max_level"] - golden["min_level"]
+    hi, lo = 7, 7 - depth
+    expression, _ = Grammar(problems.FAS_2D_BASIC, lo, hi, FAS=True).compile(golden["grammar"])
+    ops = fas.lower(expression, template_smoother=golden["template_smoother"])
+    solver = fas.FasSolver(lo, hi)
+    history, ms = solver.solve(ops)
+    u_ref, want = fo.solve_ops(ops, hi, lo)
+    assert len(history) == len(want) and len(history) > 3
+    assert np.all(np.abs(np.array(history) - np.array(want)) <= 1e-10 * np.array(want) + 1e-13 * want[0])
+    assert close(solver.solution(), u_ref, 1e-10)
+    solver.close()
+
+
+@pytest.mark.gpu
+def test_generator_mirror_evaluates_like_the_oracle():
+    from evostencils_b200 import problems
+    from evostencils_b200.grammar import Grammar
+    from oracle import fas_oracle as fo
+    gen = fas.B200ProgramGeneratorFAS(fct_smoother=None, min_level=4, max_level=7, device=0)
+    golden = load_golden()["fas_inline_w_like"]
+    expression, _ = Grammar(problems.FAS_2D_BASIC, 4, 7, FAS=True).compile(golden["grammar"])
+    t, c, n = gen.generate_and_evaluate(expression, None, 4, 7, evaluation_samples=2)
+    _, want = fo.solve_ops(gen.lower(expression), 7, 4)
+    assert n == len(want) - 1 and t > 0
+    # the last residuals sit at 1e-10 of the first, where exp() round-off shows: the n-th root agrees to 1e-3
+    assert abs(c - (want[-1] / want[0]) ** (1.0 / n)) <= 1e-3 * c
+    gen.close()
