@@ -7,8 +7,9 @@ The reference emits Layer-4 ExaSlang for such a solver (`ProgramGeneratorFAS.tra
 "total no of iterations" / "time to solution" (:369-426).  Here the statement sequence of the cycle
 function -- `FAS_2D_Basic.exa4:210-269` is one such sequence, a V(2,2) cycle over three levels -- is
 a list of `FasOp` records executed by the stage kernels of `csrc/mg_fas.cuh`; `solve` is the `Solve`
-function of the `.exa4` (:118-187).  Not built yet: the grammar productions that make such cycles
-(grammar/multigrid.py:275-299, 360-375) and the red-black / Picard smoother variants.
+function of the `.exa4` (:118-187).  `lower` turns the IR graph of a FAS individual (FAS productions of
+the grammar, grammar/multigrid.py:275-299, 323-341, 360-375; ours in `grammar.py`) into that list;
+`B200ProgramGeneratorFAS` is the reference's generator interface on top.
 """
 from __future__ import annotations
 
