@@ -255,6 +255,64 @@ class FasSolver:
 
 
 # ----------------------------------------------------------------------------------------
+# Layer-4 export (the reference's hand-off format for this path)
+# ----------------------------------------------------------------------------------------
+
+def emit_layer4(ops: List[FasOp], fct_name: str, template_smoother, names=None) -> str:
+    """The cycle function as Layer-4 ExaSlang, statement for statement the text
+    `ProgramGeneratorFAS.generate_cycle_function` returns (exastencils_FAS.py:99-319, 428-437 through
+    `layer4.print_exa`): it can be pasted into `FAS_2D_Basic_template.exa4` like the reference does
+    (:321-333).  `template_smoother`: name of the template's smoother function, or None for inline
+    smoothers.  Byte-identical to the reference's output for the listings of tests/golden/fas_golden.json."""
+    n = dict(solution="Solution", rhs="RHS", residual="Residual", approximation="Approximation",
+             restriction="RestrictionNode", prolongation="CorrectionNode", linear="Laplace", nonlinear="gamSten",
+             cgs="CGS")
+    n.update(names or {})
+    out = [f"Function {fct_name} (  ) {{"]
+
+    def applied(field, level):
+        return (f"( ( {n['linear']}@{level} * {field}@{level} ) + ( {n['nonlinear']}@{level} * {field}@{level} ) )")
+
+    for op in ops:
+        lv, sol = op.level, f"{n['solution']}@{op.level}"
+        if op.kind == "smooth" and op.cgs:
+            out.append(f"{n['cgs']}@{lv} (  )")
+        elif op.kind == "smooth" and template_smoother:
+            out.extend([f"{template_smoother}@{lv} (  )"] * op.sweeps)
+        elif op.kind == "smooth":
+            jacobian = f"gam*({sol} + 1)*exp({sol})"                  # d/du (gam u e^u), as sympy prints it (:51-54)
+            den = f"( {n['linear']}@{lv}:[0,0] + {jacobian} )" if op.newton_steps > 0 else f"{n['linear']}@{lv}:[0,0]"
+            update = f"  {sol} += {op.omega!r} * ( ( {n['rhs']}@{lv} - {applied(n['solution'], lv)} ) / {den} )"
+            steps = [update] * max(1, op.newton_steps)
+            for _ in range(op.sweeps):
+                if op.colored:
+                    out += ["color with {", "  ( i0 + i1 ) % 2,", f"  communicate {sol}", f"  loop over {sol} {{"]
+                    out += steps + ["}", f"  apply bc to {sol}", "}"]
+                else:
+                    out += [f"communicate {sol}", f"loop over {sol} {{", f"  Variable Solution_old : Real = {sol}"]
+                    out += steps + [f"  {n['solution']}<next>@{lv} = {sol}", f"  {sol} = Solution_old", "}", f"advance {sol}"]
+        elif op.kind == "residual":
+            res = f"{n['residual']}@{lv}"
+            out += [f"loop over {res} {{", f"  {res} = ( {n['rhs']}@{lv} - {applied(n['solution'], lv)} )", "}",
+                    f"apply bc to {res}", f"communicate {res}"]
+        elif op.kind == "restrict":
+            app, r = f"{n['approximation']}@{lv}", f"{n['restriction']}@{lv + 1}"
+            out += [f"loop over {app} {{", f"  {app} = ( {r} * {sol} )", f"  {sol} = {app}", "}",
+                    f"communicate {app}", f"communicate {sol}",
+                    f"loop over {n['rhs']}@{lv} {{",
+                    f"  {n['rhs']}@{lv} = ( ( {r} * {n['residual']}@{lv + 1} ) + {applied(n['approximation'], lv)} )", "}"]
+        elif op.kind == "subtract":
+            out += [f"loop over {sol} {{", f"  {sol} -= {n['approximation']}@{lv}", "}", f"communicate {sol}"]
+        elif op.kind == "prolong_add":
+            out += [f"loop over {sol} {{",
+                    f"  {sol} += ( {op.omega!r} * ( {n['prolongation']}@{lv - 1} * {n['solution']}@{lv - 1} ) )", "}",
+                    f"apply bc to {sol}", f"communicate {sol}"]
+        else:
+            raise ValueError(f"unknown FAS op '{op.kind}'")
+    return "\n".join(out) + "\n}\n\n"
+
+
+# ----------------------------------------------------------------------------------------
 # the reference's generator interface for this path
 # ----------------------------------------------------------------------------------------
 
@@ -281,6 +339,9 @@ class B200ProgramGeneratorFAS:
         self.mpi_rank = mpi_rank
         self.fct_smoother = fct_smoother
         self.fct_CGS = fct_cgs
+        self._names = dict(solution=solution, rhs=rhs, residual=residual, approximation=FASApproximation,
+                           restriction=restriction, prolongation=prolongation, linear=op_linear, nonlinear=op_nonlinear,
+                           cgs=fct_cgs)
         self.fct_name = fct_name_mgcycle + f"@{self.max_level}"
         self.gamma = float(self._problem.parameters["gam"])
         self._device = device
@@ -357,14 +418,9 @@ class B200ProgramGeneratorFAS:
         return sum(times) / samples, sum(factors) / samples, sum(iterations) / samples
 
     def generate_cycle_function(self, *args):
-        """The statement list as text, one statement per line (the reference returns Layer-4 ExaSlang,
-        :428-437; the listings under tests/golden/fas_golden.json are the reference's)."""
+        """Layer-4 ExaSlang of the cycle function, like the reference's (:428-437)."""
         expression = next((a for a in args if type(a).__name__ == "Cycle"), None)
-        lines = [f"Function {self.fct_name} (  ) {{"]
-        for op in self.lower(expression):
-            lines.append(f"  {op.kind}@{op.level} omega={op.omega!r} sweeps={op.sweeps} newton_steps={op.newton_steps} "
-                         f"colored={op.colored}")
-        return "\n".join(lines + ["}"])
+        return emit_layer4(self.lower(expression), self.fct_name, self.fct_smoother, self._names)
 
     def close(self):
         if self._solver is not None:
