@@ -20,10 +20,29 @@ def main(argv=None):
     ap.add_argument("--pre", type=int, default=2)
     ap.add_argument("--post", type=int, default=2)
     ap.add_argument("--nruns", type=int, default=5)
+    ap.add_argument("--individual", default=None,
+                    help="file with the grammar string of an evolved FAS solver (FAS productions, depth = max - min level): "
+                         "evaluated through B200ProgramGeneratorFAS.generate_and_evaluate instead of the V(pre, post) cycle")
+    ap.add_argument("--template-smoother", action="store_true",
+                    help="with --individual: every smoothing step calls the template's Smoother (fct_smoother given)")
     ap.add_argument("--cpu", action="store_true", help="time the numpy restatement too (test infrastructure, one run)")
     ap.add_argument("--device", type=int, default=0)
     a = ap.parse_args(argv)
     from evostencils_b200 import fas
+    if a.individual:
+        from evostencils_b200 import problems
+        from evostencils_b200.grammar import Grammar
+        with open(a.individual) as fh:
+            string = fh.read().strip()
+        expression, _ = Grammar(problems.FAS_2D_BASIC, a.min_level, a.max_level, FAS=True).compile(string)
+        gen = fas.B200ProgramGeneratorFAS(fct_smoother="Smoother" if a.template_smoother else None,
+                                          min_level=a.min_level, max_level=a.max_level, device=a.device)
+        t, c, n = gen.generate_and_evaluate(expression, evaluation_samples=a.nruns)
+        gen.close()
+        print("total no of iterations", n)
+        print("time to solution (in ms) is", t)
+        print(f"convergence factor {c}")
+        return n, t
     solver = fas.FasSolver(a.min_level, a.max_level, device=a.device)
     ops = fas.v_cycle_ops(a.max_level, a.min_level, a.pre, a.post)
     solver.solve(ops)                                   # warm-up

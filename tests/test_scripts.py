@@ -45,6 +45,34 @@ def test_reference_solver_script_needs_a_gpu():
         load("evaluate_reference_solver").main(["--nruns", "1"])
 
 
+def test_fas_script_needs_a_gpu(tmp_path):
+    import json
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CPU-only check")
+    from evostencils_b200.engine import EngineError
+    script = load("evaluate_fas_solver")
+    with pytest.raises(EngineError, match="no CPU fallback"):
+        script.main(["--min-level", "3", "--max-level", "5", "--nruns", "1"])
+    golden = json.load(open(os.path.join(REPO, "tests", "golden", "fas_golden.json")))["fas_inline_v_two_coarsenings"]
+    path = tmp_path / "individual_0.txt"
+    path.write_text(golden["grammar"])
+    with pytest.raises(EngineError, match="no CPU fallback"):
+        script.main(["--individual", str(path), "--min-level", "4", "--max-level", "6", "--nruns", "1"])
+
+
+@pytest.mark.gpu
+def test_fas_script_evaluates_an_individual(tmp_path, capsys):
+    import json
+    golden = json.load(open(os.path.join(REPO, "tests", "golden", "fas_golden.json")))["fas_inline_v_two_coarsenings"]
+    path = tmp_path / "individual_0.txt"
+    path.write_text(golden["grammar"])
+    n, t = load("evaluate_fas_solver").main(["--individual", str(path), "--min-level", "4", "--max-level", "6", "--nruns", "2"])
+    assert 3 < n <= 100 and t > 0 and "total no of iterations" in capsys.readouterr().out
+    n2, t2 = load("evaluate_fas_solver").main(["--min-level", "3", "--max-level", "6", "--nruns", "2"])
+    assert n2 == 13                                                   # oracle: FAS V(2,2) on levels 3..6
+
+
 @pytest.mark.gpu
 def test_reference_solver_script_matches_the_oracle(capsys):
     """Config 1 in small: the `.exa3` default solver (V(2,1) RB-GS, CG below) on levels 3..6."""
