@@ -48,7 +48,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, with_costs, queue, schedule="static"):
+def _worker(rank, world, port, with_costs, queue, schedule="static", evaluators=1):
     sys.path.insert(0, REPO)
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -64,7 +64,8 @@ def _worker(rank, world, port, with_costs, queue, schedule="static"):
         return fake_evaluate(s)
 
     costs = [float((i * 7) % 5) for i in range(len(STRINGS))] if with_costs else None
-    out = population.evaluate_population(evaluate, STRINGS, costs=costs, schedule=schedule)
+    target = evaluate if evaluators == 1 else [evaluate] * evaluators        # several host threads per rank
+    out = population.evaluate_population(target, STRINGS, costs=costs, schedule=schedule)
     if schedule == "dynamic":                 # a second batch uses a fresh counter
         assert population.evaluate_population(fake_evaluate, STRINGS[:5], schedule=schedule) == out[:5]
     queue.put((rank, out, calls))
@@ -152,6 +153,27 @@ def test_world_size_2_gloo_dynamic_schedule():
     assert sorted(all_calls) == sorted(set(STRINGS))      # every unique individual exactly once
     by_rank = {rank: len(calls) for rank, _, calls in got}
     assert by_rank[1] > by_rank[0]                        # the fast rank took more of the queue
+
+
+def test_world_size_2_gloo_dynamic_schedule_with_two_evaluators_per_rank():
+    """The bench's configuration: ranks take individuals from the shared counter, two host threads each."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    queue = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, True, queue, "dynamic", 2)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = [queue.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    want = [fake_evaluate(s) for s in STRINGS]
+    all_calls = []
+    for rank, out, calls in got:
+        assert out == want, rank
+        all_calls += calls
+    assert sorted(all_calls) == sorted(set(STRINGS))      # every unique individual exactly once
 
 
 def test_batched_map_fitness_conventions():
