@@ -31,6 +31,7 @@ typedef struct {
     int n;
     long long total;
     double *sol, *alt, *rhs, *res, *cor, *init;
+    double* approx;                 /* FAS: restricted fine solution (allocated on first use) */
     int ne;
     int off[MAXE][3];
     double val[MAXE];
@@ -112,7 +113,7 @@ int mg_destroy(mg_workspace* ws) {
     mg_clear_smoothers(ws);
     for (int level = ws->lo; level <= ws->hi; ++level) {
         level_t* l = L(ws, level);
-        free(l->sol); free(l->alt); free(l->rhs); free(l->res); free(l->cor); free(l->init);
+        free(l->sol); free(l->alt); free(l->rhs); free(l->res); free(l->cor); free(l->init); free(l->approx);
     }
     free(ws->lv); free(ws->sm); free(ws->cy); free(ws);
     return MG_OK;
@@ -521,5 +522,166 @@ int mg_solve(mg_workspace* ws, int cycle, double tol, int max_its, double* hist,
         if (hist[it] < tol * hist[0]) { *converged = 1; break; }
     }
     if (ms) *ms = (float)(now_ms() - t0);
+    return MG_OK;
+}
+
+
+/* ---- nonlinear FAS stages (example_problems/FAS_2D_Basic/FAS_2D_Basic.exa4; oracle/fas_oracle.py is the
+ * numpy statement of the same arithmetic): -Laplace(u) + gam u e^u = f, 2D, one loop nest per statement ---- */
+typedef struct { double cc, cx, cy, gam; } fas_star_t;
+
+static int fas_prepare(mg_workspace* ws, int level, double gamma, level_t** out, fas_star_t* s) {
+    if (ws->dim != 2) return fail(MG_ERR_INVALID, "FAS stages: 2D only");
+    if (level < ws->lo || level > ws->hi) return fail(MG_ERR_INVALID, "level out of range");
+    level_t* l = L(ws, level);
+    if (!l->set || l->ne != 5) return fail(MG_ERR_INVALID, "FAS stages need a 5-point star operator");
+    s->gam = gamma; s->cc = s->cx = s->cy = 0.0;
+    for (int k = 0; k < 5; ++k) {
+        if (l->off[k][0] == 0 && l->off[k][1] == 0) s->cc = l->val[k];
+        else if (l->off[k][1] == 0) s->cx = l->val[k];
+        else s->cy = l->val[k];
+    }
+    if (!l->approx) l->approx = calloc(1, (size_t)l->total * sizeof(double));
+    *out = l;
+    return MG_OK;
+}
+
+/* (L u + gam e^u u): centre, E, W, N, S in the order the .exa4 declares the stencil (:18-24) */
+static inline double fas_apply(const fas_star_t* s, const double* u, long long i, int n) {
+    const double c = u[i];
+    double a = s->cc * c;
+    a = a + s->cx * u[i + 1];
+    a = a + s->cx * u[i - 1];
+    a = a + s->cy * u[i + n];
+    a = a + s->cy * u[i - n];
+    return a + (s->gam * exp(c)) * c;
+}
+
+static inline double fas_relax(const fas_star_t* s, const double* u, const double* f, long long i, int n, double w,
+                               int newton_steps) {
+    const double e = s->cx * u[i + 1], wt = s->cx * u[i - 1], nt = s->cy * u[i + n], st = s->cy * u[i - n];
+    double v = u[i];
+    const int steps = newton_steps > 0 ? newton_steps : 1;
+    for (int k = 0; k < steps; ++k) {
+        double a = s->cc * v;
+        a = a + e; a = a + wt; a = a + nt; a = a + st;
+        const double ev = exp(v);
+        const double num = f[i] - (a + (s->gam * ev) * v);
+        const double den = newton_steps > 0 ? s->cc + s->gam * (v + 1.0) * ev : s->cc;
+        v = v + w * (num / den);
+    }
+    return v;
+}
+
+int mg_fas_smooth(mg_workspace* ws, int level, double omega, double gamma, int sweeps, int newton_steps, int colored) {
+    level_t* l; fas_star_t s;
+    int rc = fas_prepare(ws, level, gamma, &l, &s);
+    if (rc) return rc;
+    const int n = l->n;
+    for (int k = 0; k < sweeps; ++k) {
+        if (colored) {
+            for (int colour = 0; colour < 2; ++colour) {
+#pragma omp parallel for schedule(static)
+                for (int y = 1; y <= n - 2; ++y)
+                    for (int x = 1 + ((1 + y + colour) & 1); x <= n - 2; x += 2) {
+                        const long long i = (long long)y * n + x;
+                        l->sol[i] = fas_relax(&s, l->sol, l->rhs, i, n, omega, newton_steps);
+                    }
+            }
+        } else {
+            memcpy(l->alt, l->sol, (size_t)l->total * sizeof(double));       /* boundary values */
+#pragma omp parallel for schedule(static)
+            for (int y = 1; y <= n - 2; ++y)
+                for (int x = 1; x <= n - 2; ++x) {
+                    const long long i = (long long)y * n + x;
+                    l->alt[i] = fas_relax(&s, l->sol, l->rhs, i, n, omega, newton_steps);
+                }
+            double* t = l->sol; l->sol = l->alt; l->alt = t;
+        }
+    }
+    return MG_OK;
+}
+
+int mg_fas_residual(mg_workspace* ws, int level, double gamma) {
+    level_t* l; fas_star_t s;
+    int rc = fas_prepare(ws, level, gamma, &l, &s);
+    if (rc) return rc;
+    const int n = l->n;
+    memset(l->res, 0, (size_t)l->total * sizeof(double));
+#pragma omp parallel for schedule(static)
+    for (int y = 1; y <= n - 2; ++y)
+        for (int x = 1; x <= n - 2; ++x) {
+            const long long i = (long long)y * n + x;
+            l->res[i] = l->rhs[i] - fas_apply(&s, l->sol, i, n);
+        }
+    return MG_OK;
+}
+
+static inline double fas_restrict_at(const double* fine, int nf, int X, int Y) {
+    static const double w1[3] = {0.25, 0.5, 0.25};
+    double acc = 0.0;
+    int first = 1;
+    for (int oy = -1; oy <= 1; ++oy)
+        for (int ox = -1; ox <= 1; ++ox) {
+            const double term = (w1[ox + 1] * w1[oy + 1]) * fine[(long long)(2 * Y + oy) * nf + 2 * X + ox];
+            acc = first ? term : acc + term;
+            first = 0;
+        }
+    return acc;
+}
+
+int mg_fas_restrict(mg_workspace* ws, int level, double gamma) {
+    level_t *lc, *lf; fas_star_t sc, sf;
+    int rc = fas_prepare(ws, level, gamma, &lc, &sc);
+    if (!rc) rc = fas_prepare(ws, level + 1, gamma, &lf, &sf);
+    if (rc) return rc;
+    const int n = lc->n;
+    memset(lc->approx, 0, (size_t)lc->total * sizeof(double));
+    memset(lc->sol, 0, (size_t)lc->total * sizeof(double));
+#pragma omp parallel for schedule(static)
+    for (int Y = 1; Y <= n - 2; ++Y)
+        for (int X = 1; X <= n - 2; ++X) {
+            const long long i = (long long)Y * n + X;
+            lc->approx[i] = fas_restrict_at(lf->sol, lf->n, X, Y);
+            lc->sol[i] = lc->approx[i];
+        }
+#pragma omp parallel for schedule(static)
+    for (int Y = 1; Y <= n - 2; ++Y)
+        for (int X = 1; X <= n - 2; ++X) {
+            const long long i = (long long)Y * n + X;
+            lc->rhs[i] = fas_restrict_at(lf->res, lf->n, X, Y) + fas_apply(&sc, lc->approx, i, n);
+        }
+    return MG_OK;
+}
+
+int mg_fas_subtract_approximation(mg_workspace* ws, int level) {
+    level_t* l; fas_star_t s;
+    int rc = fas_prepare(ws, level, 0.0, &l, &s);
+    if (rc) return rc;
+#pragma omp parallel for schedule(static)
+    for (long long i = 0; i < l->total; ++i) l->sol[i] = l->sol[i] - l->approx[i];
+    return MG_OK;
+}
+
+int mg_fas_residual_norm(mg_workspace* ws, int level, double gamma, double* out) {
+    level_t* l; fas_star_t s;
+    int rc = fas_prepare(ws, level, gamma, &l, &s);
+    if (rc) return rc;
+    const int n = l->n;
+    double* rows = calloc((size_t)n, sizeof(double));
+#pragma omp parallel for schedule(static)
+    for (int y = 1; y <= n - 2; ++y) {
+        double acc = 0.0;
+        for (int x = 1; x <= n - 2; ++x) {
+            const long long i = (long long)y * n + x;
+            const double r = l->rhs[i] - fas_apply(&s, l->sol, i, n);
+            acc = acc + r * r;
+        }
+        rows[y] = acc;
+    }
+    double sum = 0.0;
+    for (int y = 1; y <= n - 2; ++y) sum = sum + rows[y];
+    free(rows);
+    *out = sqrt(sum);
     return MG_OK;
 }

@@ -245,6 +245,30 @@ def test_oracle_stages_are_consistent():
     assert np.array_equal(fas.exact_solution(level), fo.exact_solution(level))
 
 
+def test_c_port_of_the_fas_stages_matches_the_numpy_oracle():
+    """oracle/mg_oracle_c.c carries the FAS statements too (the timed CPU figure of
+    scripts/evaluate_fas_solver.py); same arithmetic as oracle/fas_oracle.py up to libm's exp."""
+    import os
+    import subprocess
+    from evostencils_b200 import engine, problems
+    from evostencils_b200.grammar import Grammar
+    from oracle import fas_oracle as fo
+    oracle_dir = os.path.join(os.path.dirname(__file__), "..", "oracle")
+    subprocess.run(["make", "-s", "-C", oracle_dir], check=True)
+    clib = engine.load_library(os.path.join(oracle_dir, "_build", "libmgoracle.so"))
+    golden = load_golden()
+    for case, lo, hi in (("fas_inline_w_like", 3, 6), ("fas_inline_v_two_coarsenings", 4, 6), ("fas_v22_two_coarsenings", 3, 5)):
+        expression, _ = Grammar(problems.FAS_2D_BASIC, lo, hi, FAS=True).compile(golden[case]["grammar"])
+        ops = fas.lower(expression, template_smoother=golden[case]["template_smoother"])
+        solver = fas.FasSolver(lo, hi, lib=clib)
+        history, ms = solver.solve(ops)
+        u_ref, want = fo.solve_ops(ops, hi, lo)
+        assert len(history) == len(want), case
+        assert np.all(np.abs(np.array(history) - np.array(want)) <= 1e-10 * np.array(want) + 1e-13 * want[0]), case
+        assert np.max(np.abs(solver.solution() - u_ref)) <= 1e-10 * np.max(np.abs(u_ref)), case
+        solver.close()
+
+
 def close(got, want, tol=1e-12):
     scale = np.max(np.abs(want)) + 1e-300
     return np.max(np.abs(got - want)) <= tol * scale
