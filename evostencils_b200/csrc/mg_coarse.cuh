@@ -102,10 +102,10 @@ __device__ inline void coarse_bc(cplx* v, const Geom& g, cplx c) {
 __device__ inline void coarse_bc(double*, const Geom&, cplx) {}
 
 __device__ inline double t_abs(double a) { return fabs(a); }
-__device__ inline double t_abs(cplx a) { return hypot(a.re, a.im); }
+__device__ inline double t_abs(cplx a) { return t_hypot(a.re, a.im); }
 __device__ inline double t_sqrt(double a) { return sqrt(a); }
 __device__ inline cplx t_sqrt(cplx z) {      // principal square root
-    double r = hypot(z.re, z.im);
+    double r = t_hypot(z.re, z.im);
     double sr = sqrt(0.5 * (r + z.re));
     double si = sqrt(0.5 * (r - z.re));
     return make_cplx(sr, z.im < 0 ? -si : si);

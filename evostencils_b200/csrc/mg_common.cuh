@@ -5,6 +5,7 @@
 // --fmad=false so that results are bit-identical to the numpy oracle for real fp64.
 #pragma once
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdint.h>
 
 #define MG_MAX_DIM 3
@@ -38,6 +39,9 @@ __host__ __device__ inline cplx t_div(cplx a, cplx b) {
     return make_cplx((a.re * b.re + a.im * b.im) / d, (a.im * b.re - a.re * b.im) / d);
 }
 __host__ __device__ inline double t_div(double a, double b) { return a / b; }
+// |z| in plain IEEE operations (not hypot, whose last bit differs between libm and the device): the
+// oracle states the same formula, so complex Krylov scalars are bit-reproducible against it
+__host__ __device__ inline double t_hypot(double re, double im) { return sqrt(re * re + im * im); }
 
 // ---- geometry of one level -------------------------------------------------------------------
 struct Geom {

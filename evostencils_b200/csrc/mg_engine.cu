@@ -1,5 +1,6 @@
 // mg_engine.cu -- C ABI of the B200 multigrid cycle engine (see include/mgengine.h).
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a --fmad=false -lineinfo -shared ...
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>

@@ -376,7 +376,7 @@ __global__ void __launch_bounds__(256) k_norm_final(const T* __restrict__ partia
             out[0] = sqrt(*reinterpret_cast<double*>(&total));
         } else {
             cplx c = *reinterpret_cast<cplx*>(&total);
-            out[0] = sqrt(hypot(c.re, c.im));       // |sqrt(z)| = sqrt(|z|)
+            out[0] = sqrt(t_hypot(c.re, c.im));       // |sqrt(z)| = sqrt(|z|)
         }
     }
 }

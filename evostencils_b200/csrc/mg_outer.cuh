@@ -72,10 +72,10 @@ __global__ void __launch_bounds__(256) k_outer_dot_final(const T* __restrict__ p
 }
 
 __device__ __forceinline__ double t_modulus(double a) { return fabs(a); }
-__device__ __forceinline__ double t_modulus(cplx a) { return hypot(a.re, a.im); }
+__device__ __forceinline__ double t_modulus(cplx a) { return t_hypot(a.re, a.im); }
 __device__ __forceinline__ double t_root(double a) { return sqrt(a); }
 __device__ __forceinline__ cplx t_root(cplx z) {
-    double r = hypot(z.re, z.im);
+    double r = t_hypot(z.re, z.im);
     double sr = sqrt(0.5 * (r + z.re));
     double si = sqrt(0.5 * (r - z.re));
     return make_cplx(sr, z.im < 0 ? -si : si);

@@ -107,6 +107,7 @@ struct mg_workspace {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, mark[2] = {nullptr, nullptr};
     void* flush_buf = nullptr;
     size_t flush_bytes = 0;
+    double time_limit_s = 0.0;                  // wall-clock cap of one solve (mg_set_time_limit; 0 = none)
     long long launches = 0;                     // kernels launched (incl. graph replays)
     long long pending_count = 0;                // kernels issued since the counter was last sampled
     bool use_fast = true;                       // specialised kernels where applicable

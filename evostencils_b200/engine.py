@@ -32,7 +32,7 @@ EXPORTED_SYMBOLS = [
     "mg_create", "mg_create_slab", "mg_field_pointer", "mg_destroy", "mg_last_error", "mg_launch_count", "mg_set_operator", "mg_set_boundary",
     "mg_set_coarse_solver", "mg_add_smoother", "mg_clear_smoothers", "mg_upload", "mg_download",
     "mg_upload_device", "mg_save_initial_guess", "mg_restore_initial_guess", "mg_exec_ops", "mg_enqueue_ops", "mg_set_stream", "mg_build_cycle",
-    "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_set_outer_operator",
+    "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_set_time_limit", "mg_set_outer_operator",
     "mg_solve_bicgstab", "mg_synchronize",
     "mg_time_ops", "mg_profile_ops", "mg_mark", "mg_elapsed", "mg_flush_l2", "mg_set_fast_kernels",
     "mg_fas_smooth", "mg_fas_residual", "mg_fas_restrict", "mg_fas_subtract_approximation", "mg_fas_residual_norm",
@@ -44,71 +44,97 @@ class MgOp(C.Structure):
                 ("smoother", C.c_int32)]
 
 
+MG_ERR_INVALID, MG_ERR_CUDA, MG_ERR_STATE, MG_ERR_NOMEM, MG_ERR_TIMEOUT = -1, -2, -3, -4, -5
+
+
 class EngineError(RuntimeError):
-    pass
+    """`code` = the mg_status of the failing call (0: raised by the host side).  `fatal`: the engine
+    itself is broken (CUDA failure, out of memory, library missing) -- everything else is a property
+    of the individual being evaluated and maps to the reference's `(infinity,)*3` sentinel
+    (code_generation/exastencils.py:424-431)."""
+
+    def __init__(self, message, code=0, fatal=False):
+        super().__init__(message)
+        self.code = code
+        self.fatal = fatal or code in (MG_ERR_CUDA, MG_ERR_NOMEM)
 
 
 _lib = None
 
 
-def load_library(path: Optional[str] = None):
+def _signatures():
+    vp, i32, dbl = C.c_void_p, C.c_int, C.c_double
+    pi32, pdbl, pint, pflt = C.POINTER(C.c_int32), C.POINTER(dbl), C.POINTER(C.c_int), C.POINTER(C.c_float)
+    ops = C.POINTER(MgOp)
+    return {
+        "mg_create": [C.POINTER(vp), i32, i32, i32, i32, i32, i32],
+        "mg_create_slab": [C.POINTER(vp), i32, i32, i32, i32, i32, pi32, pi32],
+        "mg_field_pointer": [vp, i32, i32, i32, C.POINTER(vp), pi32, pi32, pi32, pi32],
+        "mg_destroy": [vp],
+        "mg_last_error": [],
+        "mg_launch_count": [vp, C.POINTER(C.c_int64)],
+        "mg_set_operator": [vp, i32, i32, i32, i32, pi32, pdbl],
+        "mg_set_boundary": [vp, i32, dbl],
+        "mg_set_coarse_solver": [vp, i32, i32, dbl],
+        "mg_add_smoother": [vp, i32, i32, i32, pi32, i32, pi32, pi32, i32, C.POINTER(C.c_uint32), pdbl, pint],
+        "mg_clear_smoothers": [vp],
+        "mg_upload": [vp, i32, i32, i32, vp],
+        "mg_download": [vp, i32, i32, i32, vp],
+        "mg_upload_device": [vp, i32, i32, i32, vp],
+        "mg_save_initial_guess": [vp],
+        "mg_restore_initial_guess": [vp],
+        "mg_exec_ops": [vp, ops, i32],
+        "mg_enqueue_ops": [vp, ops, i32],
+        "mg_set_stream": [vp, vp],
+        "mg_build_cycle": [vp, ops, i32, pint],
+        "mg_free_cycles": [vp],
+        "mg_run_cycles": [vp, i32, i32, pflt],
+        "mg_residual_norm": [vp, i32, pdbl],
+        "mg_solve": [vp, i32, dbl, i32, pdbl, pint, pint, pflt],
+        "mg_set_time_limit": [vp, dbl],
+        "mg_set_outer_operator": [vp, i32, pi32, pdbl],
+        "mg_solve_bicgstab": [vp, i32, dbl, i32, pdbl, pint, pint, pflt],
+        "mg_synchronize": [vp],
+        "mg_time_ops": [vp, ops, i32, i32, pflt],
+        "mg_profile_ops": [vp, ops, i32, pflt],
+        "mg_mark": [vp, i32],
+        "mg_elapsed": [vp, pflt],
+        "mg_flush_l2": [vp, C.c_size_t],
+        "mg_set_fast_kernels": [vp, i32],
+        "mg_fas_smooth": [vp, i32, dbl, dbl, i32, i32, i32],
+        "mg_fas_residual": [vp, i32, dbl],
+        "mg_fas_restrict": [vp, i32, dbl],
+        "mg_fas_subtract_approximation": [vp, i32],
+        "mg_fas_residual_norm": [vp, i32, dbl, pdbl],
+    }
+
+
+def bind(lib, strict=True):
+    """Attach the argument types of include/mgengine.h to a loaded library.  `strict`: every
+    declared entry point must be exported (the engine); otherwise absent ones are skipped (a library
+    that implements a subset of the ABI)."""
+    for name, argtypes in _signatures().items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            if strict:
+                raise EngineError(f"the engine library does not export {name}", fatal=True) from None
+            continue
+        fn.argtypes = argtypes
+    lib.mg_last_error.restype = C.c_char_p
+    return lib
+
+
+def load_library():
     """dlopen the engine; raises (loudly) when it has not been built."""
     global _lib
-    if _lib is not None and path is None:
+    if _lib is not None:
         return _lib
-    path = path or LIB_PATH
-    if not os.path.exists(path):
-        raise EngineError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
-                          "(the engine has no CPU fallback)")
-    lib = C.CDLL(path)
-    lib.mg_last_error.restype = C.c_char_p
-    vp, i32, dbl = C.c_void_p, C.c_int, C.c_double
-    lib.mg_create.argtypes = [C.POINTER(vp), i32, i32, i32, i32, i32, i32]
-    lib.mg_destroy.argtypes = [vp]
-    lib.mg_launch_count.argtypes = [vp, C.POINTER(C.c_int64)]
-    lib.mg_set_operator.argtypes = [vp, i32, i32, i32, i32, C.POINTER(C.c_int32), C.POINTER(dbl)]
-    lib.mg_set_boundary.argtypes = [vp, i32, dbl]
-    lib.mg_set_coarse_solver.argtypes = [vp, i32, i32, dbl]
-    lib.mg_add_smoother.argtypes = [vp, i32, i32, i32, C.POINTER(C.c_int32), i32, C.POINTER(C.c_int32),
-                                    C.POINTER(C.c_int32), i32, C.POINTER(C.c_uint32), C.POINTER(dbl),
-                                    C.POINTER(C.c_int)]
-    lib.mg_clear_smoothers.argtypes = [vp]
-    lib.mg_upload.argtypes = [vp, i32, i32, i32, vp]
-    lib.mg_download.argtypes = [vp, i32, i32, i32, vp]
-    lib.mg_upload_device.argtypes = [vp, i32, i32, i32, vp]
-    lib.mg_save_initial_guess.argtypes = [vp]
-    lib.mg_restore_initial_guess.argtypes = [vp]
-    lib.mg_exec_ops.argtypes = [vp, C.POINTER(MgOp), i32]
-    if path == LIB_PATH or hasattr(lib, "mg_enqueue_ops"):
-        lib.mg_enqueue_ops.argtypes = [vp, C.POINTER(MgOp), i32]
-        lib.mg_set_stream.argtypes = [vp, vp]
-    lib.mg_build_cycle.argtypes = [vp, C.POINTER(MgOp), i32, C.POINTER(C.c_int)]
-    lib.mg_free_cycles.argtypes = [vp]
-    lib.mg_run_cycles.argtypes = [vp, i32, i32, C.POINTER(C.c_float)]
-    lib.mg_residual_norm.argtypes = [vp, i32, C.POINTER(dbl)]
-    lib.mg_solve.argtypes = [vp, i32, dbl, i32, C.POINTER(dbl), C.POINTER(C.c_int), C.POINTER(C.c_int),
-                             C.POINTER(C.c_float)]
-    if path == LIB_PATH or hasattr(lib, "mg_solve_bicgstab"):   # the CPU oracle port has no outer Krylov solver
-        lib.mg_set_outer_operator.argtypes = [vp, i32, C.POINTER(C.c_int32), C.POINTER(dbl)]
-        lib.mg_solve_bicgstab.argtypes = [vp, i32, dbl, i32, C.POINTER(dbl), C.POINTER(C.c_int), C.POINTER(C.c_int),
-                                          C.POINTER(C.c_float)]
-    lib.mg_synchronize.argtypes = [vp]
-    lib.mg_time_ops.argtypes = [vp, C.POINTER(MgOp), i32, i32, C.POINTER(C.c_float)]
-    if path == LIB_PATH or hasattr(lib, "mg_profile_ops"):      # the CPU oracle port has no per-op profiler
-        lib.mg_profile_ops.argtypes = [vp, C.POINTER(MgOp), i32, C.POINTER(C.c_float)]
-    lib.mg_mark.argtypes = [vp, i32]
-    lib.mg_elapsed.argtypes = [vp, C.POINTER(C.c_float)]
-    lib.mg_flush_l2.argtypes = [vp, C.c_size_t]
-    lib.mg_set_fast_kernels.argtypes = [vp, i32]
-    if path == LIB_PATH or hasattr(lib, "mg_fas_smooth"):       # nonlinear FAS stages: CUDA engine only
-        lib.mg_fas_smooth.argtypes = [vp, i32, dbl, dbl, i32, i32, i32]
-        lib.mg_fas_residual.argtypes = [vp, i32, dbl]
-        lib.mg_fas_restrict.argtypes = [vp, i32, dbl]
-        lib.mg_fas_subtract_approximation.argtypes = [vp, i32]
-        lib.mg_fas_residual_norm.argtypes = [vp, i32, dbl, C.POINTER(dbl)]
-    if path == LIB_PATH:
-        _lib = lib
-    return lib
+    if not os.path.exists(LIB_PATH):
+        raise EngineError(f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(the engine has no CPU fallback)", fatal=True)
+    _lib = bind(C.CDLL(LIB_PATH))
+    return _lib
 
 
 # ----------------------------------------------------------------------------------------
@@ -187,7 +213,7 @@ class Workspace:
     # -- plumbing ------------------------------------------------------------------------
     def _check(self, rc):
         if rc != 0:
-            raise EngineError(f"mgengine error {rc}: {self.lib.mg_last_error().decode()}")
+            raise EngineError(f"mgengine error {rc}: {self.lib.mg_last_error().decode()}", code=rc)
 
     def close(self):
         if self._h:
@@ -411,6 +437,10 @@ class Workspace:
 
     def synchronize(self):
         self._check(self.lib.mg_synchronize(self._h))
+
+    def set_time_limit(self, seconds):
+        """Wall-clock cap of one solve; an expired solve raises EngineError(code=MG_ERR_TIMEOUT)."""
+        self._check(self.lib.mg_set_time_limit(self._h, float(seconds or 0.0)))
 
     def launch_count(self) -> int:
         out = C.c_int64()

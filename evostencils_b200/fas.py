@@ -206,14 +206,15 @@ class FasSolver:
     """FAS_2D_Basic on one GPU: level hierarchy, right-hand side of the enhanced test problem, zero
     initial guess; `solve` runs a cycle until the `.exa4`'s stopping rule holds."""
 
-    def __init__(self, min_level: int, max_level: int, gamma: float = GAMMA, device: int = 0, lib=None):
-        """`lib`: another library with the same C ABI (the tests and the CPU leg of
-        scripts/evaluate_fas_solver.py pass the C/OpenMP oracle port); default: the CUDA engine."""
+    def __init__(self, min_level: int, max_level: int, gamma: float = GAMMA, device: int = 0):
         self.min_level, self.max_level, self.gamma = min_level, max_level, gamma
-        self.ws = Workspace(2, min_level, max_level, 1, "f64", device, lib=lib)
+        self.ws = self._make_workspace(device)
         for level in range(min_level, max_level + 1):
             self.ws.set_operator(level, laplace_table(level))
         self.reset()
+
+    def _make_workspace(self, device):
+        return Workspace(2, self.min_level, self.max_level, 1, "f64", device)
 
     def reset(self):
         n = 2 ** self.max_level + 1

@@ -15,6 +15,7 @@ sentinel behaviour: a bad individual never raises, it returns `(infinity,)*3`.
 """
 from __future__ import annotations
 
+import contextlib
 import math
 import os
 import time
@@ -158,6 +159,11 @@ class B200ProgramGenerator:
         # evaluation i solves (one H2D copy per evaluation, off the critical path)
         self._prefetch_inputs = prefetch_inputs
         self._stage = None
+        # population.SoloGate shared with the other generators of this process, or None: when set, the
+        # solve runs overlapped with theirs (results do not depend on that) and the *time* objective is
+        # measured by replaying the captured cycle while the others pause
+        self.solo_timing = None
+        self.solo_timing_cycles = 3
         self._workspace: Optional[Workspace] = None
         self._workspace_key = None
         self._inputs_key = None
@@ -166,6 +172,8 @@ class B200ProgramGenerator:
         self.last_residual_history: List[float] = []
         self.last_launch_count = 0
         self.last_program = None
+        self.last_error = None
+        self.last_sweep = []
         self._default_cycle_cache = {}
         self.h2d_bytes = 0
         self.d2h_bytes = 0
@@ -382,6 +390,8 @@ class B200ProgramGenerator:
                 return _cache[key]
         cycle = ws.build_cycle(program.ops, default_cycle)
         self.last_program = program
+        # wall-clock cap of one run of the solver (`timeout_evaluate`, exastencils.py:42, 424-431)
+        ws.set_time_limit(self.timeout_evaluate)
         tol = p.solver.target_reduction
         max_its = p.solver.max_iterations if max_iterations is None else max_iterations
         total_time = total_rho = total_n = 0.0
@@ -390,6 +400,8 @@ class B200ProgramGenerator:
             merged = dict(p.parameters)
             merged.update(params)
             ws.set_outer_operator(lowering._canon(stencils.helmholtz_2d(p.spacing(program.max_level), merged["k"], 1.0)))
+        gate = self.solo_timing
+        shared = gate.shared if gate is not None else contextlib.nullcontext
         for sample in range(evaluation_samples):
             if sample == 0 and p.outer == "mg":
                 self._load_inputs(ws, params, self._custom_rhs, self._custom_u0)
@@ -399,16 +411,22 @@ class B200ProgramGenerator:
                 self._inputs_key = None          # the preconditioner calls overwrite the right-hand side field
                 self._load_inputs(ws, params, self._custom_rhs, self._custom_u0)
             if p.outer == "bicgstab":
-                history, converged, ms = ws.solve_bicgstab(cycle, tol, max_its)
+                # small grids: the whole solve is the timed unit, so it runs alone when a gate is set
+                with (gate.exclusive() if gate is not None else contextlib.nullcontext()):
+                    history, converged, ms = ws.solve_bicgstab(cycle, tol, max_its)
                 self.d2h_bytes += 8 * len(history)
                 self.last_residual_history = history
                 rho, n = summarise_bicgstab(history, converged, infinity, self._solver_iteration_limit)
             else:
-                history, converged, ms = ws.solve(cycle, tol, max_its)
+                with shared():
+                    history, converged, ms = ws.solve(cycle, tol, max_its)
                 self.d2h_bytes += 8 * len(history)
                 self.last_residual_history = history
                 rho, n = summarise_history(history, len(history) - 1, converged, infinity,
                                            self._solver_iteration_limit)
+                if gate is not None and len(history) > 1:
+                    with gate.exclusive():
+                        ms = ws.run_cycles(cycle, self.solo_timing_cycles) / self.solo_timing_cycles * (len(history) - 1)
             if n >= infinity or rho > 1:
                 return ms, rho, n
             if math.isinf(rho) or math.isnan(rho):
@@ -421,24 +439,48 @@ class B200ProgramGenerator:
 
     def generate_and_evaluate(self, expression, storages, min_level: int, max_level: int, solver_program: str,
                               infinity=1e100, evaluation_samples=3, global_variable_values=None):
+        """exastencils.py:485-537.  A bad individual never raises: constructs the engine cannot execute,
+        an evaluation that exceeds `evaluation_timeout` seconds and per-individual engine errors all give
+        the sentinel `(infinity,)*3`, like the reference's failed code generation / non-zero exit /
+        `subprocess.TimeoutExpired` (:424-431, :493-507).  Only a broken engine (CUDA failure, out of
+        memory, missing library: `EngineError.fatal`) propagates."""
         if global_variable_values is None:
             global_variable_values = {}
-        t0 = time.time()
-        try:
-            program = lowering.lower(expression, min_level, max_level)
-        except lowering.LoweringError:
-            return infinity, infinity, infinity
-        self._counter += 1
-        self._average_generation_time += (time.time() - t0 - self._average_generation_time) / self._counter
         mapping = dict(self._parameters)
         mapping.update(global_variable_values)
-        n = 3 if "k" in mapping else 1          # exastencils.py:518-532: k, 2k, 4k on the same grid
+        n = 3 if "k" in global_variable_values else 1     # :518-521: k, 2k, 4k on the same grid
         avg_t = avg_rho = avg_n = 0.0
+        self.last_sweep = []
         for _ in range(n):
+            t0 = time.time()
+            try:
+                # The stencil values of the IR are numbers, so the individual is lowered again for every
+                # wave number: operators and local-solve matrices are rebuilt from the problem definition
+                # at the current parameter values (the reference substitutes the global variable in the
+                # generated program instead, :518-532).
+                override = None
+                if mapping and set(mapping) & set(self._problem.parameters):
+                    merged = dict(self._problem.parameters)
+                    merged.update(mapping)
+                    cache = {}
+
+                    def override(level, _cache=cache, _merged=merged):
+                        if level not in _cache:
+                            _cache[level] = self._problem.system_operator(level, 0, _merged)
+                        return _cache[level]
+                program = lowering.lower(expression, min_level, max_level, override)
+            except lowering.LoweringError:
+                return infinity, infinity, infinity
+            self._counter += 1
+            self._average_generation_time += (time.time() - t0 - self._average_generation_time) / self._counter
             try:
                 runtime, rho, its = self.evaluate_program(program, mapping, infinity, evaluation_samples)
-            except EngineError:
-                raise
+            except EngineError as exc:
+                if exc.fatal:
+                    raise
+                self.last_error = str(exc)
+                return infinity, infinity, infinity
+            self.last_sweep.append((dict(mapping), runtime, rho, its, list(self.last_residual_history)))
             avg_t += runtime
             avg_rho += rho
             avg_n += its

@@ -273,9 +273,13 @@ def local_solve_statements(smoothing_operator, system_operator, level, omega, pa
 # main traversal
 # ----------------------------------------------------------------------------------------
 class _Lowerer:
-    def __init__(self, min_level, max_level):
+    def __init__(self, min_level, max_level, operator_override=None):
         self.min_level = min_level
         self.max_level = max_level
+        # level -> SystemOperator that replaces the graph's own system operator on that level: the same
+        # individual evaluated for other PDE parameters (k, 2k, 4k of exastencils.py:518-532 -- there
+        # the parameter is a global variable of the generated program, here the stencil values are numbers)
+        self.operator_override = operator_override
         self.ops: List[object] = []
         self.emitted = set()
         self.operators: Dict[int, list] = {}
@@ -285,8 +289,25 @@ class _Lowerer:
     def sol_kind(self, level):
         return SOL
 
+    def system_operator(self, system_operator, level):
+        return self.operator_override(level) if self.operator_override else system_operator
+
+    def smoothing_operator(self, smoothing_operator, level):
+        """The smoother marker of the graph, rebuilt around the overriding system operator."""
+        if not self.operator_override:
+            return smoothing_operator
+        from . import ir
+        operator = self.operator_override(level)
+        if _is(smoothing_operator, "ElementwiseDiagonal"):
+            return ir.ElementwiseDiagonal(operator)
+        if _is(smoothing_operator, "Diagonal"):
+            return ir.Diagonal(operator)
+        if hasattr(smoothing_operator, "block_sizes"):
+            return ir.BlockDiagonalOperator(operator, smoothing_operator.block_sizes)
+        raise LoweringError("the smoothing operator can not be rebuilt for other PDE parameters")
+
     def note_operator(self, system_operator, level):
-        table = operator_table(system_operator)
+        table = operator_table(self.system_operator(system_operator, level))
         if level in self.operators and self.operators[level] != table:
             raise LoweringError(f"two different system operators on level {level}")
         self.operators[level] = table
@@ -333,8 +354,9 @@ class _Lowerer:
                     residual = op2
                     self.preamble(residual.rhs, residual.rhs, residual.approximation, expression.approximation)
                     self.note_operator(residual.operator, level)
-                    self.ops.extend(local_solve_statements(op1.operand, residual.operator, level, weight,
-                                                           expression.partitioning))
+                    self.ops.extend(local_solve_statements(self.smoothing_operator(op1.operand, level),
+                                                           self.system_operator(residual.operator, level), level,
+                                                           weight, expression.partitioning))
                 else:
                     raise LoweringError("Unsupported operator")
             else:
@@ -365,7 +387,7 @@ class _Lowerer:
                     if sub is not None:
                         # previously optimised cycle for the levels below
                         # (optimization/program.py:863-897: `best_expression`)
-                        lw = _Lowerer(self.min_level, level)
+                        lw = _Lowerer(self.min_level, level, self.operator_override)
                         lw.emit(sub)
                         inner = lw.ops
                         for lv, table in lw.operators.items():
@@ -379,11 +401,12 @@ class _Lowerer:
             raise LoweringError(f"Not implemented: {type(expression).__name__}")
 
 
-def lower(expression, min_level: int, max_level: int) -> Program:
+def lower(expression, min_level: int, max_level: int, operator_override=None) -> Program:
     """IR graph of one solver -> `Program`.  `min_level` is the level of the coarse-grid
     solver, `max_level` the finest level (same meaning as the arguments of
-    `generate_cycle_function`, exastencils.py:318-336)."""
-    lw = _Lowerer(min_level, max_level)
+    `generate_cycle_function`, exastencils.py:318-336).  `operator_override(level)` -> system operator
+    used instead of the graph's own (same individual, other PDE parameter values)."""
+    lw = _Lowerer(min_level, max_level, operator_override)
     lw.emit(expression)
     if lw.n_fields is None:
         raise LoweringError("empty program")

@@ -12,6 +12,7 @@ independent, so there is no data-path collective -- only this result exchange.
 """
 from __future__ import annotations
 
+import contextlib
 from typing import Callable, List, Optional, Sequence, Tuple
 
 Result = Tuple[float, float, float]
@@ -91,13 +92,18 @@ class WorkQueue:
         return k
 
 
-def gather_results(local: dict, n_items: int, group=None, device=None) -> List[Result]:
+def gather_results(local: dict, n_items: int, group=None, device=None, error: Optional[BaseException] = None) -> List[Result]:
     """Combine `{index: (t, rho, n)}` of every rank into the full list on every rank.
 
     Each slot is written by exactly one rank and is 0.0 elsewhere, so the SUM all-reduce is exact
-    (x + 0.0 == x for every finite x and for +inf) and independent of the reduction order."""
+    (x + 0.0 == x for every finite x and for +inf) and independent of the reduction order.
+    `error`: the exception that stopped this rank's evaluations, if any.  The rank still takes part
+    in the exchange (an extra row counts the failed ranks), so the others are not left waiting in
+    the collective; afterwards every rank raises."""
     rank, world, dist = _world(group)
     if world == 1:
+        if error is not None:
+            raise error
         missing = [i for i in range(n_items) if i not in local]
         if missing:
             raise ValueError(f"results missing for individuals {missing[:5]}")
@@ -105,12 +111,19 @@ def gather_results(local: dict, n_items: int, group=None, device=None) -> List[R
     import torch
     if device is None:
         device = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
-    buf = torch.zeros((n_items, 4), dtype=torch.float64)
+    buf = torch.zeros((n_items + 1, 4), dtype=torch.float64)
     for i, r in local.items():
         buf[i, 0], buf[i, 1], buf[i, 2], buf[i, 3] = float(r[0]), float(r[1]), float(r[2]), 1.0
+    buf[n_items, 0] = 0.0 if error is None else 1.0
     buf = buf.to(device)
     dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
     buf = buf.cpu()
+    failed = int(buf[n_items, 0].item())
+    if error is not None:
+        raise error
+    if failed:
+        raise RuntimeError(f"the evaluation failed on {failed} other rank(s)")
+    buf = buf[:n_items]
     counts = buf[:, 3]
     if not bool((counts == 1.0).all()):
         bad = [i for i in range(n_items) if counts[i] != 1.0]
@@ -157,6 +170,7 @@ def run_concurrently(evaluators: Sequence[Callable[[str], Result]], jobs, unique
         for t in threads:
             t.join()
     if errors:
+        errors[0].partial_results = local
         raise errors[0]
     return local
 
@@ -189,8 +203,12 @@ def evaluate_population(evaluate, strings: Sequence[str], group=None, device=Non
         jobs = [order[k] for k in shard_indices(len(order), rank, world)]
     else:
         raise ValueError("schedule must be 'static' or 'dynamic'")
-    local = run_concurrently(evaluators, jobs, unique)
-    results = gather_results(local, len(unique), group, device)
+    error = None
+    try:
+        local = run_concurrently(evaluators, jobs, unique)
+    except Exception as exc:            # still join the exchange, then raise on every rank
+        error, local = exc, getattr(exc, "partial_results", {})
+    results = gather_results(local, len(unique), group, device, error)
     return [results[b] for b in back]
 
 
@@ -208,24 +226,119 @@ def make_evaluator(generator, grammar, min_level: int, max_level: int, evaluatio
     return evaluate
 
 
+class SoloGate:
+    """Readers-writer gate shared by the generators of one rank: ordinary solves hold it `shared`
+    (they overlap on the GPU), the timing replay of an individual holds it `exclusive` (nothing else
+    of this process runs on the GPU meanwhile)."""
+
+    def __init__(self):
+        import threading
+        self._cond = threading.Condition()
+        self._readers = 0
+        self._writer = False
+        self._writers_waiting = 0
+
+    @contextlib.contextmanager
+    def shared(self):
+        with self._cond:
+            while self._writer or self._writers_waiting:
+                self._cond.wait()
+            self._readers += 1
+        try:
+            yield
+        finally:
+            with self._cond:
+                self._readers -= 1
+                self._cond.notify_all()
+
+    @contextlib.contextmanager
+    def exclusive(self):
+        with self._cond:
+            self._writers_waiting += 1
+            while self._writer or self._readers:
+                self._cond.wait()
+            self._writers_waiting -= 1
+            self._writer = True
+        try:
+            yield
+        finally:
+            with self._cond:
+                self._writer = False
+                self._cond.notify_all()
+
+
+def node_count(individual) -> int:
+    """Number of nodes of a derivation tree: `len(individual)` of a deap PrimitiveTree; for a grammar
+    string one per call, name and literal (a block-shape tuple is one terminal, multigrid.py:388-407)."""
+    if not isinstance(individual, str):
+        return len(individual)
+    import ast
+
+    def count(node):
+        if isinstance(node, ast.Call):
+            return 1 + sum(count(a) for a in node.args)
+        return 1
+    return count(ast.parse(individual, mode="eval").body)
+
+
+def fitness_from_result(result: Result, objectives: str = "multi", infinity: float = 1e100):
+    """(time_ms, rho, n) -> the fitness tuple of the reference's wrappers: `multi` =
+    evaluate_multiple_objectives (program.py:419-453): (rho, t / n), or (rho, infinity) when the solver
+    did not converge; `single` = evaluate_single_objective (:386-417): (t,), or (sqrt(rho) sqrt(n),)."""
+    t, rho, n = result
+    if objectives == "single":
+        if n >= infinity:
+            return (rho ** 0.5 * n ** 0.5,)
+        return (t,)
+    if objectives != "multi":
+        raise ValueError("objectives must be 'multi' or 'single'")
+    if n >= infinity:
+        return (rho, infinity)
+    return (rho, t / n)
+
+
+MAX_INDIVIDUAL_SIZE = 150            # program.py:390, 423: larger trees are not evaluated
+
+
 def batched_map(generator, grammar, min_level, max_level, evaluation_samples=1, group=None, infinity=1e100,
-                schedule="static"):
+                schedule="static", objectives=None, solo_timing=True):
     """A `toolbox.map` replacement (the reference's extension point, program.py:491, 577):
     `toolbox.register("map", batched_map(...))` makes one generation's evaluations run sharded.
-    The mapped function is ignored for individuals given as grammar strings / PrimitiveTrees:
-    they are evaluated through `generate_and_evaluate` and returned as (rho, t/n) fitness tuples
-    like `evaluate_multiple_objectives` (program.py:419-453)."""
+    Individuals (grammar strings / PrimitiveTrees) are evaluated through `generate_and_evaluate` and
+    mapped to the fitness tuple of the wrapper that `toolbox.map` was called with: the function's name
+    (`evaluate_single_objective` / `evaluate_multiple_objectives`, also through functools.partial) or
+    the explicit `objectives` = "single" | "multi" selects the mapping (program.py:386-453); trees of
+    more than 150 nodes get the infinity tuple without being evaluated (:390, :423).
+
+    `solo_timing`: with several generators per rank the solves overlap on the GPU for throughput, which
+    makes the measured time of an individual depend on its neighbour; the time objective is therefore
+    taken from a replay of the already captured cycle graph while the rank's other generators pause
+    (`SoloGate`, `B200ProgramGenerator.solo_timing`): time = replayed ms per cycle x iterations.
+    False keeps the overlapped timings.  One generator per rank: solves are solo anyway."""
     generators = list(generator) if isinstance(generator, (list, tuple)) else [generator]
+    if solo_timing and len(generators) > 1:
+        gate = SoloGate()
+        for g in generators:
+            g.solo_timing = gate
     # several generators (one workspace and stream each): their evaluations overlap on the GPU
     evaluators = [make_evaluator(g, grammar, min_level, max_level, evaluation_samples, infinity) for g in generators]
 
-    def _map(_function, individuals):
-        strings = [str(ind) for ind in individuals]
-        out = []
-        for t, rho, n in evaluate_population(evaluators, strings, group, schedule=schedule):
-            if n >= infinity:                            # program.py:447-448
-                out.append((rho, infinity))
-            else:
-                out.append((rho, t / n))
+    def _objectives(function):
+        if objectives is not None:
+            return objectives
+        f = function
+        while hasattr(f, "func"):          # functools.partial
+            f = f.func
+        return "single" if "single" in getattr(f, "__name__", "") else "multi"
+
+    def _map(function, individuals):
+        individuals = list(individuals)
+        kind = _objectives(function)
+        too_large = (infinity,) if kind == "single" else (infinity, infinity)
+        keep = [i for i, ind in enumerate(individuals) if node_count(ind) <= MAX_INDIVIDUAL_SIZE]
+        strings = [str(individuals[i]) for i in keep]
+        out = [too_large] * len(individuals)
+        for i, result in zip(keep, evaluate_population(evaluators, strings, group, schedule=schedule)):
+            out[i] = fitness_from_result(result, kind, infinity)
         return out
     return _map

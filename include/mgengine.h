@@ -39,7 +39,8 @@ typedef enum {
     MG_ERR_INVALID = -1,      /* bad argument / unsupported construct */
     MG_ERR_CUDA = -2,         /* a CUDA runtime call failed */
     MG_ERR_STATE = -3,        /* call sequence violated (e.g. operator missing) */
-    MG_ERR_NOMEM = -4
+    MG_ERR_NOMEM = -4,
+    MG_ERR_TIMEOUT = -5       /* a solve exceeded the limit set by mg_set_time_limit */
 } mg_status;
 
 typedef enum { MG_F64 = 0, MG_C128 = 1 } mg_dtype;
@@ -146,6 +147,11 @@ int mg_residual_norm(mg_workspace* ws, int level, double* out);
  * res_hist must hold max_its + 1 doubles.  *ms = device time of the solve phase. */
 int mg_solve(mg_workspace* ws, int cycle, double tol, int max_its, double* res_hist,
              int* n_its, int* converged, float* ms);
+/* Wall-clock cap (seconds, 0 = none) of one mg_solve / mg_solve_bicgstab call: the reference kills the
+ * generated binary after `timeout_evaluate` seconds and scores the individual with the sentinel triple
+ * (code_generation/exastencils.py:42, 424-431).  Checked after every outer iteration; an expired solve
+ * returns MG_ERR_TIMEOUT with res_hist / n_its filled up to that iteration. */
+int mg_set_time_limit(mg_workspace* ws, double seconds);
 /* Preconditioned BiCGStab outer solver of the Helmholtz configuration
  * (example_problems/Helmholtz/2D_FD_Helmholtz_fromL3.exa3:144-200): the cycle is the preconditioner
  * (u = 0; f = p; cycle), `A` the unshifted operator of the finest level set by mg_set_outer_operator.

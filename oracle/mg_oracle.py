@@ -61,6 +61,78 @@ def _interior(a: np.ndarray):
     return a[tuple([slice(1, -1)] * a.ndim)]
 
 
+# ----------------------------------------------------------------------------------------
+# complex arithmetic, spelled out
+# ----------------------------------------------------------------------------------------
+# The engine evaluates complex products / quotients / roots with the textbook formulas in separate
+# IEEE operations (csrc/mg_common.cuh t_mul / t_div, compiled with --fmad=false).  numpy's and
+# CPython's complex multiply may contract to FMA (AVX2/AVX-512 loops) and both divide by Smith's
+# method, so `a * b` on complex128 is NOT bit-reproducible across machines.  Preconditioned BiCGStab
+# at k = 80 amplifies last-bit differences into different iteration counts, and `north_star` asks
+# for identical counts -- so the oracle states every complex operation in real arithmetic, in the
+# operand order of the engine.  Real data takes the plain numpy path.
+
+def _is_complex(x) -> bool:
+    return isinstance(x, complex) or np.iscomplexobj(x)
+
+
+def _pack(re, im):
+    out = np.empty(np.shape(re), dtype=np.complex128)
+    out.real = re
+    out.imag = im
+    return out if out.shape else complex(out)
+
+
+def mul(a, b):
+    """a * b.  Complex: (a.re b.re - a.im b.im, a.re b.im + a.im b.re), four products, one
+    subtraction, one addition, no FMA (t_mul); real operands are promoted with a zero imaginary part
+    like the engine's operator tables."""
+    if not (_is_complex(a) or _is_complex(b)):
+        return a * b
+    ar, ai = np.real(a), np.imag(a)
+    br, bi = np.real(b), np.imag(b)
+    return _pack(ar * br - ai * bi, ar * bi + ai * br)
+
+
+def scale(s, a):
+    """real scalar * field (t_scale): component-wise for complex data."""
+    if not _is_complex(a):
+        return s * a
+    return _pack(s * np.real(a), s * np.imag(a))
+
+
+def div(a, b):
+    """a / b for scalars.  Complex: ((a.re b.re + a.im b.im) / d, (a.im b.re - a.re b.im) / d) with
+    d = b.re^2 + b.im^2 (t_div)."""
+    if not (_is_complex(a) or _is_complex(b)):
+        return a / b
+    ar, ai, br, bi = float(np.real(a)), float(np.imag(a)), float(np.real(b)), float(np.imag(b))
+    d = br * br + bi * bi
+    with np.errstate(all="ignore"):
+        return complex(np.float64(ar * br + ai * bi) / np.float64(d), np.float64(ai * br - ar * bi) / np.float64(d))
+
+
+def modulus(z) -> float:
+    """|z| = sqrt(re^2 + im^2) (t_abs)."""
+    if not _is_complex(z):
+        return abs(float(z))
+    re, im = float(np.real(z)), float(np.imag(z))
+    return math.sqrt(re * re + im * im)
+
+
+def root(z):
+    """Principal square root: r = |z|, (sqrt((r + re)/2), sign(im) sqrt((r - re)/2)) (t_sqrt)."""
+    if not _is_complex(z):
+        return math.sqrt(z) if z >= 0 else float("nan")
+    re, im = float(np.real(z)), float(np.imag(z))
+    r = modulus(z)
+    if not math.isfinite(r):
+        return complex(float("nan"), float("nan"))
+    sr = math.sqrt(0.5 * (r + re))
+    si = math.sqrt(max(0.0, 0.5 * (r - re)))
+    return complex(sr, -si if im < 0 else si)
+
+
 def butterfly_sum(v: np.ndarray) -> float:
     """Sum of `DOT_LANES` lane partials exactly as the coarse-solver CTA forms it:
     xor-butterfly (16, 8, 4, 2, 1) inside each warp, then the same over the warp sums."""
@@ -80,7 +152,7 @@ def lane_dot(a: np.ndarray, b: np.ndarray):
     """dot(a, b) without conjugation over flat vectors, lane-strided partials + butterfly."""
     n = a.size
     pad = (-n) % DOT_LANES
-    prod = a.reshape(-1) * b.reshape(-1)
+    prod = mul(a.reshape(-1), b.reshape(-1))
     if pad:
         prod = np.concatenate([prod, np.zeros(pad, dtype=prod.dtype)])
     rows = prod.reshape(-1, DOT_LANES)
@@ -90,6 +162,39 @@ def lane_dot(a: np.ndarray, b: np.ndarray):
     return butterfly_sum(part)
 
 
+GRID_DOT_BLOCKS = 1184   # CTAs of the engine's grid-wide dot / norm kernels (8 x 148 SMs), 256 threads each
+
+
+def grid_dot(a: np.ndarray, b: np.ndarray):
+    """sum over the interior of a * b (no conjugation) in the order of the engine's two-stage
+    reduction (csrc/mg_outer.cuh k_outer_dot + k_outer_dot_final; 2D fields): CTA c of
+    min(n, 1184) owns the rows c, c + grid, ...; thread t of 256 accumulates x = 1 + t, 257 + t, ...
+    of each of them in turn; butterfly over the CTA; then thread t adds the CTA sums t, t + 256, ...
+    and the same butterfly gives the total."""
+    n = a.shape[0]
+    assert a.ndim == 2, "grid_dot mirrors the 2D kernel"
+    blocks = min(n, GRID_DOT_BLOCKS)
+    prod = mul(a, b)
+    lanes = np.zeros((blocks, DOT_LANES), dtype=prod.dtype)
+    for first in range(0, n, blocks):                     # one row per CTA and round
+        rows = np.arange(first, min(first + blocks, n))
+        rows = rows[(rows >= 1) & (rows <= n - 2)]
+        if rows.size == 0:
+            continue
+        for x0 in range(1, n - 1, DOT_LANES):
+            x1 = min(x0 + DOT_LANES, n - 1)
+            lanes[rows - first, : x1 - x0] = lanes[rows - first, : x1 - x0] + prod[rows, x0:x1]
+    partial = np.array([butterfly_sum(lanes[c]) for c in range(blocks)], dtype=prod.dtype)
+    pad = (-blocks) % DOT_LANES
+    if pad:
+        partial = np.concatenate([partial, np.zeros(pad, dtype=prod.dtype)])
+    rounds = partial.reshape(-1, DOT_LANES)
+    acc = np.zeros(DOT_LANES, dtype=prod.dtype)
+    for r in rounds:
+        acc = acc + r
+    return butterfly_sum(acc)
+
+
 @dataclass
 class BoundaryCondition:
     kind: str = "dirichlet"               # "dirichlet" | "helmholtz_robin"
@@ -97,7 +202,7 @@ class BoundaryCondition:
 
     def factor(self, h):
         # u_0 = u_1 / (1 - i k h)   (Helmholtz/...exa4:25-59)
-        return 1.0 / (1.0 - 1j * self.k * h)
+        return div(complex(1.0, 0.0), complex(1.0, -self.k * h))
 
 
 class Hierarchy:
@@ -140,8 +245,8 @@ class Hierarchy:
             return
         c = self.bc.factor(1.0 / 2 ** level)
         for u in arrays:
-            u[:, 0] = u[:, 1] * c
-            u[:, -1] = u[:, -2] * c
+            u[:, 0] = mul(u[:, 1], c)
+            u[:, -1] = mul(u[:, -2], c)
             u[0, :] = 0
             u[-1, :] = 0
 
@@ -155,7 +260,8 @@ def apply_operator(table, fields: List[np.ndarray], row: int):
     acc = None
     for j, entries in enumerate(table[row]):
         for off, val in entries:
-            term = val * _shift(fields[j], off)
+            operand = _shift(fields[j], off)
+            term = mul(complex(val), operand) if np.iscomplexobj(operand) else val * operand
             acc = term if acc is None else acc + term
     if acc is None:
         acc = np.zeros_like(_interior(fields[0]))
@@ -190,7 +296,7 @@ def op_restrict(h: Hierarchy, coarse_level, src_kind="res"):
             for c in off:
                 w *= w1[c]
             sl = tuple(slice(2 + c, 2 * (nc - 1) - 2 + c + 1, 2) for c in off)
-            term = w * fine[sl]
+            term = scale(w, fine[sl])
             acc = term if acc is None else acc + term
         _interior(h.rhs[coarse_level][i])[...] = acc
 
@@ -209,14 +315,14 @@ def prolongation_interior(coarse: np.ndarray, d: int):
             src = tuple(slice(c, nc - 1 + c) if p else slice(0, nc) for p, c in zip(parity, corner))
             term = coarse[src]
             acc = term if acc is None else acc + term
-        out[dst] = (0.5 ** k) * acc if k else acc
+        out[dst] = scale(0.5 ** k, acc) if k else acc
     return _interior(out)
 
 
 def op_prolong_add(h: Hierarchy, fine_level, omega, src_kind="sol"):
     for i in range(h.n_fields):
         coarse = h.field(src_kind, fine_level - 1)[i]
-        _interior(h.sol[fine_level][i])[...] += omega * prolongation_interior(coarse, h.dimension)
+        _interior(h.sol[fine_level][i])[...] += scale(omega, prolongation_interior(coarse, h.dimension))
     h.apply_bc(fine_level, h.sol[fine_level])
 
 
@@ -257,7 +363,7 @@ def op_local_solve(h: Hierarchy, stmt):
             for s, (f, _) in enumerate(slots):
                 delta = None
                 for t in range(m):
-                    term = W[s, t] * r[t]
+                    term = mul(W[s, t], r[t])
                     delta = term if delta is None else delta + term
                 target = _interior(sol[f])
                 if colour is None:
@@ -302,7 +408,7 @@ def op_local_solve(h: Hierarchy, stmt):
         for a, s in enumerate(vidx):
             delta = None
             for b_, t in enumerate(vidx):
-                term = W[a, b_] * gathered[b_]
+                term = mul(W[a, b_], gathered[b_])
                 delta = term if delta is None else delta + term
             f, ix = index[a]
             sol[f][ix] = sol[f][ix] + delta
@@ -339,21 +445,21 @@ def op_coarse_cg(h: Hierarchy, level, max_its=1000, reduction=1e-12):
     p = r.copy()
     xs = np.zeros_like(r)
     rs = lane_dot(r, r)
-    r0 = math.sqrt(rs)
+    r0 = modulus(root(rs))
     if r0 == 0.0:
         return 0
     its = 0
     for its in range(1, max_its + 1):
         _scatter_interior(work, p)
         ap = _apply_flat(h, level, work)
-        alpha = rs / lane_dot(p, ap)
-        xs = xs + alpha * p
-        r = r - alpha * ap
+        alpha = div(rs, lane_dot(p, ap))
+        xs = xs + mul(alpha, p)
+        r = r - mul(alpha, ap)
         rs_new = lane_dot(r, r)
-        if math.sqrt(rs_new) <= reduction * r0:
+        if modulus(root(rs_new)) <= reduction * r0:
             break
-        beta = rs_new / rs
-        p = r + beta * p
+        beta = div(rs_new, rs)
+        p = r + mul(beta, p)
         rs = rs_new
     _scatter_interior(x, xs)
     return its
@@ -369,11 +475,12 @@ def op_coarse_bicgstab(h: Hierarchy, level, max_its=1000, reduction=1e-6):
     ws = [np.zeros_like(a) for a in x]
     xs = np.zeros_like(_flat_interior(x))
     res = _flat_interior(h.rhs[level]) - _apply_flat(h, level, x)
-    cur = np.sqrt(lane_dot(res, res))
-    init = cur
+    cur = root(lane_dot(res, res))
+    init = modulus(cur)
     if cur == 0.0:
         return 0
-    alpha = beta = rho_new = omega = 1.0 + 0j
+    one = 1.0 + 0j if np.iscomplexobj(res) else 1.0
+    alpha = beta = rho_new = omega = one
     res_hat = res.copy()
     nu = np.zeros_like(res)
     p = np.zeros_like(res)
@@ -381,22 +488,22 @@ def op_coarse_bicgstab(h: Hierarchy, level, max_its=1000, reduction=1e-6):
     for its in range(1, max_its + 1):
         rho = rho_new
         rho_new = lane_dot(res_hat, res)
-        beta = (rho_new / rho) * (alpha / omega)
-        p = res + beta * (p - omega * nu)
+        beta = mul(div(rho_new, rho), div(alpha, omega))
+        p = res + mul(beta, p - mul(omega, nu))
         _scatter_interior(wp, p)
         h.apply_bc(level, wp)
         nu = _apply_flat(h, level, wp)
-        alpha = rho_new / lane_dot(res_hat, nu)
-        hh = xs + alpha * p
-        s = res - alpha * nu
+        alpha = div(rho_new, lane_dot(res_hat, nu))
+        hh = xs + mul(alpha, p)
+        s = res - mul(alpha, nu)
         _scatter_interior(ws, s)
         h.apply_bc(level, ws)
         t = _apply_flat(h, level, ws)
-        omega = lane_dot(t, s) / lane_dot(t, t)
-        xs = hh + omega * s
-        res = s - omega * t
-        cur = np.sqrt(lane_dot(res, res))
-        if abs(cur) < reduction * abs(init):
+        omega = div(lane_dot(t, s), lane_dot(t, t))
+        xs = hh + mul(omega, s)
+        res = s - mul(omega, t)
+        cur = root(lane_dot(res, res))
+        if modulus(cur) < reduction * init:
             break
     _scatter_interior(x, xs)
     h.apply_bc(level, x)
@@ -530,7 +637,7 @@ def helmholtz_bicgstab_solve(h: Hierarchy, ops, settings: SolverSettings, operat
         return out
 
     def dot(a, b):
-        return np.sum(_interior(a) * _interior(b))
+        return grid_dot(a, b)
 
     def precondition(v):
         h.sol[L][0][...] = 0
@@ -540,9 +647,9 @@ def helmholtz_bicgstab_solve(h: Hierarchy, ops, settings: SolverSettings, operat
 
     residual = np.zeros(shape, dt)
     _interior(residual)[...] = _interior(rhs) - _interior(A(solution))
-    cur = np.sqrt(dot(residual, residual))
+    cur = root(dot(residual, residual))
     init = cur
-    history = [abs(cur)]
+    history = [modulus(cur)]
     if cur == 0.0:
         return history, infinity, infinity
     alpha = beta = rho_new = omega = 1.0 + 0j
@@ -554,24 +661,24 @@ def helmholtz_bicgstab_solve(h: Hierarchy, ops, settings: SolverSettings, operat
     for step in range(max_its):
         rho = rho_new
         rho_new = dot(res_hat, residual)
-        beta = (rho_new / rho) * (alpha / omega)
-        p = residual + beta * (p - omega * ap)
+        beta = mul(div(rho_new, rho), div(alpha, omega))
+        p = residual + mul(beta, p - mul(omega, ap))
         u = precondition(p)
         ap = A(u)
-        alpha = rho_new / dot(res_hat, ap)
-        hh = solution + alpha * u
-        s = residual - alpha * ap
+        alpha = div(rho_new, dot(res_hat, ap))
+        hh = solution + mul(alpha, u)
+        s = residual - mul(alpha, ap)
         u = precondition(s)
         t = A(u)
-        omega = dot(t, s) / dot(t, t)
-        solution = hh + omega * u
+        omega = div(dot(t, s), dot(t, t))
+        solution = hh + mul(omega, u)
         h.apply_bc(L, [solution])
-        residual = s - omega * t
-        cur = np.sqrt(dot(residual, residual))
-        history.append(abs(cur))
-        if not np.isfinite(abs(cur)):
+        residual = s - mul(omega, t)
+        cur = root(dot(residual, residual))
+        history.append(modulus(cur))
+        if not math.isfinite(history[-1]):
             break
-        if abs(cur) < settings.target_reduction * abs(init):
+        if history[-1] < settings.target_reduction * modulus(init):
             converged_at = step
             break
     # output contract: one "convergence factor" line = |cur|/|init|; iterations = curStep

@@ -480,6 +480,31 @@ int mg_build_cycle(mg_workspace* ws, const mg_op* ops, int n_ops, int* cycle) {
     return MG_OK;
 }
 
+/* OpenMP team size, set explicitly by the caller (torchrun exports OMP_NUM_THREADS=1 to its workers, which
+ * would silently time a one-thread run); the getter reports what a parallel region really gets. */
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+int mg_oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+    return MG_OK;
+}
+int mg_oracle_threads(void) {
+    int used = 1;
+#ifdef _OPENMP
+#pragma omp parallel
+    {
+#pragma omp single
+        used = omp_get_num_threads();
+    }
+#endif
+    return used;
+}
+
 static double now_ms(void) {
     struct timespec t;
     clock_gettime(CLOCK_MONOTONIC, &t);

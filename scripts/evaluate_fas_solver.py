@@ -3,12 +3,11 @@
 cycle with the damped Jacobi-Newton smoother of `FAS_2D_Basic.exa4`, solved until the `.exa4`'s
 stopping rule holds; prints the two lines the generated binary prints (:185-186), which
 `ProgramGeneratorFAS.generate_and_evaluate` parses (exastencils_FAS.py:369-426).  Levels default to
-the `.knowledge` file's (minLevel 6, maxLevel 10).  `--cpu` also times the C/OpenMP oracle port
-(oracle/mg_oracle_c.c) of the same solve on the host cores, as the CPU figure beside the GPU one."""
+the `.knowledge` file's (minLevel 6, maxLevel 10).  (The CPU figure of the same solve is timed by
+`bench.py --config fas`, not here: nothing under scripts/ touches oracle/.)"""
 import argparse
 import os
 import sys
-import time
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 
@@ -25,7 +24,6 @@ def main(argv=None):
                          "evaluated through B200ProgramGeneratorFAS.generate_and_evaluate instead of the V(pre, post) cycle")
     ap.add_argument("--template-smoother", action="store_true",
                     help="with --individual: every smoothing step calls the template's Smoother (fct_smoother given)")
-    ap.add_argument("--cpu", action="store_true", help="time the C/OpenMP oracle port of the same solve too")
     ap.add_argument("--device", type=int, default=0)
     a = ap.parse_args(argv)
     from evostencils_b200 import fas
@@ -56,21 +54,6 @@ def main(argv=None):
     print("total no of iterations", len(history) - 1)
     print("time to solution (in ms) is", best)
     print(f"residual reduction {history[-1] / history[0]:.3e}, max error against solFct {error:.3e}")
-    if a.cpu:
-        # CPU figure: the C/OpenMP oracle port of the same statements (oracle/mg_oracle_c.c; test infrastructure,
-        # like bench.py's cpu_baseline), all host cores
-        import subprocess
-        from evostencils_b200 import engine
-        oracle_dir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle")
-        subprocess.run(["make", "-s", "-B", "-C", oracle_dir, "MARCH=native"], check=True, capture_output=True)
-        cores = len(os.sched_getaffinity(0))
-        os.environ.setdefault("OMP_NUM_THREADS", str(cores))
-        cpu = fas.FasSolver(a.min_level, a.max_level, lib=engine.load_library(os.path.join(oracle_dir, "_build", "libmgoracle.so")))
-        cpu.solve(ops)
-        cpu.reset()
-        want, cpu_ms = cpu.solve(ops)
-        cpu.close()
-        print(f"C/OpenMP port on {cores} host threads: {len(want) - 1} iterations, {cpu_ms:.1f} ms")
     return len(history) - 1, best
 
 

@@ -248,19 +248,15 @@ def test_oracle_stages_are_consistent():
 def test_c_port_of_the_fas_stages_matches_the_numpy_oracle():
     """oracle/mg_oracle_c.c carries the FAS statements too (the timed CPU figure of
     scripts/evaluate_fas_solver.py); same arithmetic as oracle/fas_oracle.py up to libm's exp."""
-    import os
-    import subprocess
-    from evostencils_b200 import engine, problems
+    from evostencils_b200 import problems
     from evostencils_b200.grammar import Grammar
+    from oracle import cport
     from oracle import fas_oracle as fo
-    oracle_dir = os.path.join(os.path.dirname(__file__), "..", "oracle")
-    subprocess.run(["make", "-s", "-C", oracle_dir], check=True)
-    clib = engine.load_library(os.path.join(oracle_dir, "_build", "libmgoracle.so"))
     golden = load_golden()
     for case, lo, hi in (("fas_inline_w_like", 3, 6), ("fas_inline_v_two_coarsenings", 4, 6), ("fas_v22_two_coarsenings", 3, 5)):
         expression, _ = Grammar(problems.FAS_2D_BASIC, lo, hi, FAS=True).compile(golden[case]["grammar"])
         ops = fas.lower(expression, template_smoother=golden[case]["template_smoother"])
-        solver = fas.FasSolver(lo, hi, lib=clib)
+        solver = cport.FasSolver(lo, hi)
         history, ms = solver.solve(ops)
         u_ref, want = fo.solve_ops(ops, hi, lo)
         assert len(history) == len(want), case

@@ -15,8 +15,8 @@ LIB = os.path.join(ORACLE_DIR, "_build", "libmgoracle.so")
 
 @pytest.fixture(scope="module")
 def clib():
-    subprocess.check_call(["make", "-s", "-C", ORACLE_DIR])
-    return engine.load_library(LIB)
+    from oracle import cport
+    return cport.load()
 
 
 def c_solve(clib, problem, program, engine_min_level=None):
