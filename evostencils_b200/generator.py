@@ -175,6 +175,7 @@ class B200ProgramGenerator:
         self.last_error = None
         self.last_sweep = []
         self._default_cycle_cache = {}
+        self._operator_cache = {}
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self._update_grids()
@@ -459,15 +460,19 @@ class B200ProgramGenerator:
                 # at the current parameter values (the reference substitutes the global variable in the
                 # generated program instead, :518-532).
                 override = None
-                if mapping and set(mapping) & set(self._problem.parameters):
+                if self._problem.parameters:
+                    # PDE parameters are globals of the generated program in the reference, not properties
+                    # of the individual: the problem's / generator's / caller's values apply
                     merged = dict(self._problem.parameters)
                     merged.update(mapping)
-                    cache = {}
+                    key = tuple(sorted((name, complex(v)) for name, v in merged.items()))
 
-                    def override(level, _cache=cache, _merged=merged):
-                        if level not in _cache:
-                            _cache[level] = self._problem.system_operator(level, 0, _merged)
-                        return _cache[level]
+                    def override(level, _key=key, _merged=merged):
+                        if (level, _key) not in self._operator_cache:
+                            if len(self._operator_cache) > 256:
+                                self._operator_cache.clear()
+                            self._operator_cache[(level, _key)] = self._problem.system_operator(level, 0, _merged)
+                        return self._operator_cache[(level, _key)]
                 program = lowering.lower(expression, min_level, max_level, override)
             except lowering.LoweringError:
                 return infinity, infinity, infinity

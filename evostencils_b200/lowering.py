@@ -304,6 +304,13 @@ class _Lowerer:
             return ir.Diagonal(operator)
         if hasattr(smoothing_operator, "block_sizes"):
             return ir.BlockDiagonalOperator(operator, smoothing_operator.block_sizes)
+        if hasattr(smoothing_operator, "entries"):
+            # the reference's block-diagonal operator (ir/smoother.py:13-22) does not record its block
+            # shapes: they are the periods of the diagonal entries' stencils
+            dim = _grids(operator)[0].dimension
+            sizes = tuple(st.periodic_shape(_entry_stencil(row[i])) or (1,) * dim
+                          for i, row in enumerate(smoothing_operator.entries))
+            return ir.BlockDiagonalOperator(operator, sizes)
         raise LoweringError("the smoothing operator can not be rebuilt for other PDE parameters")
 
     def note_operator(self, system_operator, level):
@@ -472,12 +479,16 @@ def fuse(ops: Sequence[object]) -> List[object]:
     return out
 
 
-def estimate_cycle_bytes(ops: Sequence[object], dimension: int, bytes_per_value: int = 8) -> float:
+def estimate_cycle_bytes(ops: Sequence[object], dimension: int, bytes_per_value: int = 8, default_cycle=None) -> float:
     """Algorithmic HBM bytes of one cycle of `ops` (every input field read once,
-    every output written once; interior nodes only).  Static information about an individual,
-    used to order a population longest-first before it is dealt to the ranks."""
+    every output written once; interior nodes only; a zero fill that the next smoother of the level
+    absorbs is free).  `default_cycle(level)` -> op list the engine runs for a coarse-grid-solver op
+    above its min level (the `.exa3` cycle below the grammar's coarsest level).  Static information
+    about an individual: orders a population longest-first, and is the numerator of the whole-step
+    roofline fraction bench.py prints."""
     total = 0.0
-    for op in fuse(ops):
+    fused = fuse(ops)
+    for i, op in enumerate(fused):
         fine_level = op.level
         if isinstance(op, LocalSolve):
             fields = 3.0                                       # u, f in, u out
@@ -488,12 +499,14 @@ def estimate_cycle_bytes(ops: Sequence[object], dimension: int, bytes_per_value:
         elif op.kind in ("prolong_add", "prolong"):
             fields = 2.0 + 0.5 ** dimension
         elif op.kind in ("zero",):
-            fields = 1.0
+            nxt = fused[i + 1] if i + 1 < len(fused) else None
+            fields = 0.0 if isinstance(nxt, LocalSolve) and nxt.level == op.level else 1.0
         elif op.kind == "copy":
             fields = 2.0
         elif op.kind == "cgs":
-            if op.inner:
-                total += estimate_cycle_bytes(op.inner, dimension, bytes_per_value)
+            inner = op.inner if op.inner else (default_cycle(op.level) if default_cycle else None)
+            if inner:
+                total += estimate_cycle_bytes(inner, dimension, bytes_per_value, default_cycle)
             continue
         else:
             fields = 3.0

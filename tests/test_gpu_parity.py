@@ -1,9 +1,10 @@
 """GPU parity tests: every CUDA stage and whole solves against the numpy oracle, through the C ABI.
 
-Bar (DESIGN.md "Numerical contract"): real fp64 fields bit-identical to the oracle for point
-smoothers, residual, restriction, prolongation and the coarse CG; <= 1e-12 relative for tile
-smoothers (LAPACK vs closed-form inverse is shared, summation identical -> in practice exact) and
-complex arithmetic; residual norms <= 1e-10 relative (north_star), iteration counts identical."""
+Bar (DESIGN.md "Numerical contract"): fields bit-identical to the oracle for point smoothers,
+residual, restriction, prolongation and the coarse Krylov solves -- real and complex (the oracle
+states complex products / quotients / roots in the engine's operand order); <= 1e-12 relative for
+tile smoothers (LAPACK vs closed-form inverse is shared, summation identical -> in practice exact);
+residual norms <= 1e-10 relative (north_star), iteration counts identical."""
 import numpy as np
 import pytest
 
@@ -90,7 +91,7 @@ def smoother_statements(problem, level, kind, partitioning, omega=0.8, block=Non
 @pytest.mark.parametrize("name", sorted(CASES))
 def test_residual_restrict_prolong(name):
     problem, lo, hi = CASES[name]
-    exact = problem.dtype == "f64"
+    exact = True
     ws, h = make_pair(problem, lo, hi, seed=1)
     run_both(ws, h, [lowering.Op("residual", hi, dst="res")], problem)
     compare(ws, h, "res", hi, exact, "residual")
@@ -116,7 +117,7 @@ def test_point_smoothers(name, partitioning, kind):
     problem, lo, hi = CASES[name]
     if kind == "decoupled" and problem.n_fields == 1:
         pytest.skip("decoupled == collective for one field")
-    exact = problem.dtype == "f64"
+    exact = True
     part = ir.Single if partitioning == "single" else ir.RedBlack
     ws, h = make_pair(problem, lo, hi, seed=2)
     for level in (hi, lo + 1):
@@ -147,7 +148,7 @@ def test_tile_smoothers(name, block):
 @pytest.mark.parametrize("name", sorted(CASES))
 def test_coarse_solver_and_norm(name):
     problem, lo, hi = CASES[name]
-    exact = problem.dtype == "f64"
+    exact = True
     from oracle import mg_oracle
     ws, h = make_pair(problem, lo, hi, seed=4)
     for level in (hi, lo):
@@ -378,11 +379,14 @@ def test_fast_tile_smoother_bit_identical_to_generic(block):
         assert np.array_equal(results[(True, level)], results[(False, level)]), (block, level)
 
 
-@pytest.mark.parametrize("k,rtol", [(5.0, 1e-9), (10.0, 1e-5)])
-def test_helmholtz_preconditioned_bicgstab(k, rtol):
+@pytest.mark.parametrize("k", [5.0, 10.0, 80.0])
+def test_helmholtz_preconditioned_bicgstab(k):
     """Outer BiCGStab with the cycle as preconditioner (Helmholtz/...exa3:144-200) on the GPU against
-    the oracle.  BiCGStab amplifies rounding differences (complex division, dot grouping), so the
-    per-iteration comparison uses well-conditioned wave numbers; iteration counts identical."""
+    the oracle: identical iteration count, per-iteration norms <= 1e-10 (`north_star`), the solution
+    bit-identical.  BiCGStab amplifies rounding differences, so this only holds because oracle and
+    engine share every operand order (complex product / quotient / root formulas, dot trees); k = 80
+    is the reference's wave number (hundreds of iterations).  Levels 3..7 of the configuration:
+    tests/test_gpu_config_sizes.py."""
     from evostencils_b200.generator import B200ProgramGenerator
     from oracle import driver
     problem, lo, hi = problems.HELMHOLTZ_2D, 3, 6
@@ -394,40 +398,11 @@ def test_helmholtz_preconditioned_bicgstab(k, rtol):
     t, rho, n = gen.evaluate_program(program, {"k": k}, evaluation_samples=2)
     h, hist, rho_ref, n_ref = driver.solve(problem, program, params={"k": k})
     got, want = np.array(gen.last_residual_history), np.array(hist)
-    assert n == n_ref
+    assert n == n_ref and n < 1e99
     assert got.shape == want.shape
-    # Two Krylov iterations are nested here (outer BiCGStab; coarse BiCGStab to 1e-6 inside every
-    # cycle): last-bit differences of the complex division / dot grouping against numpy move the
-    # inner stopping step, which shows up at ~1e-6 of the coarse correction; the recursively updated
-    # outer residual then carries that noise relative to |r0|.  Hence agreement relative to |r0|
-    # (1e-9 for k = 5, where the coarse solve is insensitive; 1e-5 for k = 10), identical iteration
-    # counts, and the first iteration relative to its own size.
-    assert np.all(np.abs(got - want) <= rtol * want[0]), np.max(np.abs(got - want)) / want[0]
-    assert abs(got[1] - want[1]) <= 1e-9 * want[1]
-    assert abs(rho - rho_ref) <= 0.5 * rho_ref
-    u = gen._workspace.download("sol", hi, 0)
-    # the oracle keeps Solution in a local array; compare through the residual of the unshifted operator instead
-    assert np.all(np.isfinite(u.view(np.float64)))
-    gen.close()
-
-
-def test_helmholtz_reference_wave_number_converges():
-    """k = 80 (kh = 0.625 on 128^2, the reference configuration): hundreds of chaotic BiCGStab
-    iterations -- no per-iteration parity, but the same convergence behaviour as the oracle."""
-    from evostencils_b200.generator import B200ProgramGenerator
-    from oracle import driver
-    problem, lo, hi = problems.HELMHOLTZ_2D, 3, 6
-    grammar = Grammar(problem, lo, hi)
-    expression, _ = grammar.compile(v_cycle_string(hi - lo, 2, 1, 10, "red_black"))
-    program = lowering.lower(expression, lo, hi)
-    gen = B200ProgramGenerator(problem=problem, min_level=lo, max_level=hi, device=0)
-    t, rho, n = gen.evaluate_program(program, {}, evaluation_samples=1)
-    _, hist, rho_ref, n_ref = driver.solve(problem, program)
-    got = np.array(gen.last_residual_history)
-    assert n < 1e99 and n_ref < 1e99
-    assert abs(n - n_ref) <= 0.25 * n_ref, (n, n_ref)
+    assert np.all(np.abs(got - want) <= 1e-10 * want), np.max(np.abs(got - want) / want)
+    assert abs(rho - rho_ref) <= 1e-10 * rho_ref
     assert got[-1] < 1e-7 * got[0]
-    assert np.allclose(got[:5], np.array(hist)[:5], rtol=1e-9)
     gen.close()
 
 

@@ -192,3 +192,113 @@ def test_batched_map_fitness_conventions():
     t, rho, n = fake_evaluate("ind_1")
     assert out[0] == ((rho, t / n) if n < 1e100 else (rho, 1e100))
     assert out[1] == (1e100, 1e100)
+
+
+def test_batched_map_objectives_and_size_guard():
+    """optimization/program.py:386-453: single objective = (t,) or (sqrt(rho) sqrt(n),) when the solver did
+    not converge; trees of more than 150 nodes get the infinity tuple without an evaluation."""
+    import functools
+    calls = []
+
+    class Gen:
+        def generate_and_evaluate(self, expression, storages, lo, hi, solver, infinity=1e100, evaluation_samples=1):
+            calls.append(expression)
+            return {"good": (12.0, 0.25, 6.0), "diverged": (3.0, 4.0, 1e100)}[expression]
+
+    class Gram:
+        def compile(self, s):
+            return s, None
+
+    class Optimizer:
+        def evaluate_single_objective(self, individual, **kw):
+            raise AssertionError("the mapped function is not called: the map evaluates the batch itself")
+
+        def evaluate_multiple_objectives(self, individual, **kw):
+            raise AssertionError
+
+    big = "f(" * 151 + "x" + ")" * 151
+    assert population.node_count(big) == 152 and population.node_count("f(1, (2, 1), g(x))") == 5
+    m = population.batched_map(Gen(), Gram(), 2, 4)
+    opt = Optimizer()
+    single = m(functools.partial(opt.evaluate_single_objective, pset=None), ["good", "diverged", big])
+    assert single == [(12.0,), (4.0 ** 0.5 * 1e100 ** 0.5,), (1e100,)]
+    multi = m(opt.evaluate_multiple_objectives, ["good", "diverged", big])
+    assert multi == [(0.25, 2.0), (4.0, 1e100), (1e100, 1e100)]
+    assert big not in calls
+    assert population.batched_map(Gen(), Gram(), 2, 4, objectives="single")(None, ["good"]) == [(12.0,)]
+
+    class Tree(list):                     # a deap PrimitiveTree: len() = node count, str() = grammar string
+        def __str__(self):
+            return "good"
+    assert m(None, [Tree(range(151)), Tree(range(150))]) == [(1e100, 1e100), (0.25, 2.0)]
+
+
+def test_solo_gate_excludes_shared_holders():
+    import threading
+    import time
+    gate = population.SoloGate()
+    active, overlaps, log = [0], [0], []
+    lock = threading.Lock()
+
+    def reader():
+        for _ in range(20):
+            with gate.shared():
+                with lock:
+                    active[0] += 1
+                time.sleep(0.001)
+                with lock:
+                    active[0] -= 1
+
+    def writer():
+        for _ in range(10):
+            with gate.exclusive():
+                with lock:
+                    if active[0]:
+                        overlaps[0] += 1
+                    log.append("w")
+                time.sleep(0.001)
+
+    threads = [threading.Thread(target=reader) for _ in range(3)] + [threading.Thread(target=writer) for _ in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=30)
+    assert overlaps[0] == 0 and len(log) == 20
+
+
+def _failing_worker(rank, world, port, queue):
+    sys.path.insert(0, REPO)
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+
+    def evaluate(s):
+        if rank == 1 and s == "ind_3":
+            raise RuntimeError("engine broke on rank 1")
+        return fake_evaluate(s)
+
+    try:
+        population.evaluate_population(evaluate, STRINGS)
+        queue.put((rank, "returned"))
+    except RuntimeError as exc:
+        queue.put((rank, str(exc)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_a_failing_rank_does_not_leave_the_others_in_the_collective():
+    """A rank whose evaluation raises still joins the result exchange; every rank raises afterwards."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    queue = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_failing_worker, args=(r, 2, port, queue)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(queue.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got[1] == "engine broke on rank 1"
+    assert "failed on 1 other rank" in got[0]
