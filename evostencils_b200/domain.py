@@ -130,6 +130,10 @@ class SlabComm:
         self.bytes_sent += padded.numel() * padded.element_size()
         return {r: torch.cat([out[q][: counts[q]] for q in range(self.world)], dim=0)}
 
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier(group=self.group)
+
     def sum_in_rank_order(self, values: Dict[int, float]) -> float:
         """Deterministic: every rank adds the world's values in rank order."""
         import torch
@@ -381,6 +385,27 @@ class DomainDecomposedSolver:
             partial[loc.rank] = v * v
         return math.sqrt(self.comm.sum_in_rank_order(partial))
 
+    def time_cycles(self, ops: Sequence[object], cycles: int, warmup: int = 1):
+        """`cycles` cycles back to back between device-synchronised barriers -> (ms per cycle on this
+        rank, record for the bench line).  The caller takes the max over ranks."""
+        import time
+        for _ in range(warmup):
+            self.run_ops(ops)
+        self.comm.bytes_sent = 0
+        self.halo_exchanges = 0
+        self.comm.barrier()
+        self._sync()
+        t0 = time.perf_counter()
+        for _ in range(cycles):
+            self.run_ops(ops)
+        self._sync()
+        self.comm.barrier()
+        ms = (time.perf_counter() - t0) * 1e3 / cycles
+        return ms, {"driver": "op-by-op host driver, NCCL send/recv halo exchange (no graph)",
+                    "halo_bytes_per_cycle_rank0": self.comm.bytes_sent / cycles,
+                    "halo_exchanges_per_cycle": self.halo_exchanges / cycles,
+                    "dd_min_level": self.dd_min_level, "splits": self.splits}
+
     def solve(self, ops: Sequence[object], tol: float, max_its: int):
         """Outer iteration of the generated solver (same conventions as mg_solve)
         -> (history, converged, milliseconds)."""
@@ -400,3 +425,9 @@ class DomainDecomposedSolver:
                 break
         self._sync()
         return history, converged, (time.perf_counter() - t0) * 1e3
+
+
+def make_solver(problem, min_level: int, max_level: int, comm: SlabComm, device: int = 0, dd_min_level=None):
+    """The decomposed solver for this process' rank(s) on `device`."""
+    return DomainDecomposedSolver(problem, min_level, max_level, comm, dd_min_level=dd_min_level,
+                                  device_of=lambda r: device)
