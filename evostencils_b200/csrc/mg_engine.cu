@@ -334,3 +334,4 @@ extern "C" int mg_clear_smoothers(mg_workspace* ws) {
 
 #include "mg_engine_run.inc"
 #include "mg_engine_fas.inc"
+#include "mg_engine_noalloc.inc"

@@ -36,6 +36,7 @@ EXPORTED_SYMBOLS = [
     "mg_solve_bicgstab", "mg_synchronize",
     "mg_time_ops", "mg_profile_ops", "mg_mark", "mg_elapsed", "mg_flush_l2", "mg_set_fast_kernels",
     "mg_fas_smooth", "mg_fas_residual", "mg_fas_restrict", "mg_fas_subtract_approximation", "mg_fas_residual_norm",
+    "mg_residual_norm_noalloc",
 ]
 
 
@@ -106,6 +107,7 @@ def _signatures():
         "mg_fas_restrict": [vp, i32, dbl],
         "mg_fas_subtract_approximation": [vp, i32],
         "mg_fas_residual_norm": [vp, i32, dbl, pdbl],
+        "mg_residual_norm_noalloc": [i32, i32, i32, i32, pi32, pdbl, vp, vp, vp, vp],
     }
 
 
@@ -135,6 +137,19 @@ def load_library():
                           "(the engine has no CPU fallback)", fatal=True)
     _lib = bind(C.CDLL(LIB_PATH))
     return _lib
+
+
+def residual_norm_noalloc(dimension, n, pitch, entries, u_device, rhs_device, out_device, cuda_stream=0):
+    """mg_residual_norm_noalloc (include/mgengine.h): the residual norm of one scalar fp64 field, enqueued
+    without any allocation; `entries` = [(offset, value), ...], the pointers are device addresses."""
+    lib = load_library()
+    k = len(entries)
+    offs = (C.c_int32 * max(1, k * dimension))(*[int(c) for off, _ in entries for c in off])
+    vals = (C.c_double * max(1, k))(*[float(v) for _, v in entries])
+    rc = lib.mg_residual_norm_noalloc(dimension, n, pitch, k, offs, vals, C.c_void_p(u_device), C.c_void_p(rhs_device),
+                                      C.c_void_p(out_device), C.c_void_p(cuda_stream or None))
+    if rc != 0:
+        raise EngineError(f"mgengine error {rc}: {lib.mg_last_error().decode()}", code=rc)
 
 
 # ----------------------------------------------------------------------------------------

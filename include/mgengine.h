@@ -200,6 +200,26 @@ int mg_fas_subtract_approximation(mg_workspace* ws, int level);
 /* sqrt(sum over interior nodes of (RHS - (L u + gamma e^u u))^2) (.exa4:83-89); synchronises */
 int mg_fas_residual_norm(mg_workspace* ws, int level, double gamma, double* out);
 
+/* ---- allocation-free residual norm ------------------------------------------------------------ */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * out_device[0] = sqrt(sum over interior nodes of (rhs - A u)^2) of one scalar fp64 field on an n^dimension
+ * node grid -- what mg_residual_norm computes for a workspace level -- without a workspace and without any
+ * allocation: u_device / rhs_device are the caller's device arrays (rows of `pitch` elements, n rows per
+ * plane, n planes in 3D; e.g. from mg_field_pointer), out_device a device double of the caller, the stencil
+ * as for mg_set_operator (offsets[n_entries][dimension], values[n_entries], accumulated in that order).
+ * The per-row partial sums live in a static device array of MG_NOALLOC_MAX_ROWS = 266240 doubles (2.03 MiB
+ * per GPU that loads the library, until exit): grids with more interior rows (3D: n > 517) are rejected with
+ * MG_ERR_INVALID.  Enqueued on `cuda_stream` (NULL: the default stream) of the CURRENT device, no
+ * synchronisation.  Every call shares the array: calls that overlap on the GPU (two streams, two threads)
+ * race; nothing in it needs clearing between calls.  The first call on a device looks the array's address
+ * up (cudaGetSymbolAddress): make it outside a stream capture.  Row sums are formed in a fixed order, so
+ * the result is deterministic; it agrees with mg_residual_norm to rounding (<= 1e-12 relative). */
+#define MG_NOALLOC_MAX_ROWS 266240
+int mg_residual_norm_noalloc(int dimension, int n, int pitch, int n_entries, const int32_t* offsets,
+                             const double* values, const void* u_device, const void* rhs_device,
+                             double* out_device, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
