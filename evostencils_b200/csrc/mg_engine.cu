@@ -109,7 +109,10 @@ static int create_impl(mg_workspace** out, int dimension, int min_level, int max
         const int arrays_per_field = 4 + (finest ? 2 : 0);
         // one guard row before and after every array so that halo reads of the specialised
         // kernels stay inside the slab
-        const long long guard = 2 * g.pitch;
+        // z-slabs: one whole plane more on either side -- the second ghost plane of the one-pass 3D kernels
+        // (local planes -1 and nz; filled by the halo exchange, mg_dd.cuh)
+        lv.wide_ghost = z_begin != nullptr;
+        const long long guard = 2 * g.pitch + (lv.wide_ghost ? g.plane : 0);
         const long long stride = g.total + 2 * guard;
         size_t bytes = (size_t)stride * arrays_per_field * n_fields * ws->elem;
         e = cudaMalloc(&lv.slab, bytes);
@@ -117,6 +120,7 @@ static int create_impl(mg_workspace** out, int dimension, int min_level, int max
             mg_destroy(ws);
             return fail(MG_ERR_NOMEM, "cudaMalloc of level " + std::to_string(level) + " failed: " + cudaGetErrorString(e));
         }
+        lv.slab_bytes = bytes;
         MG_CUDA(cudaMemsetAsync(lv.slab, 0, bytes, ws->stream));
         char* base = static_cast<char*>(lv.slab);
         long long k = 0;

@@ -250,9 +250,11 @@ template <typename T>
 int launch_zero(mg_workspace* ws, Level& lv) {
     for (int f = 0; f < ws->n_fields; ++f) {
         // a kernel, not a memset node: keeps the programmatic-dependent-launch chain of the cycle intact
-        const long long n16 = (long long)lv.g.total * sizeof(T) / 16;        // pitch is a multiple of 16 elements
+        // z-slabs: the second ghost planes (before plane 0, after plane nz-1) are part of the field
+        const long long extra = lv.wide_ghost ? lv.g.plane : 0;
+        const long long n16 = (long long)(lv.g.total + 2 * extra) * sizeof(T) / 16;        // pitch is a multiple of 16 elements
         const int blocks = (int)((n16 + 255) / 256 < 1184 ? (n16 + 255) / 256 : 1184);
-        launch_k(ws, k_zero, blocks, 256, 0, static_cast<double2*>(lv.sol[0][f]), n16);
+        launch_k(ws, k_zero, blocks, 256, 0, reinterpret_cast<double2*>(static_cast<T*>(lv.sol[0][f]) - extra), n16);
         count(ws);
     }
     return MG_OK;

@@ -19,6 +19,9 @@ namespace mg {
 constexpr int FAST_NT = 128;            // threads per CTA of the marching kernels
 constexpr int MAX_PARTIALS = 16384;     // capacity of Level::partial
 
+inline int imax_h(int a, int b) { return a > b ? a : b; }
+inline int imin_h(int a, int b) { return a < b ? a : b; }
+
 inline int tunable(const char* name, int dflt) {
     const char* v = std::getenv(name);
     return v ? std::atoi(v) : dflt;
@@ -166,18 +169,21 @@ inline EncodeTiledFn encode_tiled_fn() {
     return fn;
 }
 
-// descriptors are cached by (array, nodes per dimension, box rows): the sweeps of a solve reuse three of them
-inline const CUtensorMap* plane_tensor_map(const double* base, const Geom& g, int rows) {
+// descriptors are cached by (array, nodes per dimension, planes, box rows): the sweeps of a solve reuse three of them.
+// `base` / `planes`: first plane and plane count of the view (a z-slab view starts one plane before the array:
+// the second ghost plane, mg_engine.cu create_impl).
+inline const CUtensorMap* plane_tensor_map(const double* base, const Geom& g, int rows, int planes = -1) {
     static std::mutex lock;
-    static std::map<std::tuple<const void*, int, int>, CUtensorMap> cache;
+    static std::map<std::tuple<const void*, int, int, int>, CUtensorMap> cache;
     std::lock_guard<std::mutex> guard(lock);
-    const auto key = std::make_tuple(static_cast<const void*>(base), g.n, rows);
+    if (planes < 0) planes = g.nz;
+    const auto key = std::make_tuple(static_cast<const void*>(base), g.n, planes, rows);
     auto it = cache.find(key);
     if (it != cache.end()) return &it->second;
     EncodeTiledFn encode = encode_tiled_fn();
     if (!encode) return nullptr;
     CUtensorMap tm;
-    const cuuint64_t dims[3] = {(cuuint64_t)g.n, (cuuint64_t)g.n, (cuuint64_t)g.nz};
+    const cuuint64_t dims[3] = {(cuuint64_t)g.n, (cuuint64_t)g.n, (cuuint64_t)planes};
     const cuuint64_t strides[2] = {(cuuint64_t)g.pitch * sizeof(double), (cuuint64_t)g.plane * sizeof(double)};
     const cuuint32_t box[3] = {(cuuint32_t)RB3_W, (cuuint32_t)rows, 1u};
     const cuuint32_t elem[3] = {1u, 1u, 1u};
@@ -188,7 +194,33 @@ inline const CUtensorMap* plane_tensor_map(const double* base, const Geom& g, in
     return &cache.emplace(key, tm).first->second;
 }
 
-// one-pass 3D RB-GS sweep (mg_rbgs3d.cuh): whole grids
+// How the TMA-staged kernels see a 3D level: whole grids as they are; a z-slab with two ghost planes
+// (Level::wide_ghost) from one plane before the array, plane 0 of the view = global plane zoff.  zlo .. zhi =
+// global planes an out-of-place sweep must write: the owned ones, plus the global Dirichlet plane that the
+// first / last slab holds as its local plane 0 / nz-1.
+struct SlabView {
+    long long shift;        // elements between the view's first plane and the array's
+    int planes, zoff, zlo, zhi;
+};
+inline SlabView slab_view(const Level& lv) {
+    SlabView v;
+    const Geom& g = lv.g;
+    if (!lv.wide_ghost) {
+        v.shift = 0; v.planes = g.nz; v.zoff = g.z0; v.zlo = g.z0; v.zhi = g.z0 + g.nz - 1;
+        return v;
+    }
+    v.shift = g.plane; v.planes = g.nz + 2; v.zoff = g.z0 - 1;
+    v.zlo = g.z0 == 0 ? 0 : g.z0 + 1;
+    v.zhi = g.z0 + g.nz - 1 == g.n - 1 ? g.n - 1 : g.z0 + g.nz - 2;
+    return v;
+}
+// the one-pass kernels apply to whole grids and to slabs with two ghost planes that own at least two planes
+inline bool one_pass_geometry_ok(const Level& lv) {
+    if (lv.g.z0 == 0 && lv.g.nz == lv.g.n) return true;
+    return lv.wide_ghost && lv.g.nz - 2 >= 2;
+}
+
+// one-pass 3D RB-GS sweep (mg_rbgs3d.cuh): whole grids and z-slabs with two ghost planes
 template <int RY, int NS, int NF>
 inline bool launch_rbgs3d_cfg(mg_workspace* ws, Level& lv, const double* u, const double* f, double* out, double w) {
     static const int zc_env = tunable("MG_RBGS3D_ZCHUNK", 0), pf_env = tunable("MG_RBGS3D_PF", 0);
@@ -201,22 +233,32 @@ inline bool launch_rbgs3d_cfg(mg_workspace* ws, Level& lv, const double* u, cons
             return false;
         opted_in[dev] = true;
     }
-    const CUtensorMap* tm_u = plane_tensor_map(u, lv.g, RY + 4);
-    const CUtensorMap* tm_f = plane_tensor_map(f, lv.g, RY + 2);
+    // z-slab with two ghost planes (Level::wide_ghost): the view starts one plane before the array
+    const SlabView v = slab_view(lv);
+    const CUtensorMap* tm_u = plane_tensor_map(u - v.shift, lv.g, RY + 4, v.planes);
+    const CUtensorMap* tm_f = plane_tensor_map(f - v.shift, lv.g, RY + 2, v.planes);
     if (!tm_u || !tm_f) return false;
-    const int n = lv.g.n;
+    const int n = lv.g.n, nzo = v.zhi - v.zlo + 1;
     const int gx = (n + RB3_TW - 1) / RB3_TW, gy = (n + RY - 1) / RY;
     int zchunk = zc_env >= 3 ? zc_env : 64;
-    while (zc_env < 3 && zchunk > 4 && gx * gy * ((n + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
-    launch_k(ws, k_rbgs3d<RY, NS, NF>, dim3(gx, gy, (n + zchunk - 1) / zchunk), 32 * (RY + 2),
-             rbgs3d_smem_bytes<RY, NS, NF>(), lv.g, star3d(lv), *tm_u, *tm_f, out, w, zchunk, pf_env);
+    while (zc_env < 3 && zchunk > 4 && gx * gy * ((nzo + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
+    launch_k(ws, k_rbgs3d<RY, NS, NF>, dim3(gx, gy, (nzo + zchunk - 1) / zchunk), 32 * (RY + 2),
+             rbgs3d_smem_bytes<RY, NS, NF>(), lv.g, star3d(lv), *tm_u, *tm_f, out - v.shift, w, zchunk, pf_env,
+             v.zoff, v.zlo, v.zhi);
     return true;
 }
 
-inline bool launch_rbgs3d(mg_workspace* ws, Level& lv, const double* u, const double* f, double* out, double w) {
-    static const int enabled = tunable("MG_RBGS3D", 1), cfg = tunable("MG_RBGS3D_CFG", 0);
+// would a red-black sweep of this level run as the one-pass kernel?  (the domain-decomposition driver
+// exchanges two ghost planes once per sweep then, instead of one plane per colour pass)
+inline bool rbgs3d_applicable(const mg_workspace* ws, const Level& lv) {
+    static const int enabled = tunable("MG_RBGS3D", 1);
     const int min_n = tunable("MG_RBGS3D_MIN_N", 257);      // not cached: the tests lower it to 65
-    if (!enabled || lv.g.z0 != 0 || lv.g.nz != lv.g.n || lv.g.n < 65 || lv.g.n < min_n) return false;
+    return enabled && ws->use_fast && star3d_nt(ws, lv) && one_pass_geometry_ok(lv) && lv.g.n >= 65 && lv.g.n >= min_n;
+}
+
+inline bool launch_rbgs3d(mg_workspace* ws, Level& lv, const double* u, const double* f, double* out, double w) {
+    static const int cfg = tunable("MG_RBGS3D_CFG", 0);
+    if (!rbgs3d_applicable(ws, lv)) return false;
     switch (cfg) {
         // rows per tile, ring sizes of u / f (measured at 513^3, profiles/README.md): the default keeps
         // 3 CTAs per SM (74 KB each) with 3 planes in flight
@@ -342,26 +384,35 @@ inline bool launch_resrestrict3d_cfg(mg_workspace* ws, Level& lf, Level& lc, con
             return false;
         opted_in[dev] = true;
     }
-    const CUtensorMap* tm_u = plane_tensor_map(u, lf.g, 2 * RYC + 3);
-    const CUtensorMap* tm_f = plane_tensor_map(f, lf.g, 2 * RYC + 1);
+    const SlabView v = slab_view(lf);
+    const CUtensorMap* tm_u = plane_tensor_map(u - v.shift, lf.g, 2 * RYC + 3, v.planes);
+    const CUtensorMap* tm_f = plane_tensor_map(f - v.shift, lf.g, 2 * RYC + 1, v.planes);
     if (!tm_u || !tm_f) return false;
     const int m = lc.g.n - 2;                                              // interior coarse nodes per dimension
+    // owned coarse planes (global indices); `out` is addressed from the coarse array's local plane 0
+    const int Zlo = imax_h(1, lc.g.z0 + 1), Zhi = imin_h(lc.g.n - 2, lc.g.z0 + lc.g.nz - 2), mz = Zhi - Zlo + 1;
+    if (mz < 1) return true;                                               // nothing owned on the coarse level
     const int gx = (m + RS3_TXC - 1) / RS3_TXC, gy = (m + RYC - 1) / RYC;
     int zchunk = zc_env >= 2 ? zc_env : 32;
-    while (zc_env < 2 && zchunk > 2 && gx * gy * ((m + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
-    launch_k(ws, k_resrestrict3d<RYC, NS, NF>, dim3(gx, gy, (m + zchunk - 1) / zchunk), 32 * (2 * RYC + 1),
-             resrestrict3d_smem_bytes<RYC, NS, NF>(), lc.g, lf.g, star3d(lf), *tm_u, *tm_f, out, zchunk);
+    while (zc_env < 2 && zchunk > 2 && gx * gy * ((mz + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
+    launch_k(ws, k_resrestrict3d<RYC, NS, NF>, dim3(gx, gy, (mz + zchunk - 1) / zchunk), 32 * (2 * RYC + 1),
+             resrestrict3d_smem_bytes<RYC, NS, NF>(), lc.g, lf.g, star3d(lf), *tm_u, *tm_f, out, zchunk,
+             v.zoff, lc.g.z0, Zlo, Zhi);
     return true;
+}
+
+// would residual + restriction from this fine level run as the fused TMA kernel?
+inline bool resrestrict3d_applicable(const mg_workspace* ws, const Level& lf) {
+    static const int enabled = tunable("MG_RESTRICT3D", 1);
+    const int min_n = tunable("MG_RESTRICT3D_MIN_N", 129);     // not cached: the tests lower it to 65
+    return enabled && ws->use_fast && star3d_nt(ws, lf) && one_pass_geometry_ok(lf) && lf.g.n >= 65 && lf.g.n >= min_n;
 }
 
 template <typename T, int D, int F>
 inline bool fast_residual_restrict(mg_workspace* ws, Level& lf, Level& lc) {
     if constexpr (D == 3 && F == 1 && sizeof(T) == sizeof(double)) {
-        static const int enabled = tunable("MG_RESTRICT3D", 1), cfg = tunable("MG_RESTRICT3D_CFG", 0);
-        const int min_n = tunable("MG_RESTRICT3D_MIN_N", 129);     // not cached: the tests lower it to 65
-        if (!enabled || !star3d_nt(ws, lf) || lf.g.z0 != 0 || lf.g.nz != lf.g.n || lc.g.z0 != 0 || lc.g.nz != lc.g.n ||
-            lf.g.n < 65 || lf.g.n < min_n)
-            return false;
+        static const int cfg = tunable("MG_RESTRICT3D_CFG", 0);
+        if (!resrestrict3d_applicable(ws, lf)) return false;
         const double* u = static_cast<const double*>(lf.sol[lf.cur[0]][0]);
         const double* f = static_cast<const double*>(lf.rhs[0]);
         double* out = static_cast<double*>(lc.rhs[0]);

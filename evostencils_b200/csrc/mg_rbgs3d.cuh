@@ -88,10 +88,15 @@ __device__ __forceinline__ double rb3_get(const double2 v) { return C ? v.y : v.
 //   fp, fq        the right-hand side of the row in planes s and s-1.
 // Per step a thread reads two 16-byte pairs (rn, fp) and four 8-byte values (the y neighbours of the red
 // and of the black node, which other warps own) from shared memory.
+// z-slabs (domain decomposition): the tensor maps and `out` describe the slab array including its ghost planes,
+// plane 0 of them being the global plane `zoff`; the sweep writes the global planes zlo .. zhi (the owned ones,
+// plus the global Dirichlet plane on the first / last slab) and reads two planes beyond them -- the slab
+// carries two ghost planes on either side for this kernel.  Whole grids: zoff = 0, zlo = 0, zhi = n-1.
 template <int RY, int RB3_NS, int RB3_NF>
 __global__ void __launch_bounds__(32 * (RY + 2)) k_rbgs3d(Geom g, Star3D st, const __grid_constant__ CUtensorMap tm_u,
                                                           const __grid_constant__ CUtensorMap tm_f,
-                                                          double* __restrict__ out, double w, int zchunk, int pf) {
+                                                          double* __restrict__ out, double w, int zchunk, int pf,
+                                                          int zoff, int zlo, int zhi) {
     constexpr int UR = RY + 4, FR = RY + 2, NW = RY + 2;
     static_assert(RY % 2 == 0, "tile rows start on even y");
     constexpr uint32_t U_BYTES = UR * RB3_W * 8, F_BYTES = FR * RB3_W * 8;
@@ -105,8 +110,8 @@ __global__ void __launch_bounds__(32 * (RY + 2)) k_rbgs3d(Geom g, Star3D st, con
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n = g.n;
     const long long pitch = g.pitch, plane = g.plane;
-    const int xb = blockIdx.x * RB3_TW, yb = blockIdx.y * RY, zb = blockIdx.z * zchunk;
-    const int ze = imin(zb + zchunk, n);                                    // output planes zb .. ze-1
+    const int xb = blockIdx.x * RB3_TW, yb = blockIdx.y * RY, zb = zlo + blockIdx.z * zchunk;
+    const int ze = imin(zb + zchunk, zhi + 1);                              // output planes zb .. ze-1 (global indices)
     const int p0 = zb - 2, fp0 = zb - 1;                                    // first staged plane of u / f
     const uint32_t su_a = smem_u32(su), sf_a = smem_u32(sf), bar_a = smem_u32(bars);
 
@@ -117,14 +122,14 @@ __global__ void __launch_bounds__(32 * (RY + 2)) k_rbgs3d(Geom g, Star3D st, con
         if (lane == 0) {
             const uint32_t bar = bar_a + 8 * slot;
             mbar_arrive_expect_tx(bar, U_BYTES);
-            tma_load_3d(su_a + (uint32_t)(slot * U_SLOT * 8), &tm_u, xb - 2, yb - 2, p, bar);
+            tma_load_3d(su_a + (uint32_t)(slot * U_SLOT * 8), &tm_u, xb - 2, yb - 2, p - zoff, bar);
         }
     };
     auto stage_f = [&](int p, int slot) {
         if (lane == 0) {
             const uint32_t bar = bar_a + 8 * (RB3_NS + slot);
             mbar_arrive_expect_tx(bar, F_BYTES);
-            tma_load_3d(sf_a + (uint32_t)(slot * F_SLOT * 8), &tm_f, xb - 2, yb - 1, p, bar);
+            tma_load_3d(sf_a + (uint32_t)(slot * F_SLOT * 8), &tm_f, xb - 2, yb - 1, p - zoff, bar);
         }
     };
     auto back = [](int slot, int k, int ring) { const int v = slot - k; return v < 0 ? v + ring : v; };
@@ -165,7 +170,7 @@ __global__ void __launch_bounds__(32 * (RY + 2)) k_rbgs3d(Geom g, Star3D st, con
     const bool black_warp = warp >= 1 && warp <= RY;
     const int par_row = y & 1;                                               // + s: component of the red node (plane s)
                                                                              //      = of the black node (plane s-1)
-    double* optr = out + (long long)(zb - 2) * plane + (long long)y * pitch + x0;   // plane s-1 at s = zb-1
+    double* optr = out + (long long)(zb - 2 - zoff) * plane + (long long)y * pitch + x0;   // plane s-1 at s = zb-1
 
     double2 rzm = *reinterpret_cast<const double2*>(su + o_row);            // plane zb-2 (slot 0)
     double2 rc = *reinterpret_cast<const double2*>(su + U_SLOT + o_row);    // plane zb-1 (slot 1)
@@ -213,8 +218,8 @@ __global__ void __launch_bounds__(32 * (RY + 2)) k_rbgs3d(Geom g, Star3D st, con
             if (s - 3 >= p0 && s - 3 + RB3_NS <= ze + 1) stage_u(s - 3 + RB3_NS, back(e_m2 / U_SLOT, 1, RB3_NS));
             if (s - 2 >= fp0 && s - 2 + RB3_NF <= ze) stage_f(s - 2 + RB3_NF, back(e_f1 / F_SLOT, 1, RB3_NF));
             if (pf > 0 && lane == 0 && s + pf <= imin(ze + 1, n - 1)) {     // the boxes of plane s+pf -> L2
-                tma_prefetch_3d(&tm_u, xb - 2, yb - 2, s + pf);
-                if (s + pf <= ze) tma_prefetch_3d(&tm_f, xb - 2, yb - 1, s + pf);
+                tma_prefetch_3d(&tm_u, xb - 2, yb - 2, s + pf - zoff);
+                if (s + pf <= ze) tma_prefetch_3d(&tm_f, xb - 2, yb - 1, s + pf - zoff);
             }
         }
         // ---- black(s-1), then the finished row of plane s-1 is stored ----

@@ -42,12 +42,16 @@ __device__ __forceinline__ double rs3_plane_terms(double acc, bool first, double
     return acc;
 }
 
-// grid = (ceil((nc-2) / 30), ceil((nc-2) / RYC), ceil((nc-2) / zchunk)), block = 32 * (2 RYC + 1); whole grids.
+// grid = (ceil((nc-2) / 30), ceil((nc-2) / RYC), ceil(planes / zchunk)), block = 32 * (2 RYC + 1).
+// z-slabs: the tensor maps describe the fine slab array including its ghost planes, their plane 0 being the
+// global fine plane `zoff_f`; `coarse` points at the global coarse plane `zoff_c` of the coarse slab; the
+// coarse planes Zlo .. Zhi (global, the owned ones) are written.  Whole grids: offsets 0, Zlo = 1, Zhi = nc-2.
 template <int RYC, int NS, int NF>
 __global__ void __launch_bounds__(32 * (2 * RYC + 1)) k_resrestrict3d(Geom gc, Geom gf, Star3D st,
                                                                      const __grid_constant__ CUtensorMap tm_u,
                                                                      const __grid_constant__ CUtensorMap tm_f,
-                                                                     double* __restrict__ coarse, int zchunk) {
+                                                                     double* __restrict__ coarse, int zchunk,
+                                                                     int zoff_f, int zoff_c, int Zlo, int Zhi) {
     constexpr int RF = 2 * RYC, UR = RF + 3, FR = RF + 1, NW = RF + 1;
     constexpr uint32_t U_BYTES = UR * RB3_W * 8, F_BYTES = FR * RB3_W * 8;
     constexpr int U_SLOT = UR * RB3_W, F_SLOT = FR * RB3_W;
@@ -59,8 +63,8 @@ __global__ void __launch_bounds__(32 * (2 * RYC + 1)) k_resrestrict3d(Geom gc, G
     pdl_sync();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nc = gc.n;
-    const int X0 = 1 + blockIdx.x * RS3_TXC, Y0 = 1 + blockIdx.y * RYC, Zb = 1 + blockIdx.z * zchunk;
-    const int Ze = imin(Zb + zchunk, nc - 1);                               // coarse planes Zb .. Ze-1
+    const int X0 = 1 + blockIdx.x * RS3_TXC, Y0 = 1 + blockIdx.y * RYC, Zb = Zlo + blockIdx.z * zchunk;
+    const int Ze = imin(Zb + zchunk, Zhi + 1);                              // coarse planes Zb .. Ze-1 (global indices)
     const int xb = 2 * X0, yb = 2 * Y0;
     const int z0 = 2 * Zb - 1, z1 = 2 * Ze - 1;                             // fine planes of the march
     const int p0 = z0 - 1;                                                  // first staged plane of u (f: z0)
@@ -70,14 +74,14 @@ __global__ void __launch_bounds__(32 * (2 * RYC + 1)) k_resrestrict3d(Geom gc, G
         if (lane == 0) {
             const uint32_t bar = bar_a + 8 * slot;
             mbar_arrive_expect_tx(bar, U_BYTES);
-            tma_load_3d(su_a + (uint32_t)(slot * U_SLOT * 8), &tm_u, xb - 2, yb - 2, p, bar);
+            tma_load_3d(su_a + (uint32_t)(slot * U_SLOT * 8), &tm_u, xb - 2, yb - 2, p - zoff_f, bar);
         }
     };
     auto stage_f = [&](int p, int slot) {
         if (lane == 0) {
             const uint32_t bar = bar_a + 8 * (NS + slot);
             mbar_arrive_expect_tx(bar, F_BYTES);
-            tma_load_3d(sf_a + (uint32_t)(slot * F_SLOT * 8), &tm_f, xb - 2, yb - 1, p, bar);
+            tma_load_3d(sf_a + (uint32_t)(slot * F_SLOT * 8), &tm_f, xb - 2, yb - 1, p - zoff_f, bar);
         }
     };
 
@@ -146,7 +150,7 @@ __global__ void __launch_bounds__(32 * (2 * RYC + 1)) k_resrestrict3d(Geom gc, G
                 const int Zdone = (z - 1) >> 1;                              // oz = +1 finishes the coarse plane below
                 if (Zdone >= Zb) {
                     const double v = rs3_plane_terms(acc, false, 0.25, lm, ym, l0, r2, lp, yp);
-                    if (store_ok) cptr[(long long)Zdone * gc.plane] = v;
+                    if (store_ok) cptr[(long long)(Zdone - zoff_c) * gc.plane] = v;
                 }
                 acc = rs3_plane_terms(0.0, true, 0.25, lm, ym, l0, r2, lp, yp);      // oz = -1 starts the one above
             } else {

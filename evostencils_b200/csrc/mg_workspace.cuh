@@ -40,6 +40,7 @@ struct Level {
     int level = 0;
     Geom g{};
     void* slab = nullptr;
+    size_t slab_bytes = 0;
     void* sol[2][MG_MAX_FIELDS] = {};
     void* rhs[MG_MAX_FIELDS] = {};
     void* res[MG_MAX_FIELDS] = {};
@@ -47,6 +48,7 @@ struct Level {
     void* init[MG_MAX_FIELDS] = {};     // finest only: saved initial guess
     int cur[MG_MAX_FIELDS] = {};        // which sol buffer is current
     bool zero_pending = false;          // sol[0] is logically zero; the fill has not been issued (mg_exec.cuh)
+    bool wide_ghost = false;            // z-slab: one more ghost plane lies before local plane 0 and after nz-1
     HostOperator hop;
     void* d_op = nullptr;               // OperatorTable<T>
     bool op_dirty = true;
