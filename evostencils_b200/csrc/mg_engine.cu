@@ -138,6 +138,8 @@ static int create_impl(mg_workspace** out, int dimension, int min_level, int max
     return MG_OK;
 }
 
+static void dd_release(mg_workspace* ws);
+
 static void free_smoothers(mg_workspace* ws) {
     for (auto& s : ws->smoothers) {
         if (s.d_table) cudaFree(s.d_table);
@@ -184,6 +186,7 @@ extern "C" int mg_destroy(mg_workspace* ws) {
         if (lv.d_op) cudaFree(lv.d_op);
         if (lv.partial) cudaFree(lv.partial);
     }
+    dd_release(ws);
     if (ws->cgs_work) cudaFree(ws->cgs_work);
     for (void* p : ws->fas_raw) cudaFree(p);
     delete ws->tail;
@@ -339,3 +342,4 @@ extern "C" int mg_clear_smoothers(mg_workspace* ws) {
 #include "mg_engine_run.inc"
 #include "mg_engine_fas.inc"
 #include "mg_engine_noalloc.inc"
+#include "mg_engine_dd.inc"

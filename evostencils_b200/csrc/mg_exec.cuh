@@ -6,6 +6,7 @@
 #include "mg_tail.cuh"
 #include "mg_kernels_fast.cuh"
 #include "mg_outer.cuh"
+#include "mg_dd.cuh"
 #include "mg_workspace.cuh"
 
 namespace mg {
@@ -366,7 +367,7 @@ int exec_cgs(mg_workspace* ws, int level) {
 }
 
 template <typename T, int D, int F>
-int exec_norm(mg_workspace* ws, int level) {
+int exec_norm(mg_workspace* ws, int level, int squares = 0) {
     Level& lv = ws->L(level);
     int rc = upload_operator<T>(ws, lv);
     if (rc) return rc;
@@ -377,7 +378,7 @@ int exec_norm(mg_workspace* ws, int level) {
         lv.norm_count = lv.norm_blocks;
         count(ws);
     }
-    launch_k(ws, k_norm_final<T>, 1, 256, 0, static_cast<const T*>(lv.partial), lv.norm_count, ws->d_norm);
+    launch_k(ws, k_norm_final<T>, 1, 256, 0, static_cast<const T*>(lv.partial), lv.norm_count, ws->d_norm, squares);
     count(ws);
     return MG_OK;
 }

@@ -363,9 +363,11 @@ __global__ void __launch_bounds__(256) k_norm_partial(Geom g, const OperatorTabl
     if (threadIdx.x == 0) partial[blockIdx.x] = total;
 }
 
-// out[0] = |sqrt(sum partial)|  (real: sqrt; complex: modulus of the complex square root)
+// out[0] = |sqrt(sum partial)|  (real: sqrt; complex: modulus of the complex square root);
+// squares != 0 (real data): the sum itself -- a rank's share of a domain-decomposed norm (mg_dd.cuh)
 template <typename T>
-__global__ void __launch_bounds__(256) k_norm_final(const T* __restrict__ partial, int n, double* __restrict__ out) {
+__global__ void __launch_bounds__(256) k_norm_final(const T* __restrict__ partial, int n, double* __restrict__ out,
+                                                    int squares) {
     pdl_sync();
     __shared__ T s8[8];
     T acc = t_zero(T());
@@ -373,7 +375,8 @@ __global__ void __launch_bounds__(256) k_norm_final(const T* __restrict__ partia
     T total = block_sum_256<T>(acc, s8);
     if (threadIdx.x == 0) {
         if constexpr (sizeof(T) == sizeof(double)) {
-            out[0] = sqrt(*reinterpret_cast<double*>(&total));
+            const double t = *reinterpret_cast<double*>(&total);
+            out[0] = squares ? t : sqrt(t);
         } else {
             cplx c = *reinterpret_cast<cplx*>(&total);
             out[0] = sqrt(t_hypot(c.re, c.im));       // |sqrt(z)| = sqrt(|z|)

@@ -76,6 +76,13 @@ struct Smoother {
     bool canonical_slots = false;       // slot s sits at (s / period[1], s % period[1]) of field 0 (2D scalar tiles)
 };
 
+// domain decomposition (mg_dd.cuh, mg_engine_dd.inc): what a rank knows about a peer's level
+struct DDPeerLevel {
+    char* base = nullptr;                   // the peer's level allocation, mapped into this process
+    long long off_sol[2] = {0, 0}, off_rhs = 0, off_res = 0;       // byte offsets of its field arrays (field 0)
+    int nz = 0, z0 = 0;
+};
+
 struct GraphVariant {
     cudaGraphExec_t exec = nullptr;
     int end_state = 0;
@@ -140,6 +147,16 @@ struct mg_workspace {
     int outer_graph_cycle = -1;
     long long outer_graph_kernels = 0;
     size_t cgs_smem_bytes = 0;                  // dynamic shared memory of the coarse solver (0: global scratch)
+    // domain decomposition: this workspace is the z-slab of `dd_rank` (mg_engine_dd.inc)
+    int dd_rank = -1, dd_world = 0;
+    void* dd_comm = nullptr;                    // mg::DDComm of this rank (device)
+    void* dd_peer_comm[16] = {};                // every rank's DDComm, mapped (own included)
+    std::vector<mg::DDPeerLevel> dd_lo, dd_hi;  // neighbours' levels, index = level - min_level
+    std::vector<mg::DDPeerLevel> dd_base;       // every rank's coarsest slab level (index = rank): gather source
+    mg_workspace* dd_coarse = nullptr;          // replicated whole-grid hierarchy below the slab levels
+    std::map<std::string, void*> dd_ipc_opened; // CUDA IPC handle -> mapping (a handle is opened once)
+    std::vector<mg::Cycle> dd_cycles;
+    bool dd_use_graph = true;
     // nonlinear FAS stages (mg_fas.cuh): Approximation field per level, allocated on first use
     std::vector<void*> fas_approx;              // index = level - min_level (points past the guard rows)
     std::vector<void*> fas_raw;                 // the allocations behind them

@@ -37,6 +37,8 @@ EXPORTED_SYMBOLS = [
     "mg_time_ops", "mg_profile_ops", "mg_mark", "mg_elapsed", "mg_flush_l2", "mg_set_fast_kernels",
     "mg_fas_smooth", "mg_fas_residual", "mg_fas_restrict", "mg_fas_subtract_approximation", "mg_fas_residual_norm",
     "mg_residual_norm_noalloc",
+    "mg_dd_init", "mg_dd_describe", "mg_dd_attach", "mg_dd_exchange", "mg_dd_build_cycle", "mg_dd_prepare", "mg_dd_launch",
+    "mg_dd_norm", "mg_dd_read_norm", "mg_dd_error",
 ]
 
 
@@ -108,6 +110,16 @@ def _signatures():
         "mg_fas_subtract_approximation": [vp, i32],
         "mg_fas_residual_norm": [vp, i32, dbl, pdbl],
         "mg_residual_norm_noalloc": [i32, i32, i32, i32, pi32, pdbl, vp, vp, vp, vp],
+        "mg_dd_init": [vp, i32, i32, vp],
+        "mg_dd_describe": [vp, i32, C.POINTER(C.c_uint64), vp],
+        "mg_dd_attach": [vp, i32, i32, C.POINTER(C.c_uint64), vp],
+        "mg_dd_exchange": [vp, i32, i32, i32],
+        "mg_dd_build_cycle": [vp, ops, i32, pint],
+        "mg_dd_prepare": [vp, i32],
+        "mg_dd_launch": [vp, i32, i32],
+        "mg_dd_norm": [vp],
+        "mg_dd_read_norm": [vp, pdbl],
+        "mg_dd_error": [vp, pint],
     }
 
 
@@ -487,6 +499,45 @@ class Workspace:
 
     def flush_l2(self, nbytes=256 << 20):
         self._check(self.lib.mg_flush_l2(self._h, nbytes))
+
+    # -- domain decomposition with peer-to-peer halo exchange (mg_dd.cuh, mg_engine_dd.inc) ----------------
+    def dd_init(self, rank: int, world: int, coarse: "Workspace"):
+        self._check(self.lib.mg_dd_init(self._h, rank, world, coarse._h))
+
+    def dd_describe(self, level: int, ipc: bool):
+        """-> (descriptor tuple of 8 ints, 64-byte CUDA IPC handle or None); level < 0: the comm block."""
+        desc = (C.c_uint64 * 8)()
+        handle = C.create_string_buffer(64) if ipc else None
+        self._check(self.lib.mg_dd_describe(self._h, level, desc, handle))
+        return tuple(int(v) for v in desc), (handle.raw if ipc else None)
+
+    def dd_attach(self, peer: int, level: int, desc, handle):
+        d = (C.c_uint64 * 8)(*desc)
+        buf = C.create_string_buffer(handle, 64) if handle is not None else None
+        self._check(self.lib.mg_dd_attach(self._h, peer, level, d, buf))
+
+    def dd_exchange(self, kind: str, level: int, planes: int):
+        self._check(self.lib.mg_dd_exchange(self._h, _FIELD[kind], level, planes))
+
+    def dd_build_cycle(self, encoded) -> int:
+        """`encoded`: MgOp array of the unfused cycle (domain.encode_for_slabs)."""
+        cycle = C.c_int()
+        self._check(self.lib.mg_dd_build_cycle(self._h, encoded, len(encoded), C.byref(cycle)))
+        return cycle.value
+
+    def dd_prepare(self, cycle: int):
+        self._check(self.lib.mg_dd_prepare(self._h, cycle))
+
+    def dd_launch(self, cycle: int, n: int = 1):
+        self._check(self.lib.mg_dd_launch(self._h, cycle, n))
+
+    def dd_norm(self):
+        self._check(self.lib.mg_dd_norm(self._h))
+
+    def dd_read_norm(self) -> float:
+        out = C.c_double()
+        self._check(self.lib.mg_dd_read_norm(self._h, C.byref(out)))
+        return out.value
 
     # -- nonlinear FAS stages (mg_fas.cuh; FAS_2D_Basic.exa4) ------------------------------------
     def fas_smooth(self, level, omega, gamma, sweeps=1, newton_steps=1, colored=False):

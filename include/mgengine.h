@@ -176,6 +176,32 @@ int mg_flush_l2(mg_workspace* ws, size_t bytes);
  * (default 3 = both; 0 = generic grid kernels only) */
 int mg_set_fast_kernels(mg_workspace* ws, int enabled);
 
+/* ---- 3D domain decomposition with peer-to-peer halo exchange (BASELINE.json configs[2]) ------------ */
+/* No reference counterpart (one block / one fragment: example_problems/lib/domain_onePatch.knowledge:4-9,
+ * parallelization_pureOmp.knowledge:5).  A rank = a z-slab workspace (mg_create_slab; it carries two ghost
+ * planes on either side) + a whole-grid workspace of the levels below, run redundantly by every rank.
+ * Ranks store halo planes straight into each other's memory (NVLink; CUDA IPC between processes) and
+ * order them with flag words -- no collective-library call inside a cycle, one CUDA graph per cycle and rank.
+ * Setup: mg_dd_init on every rank; mg_dd_describe for the comm block (level < 0) and every slab level; the
+ * caller ships descriptors + IPC handles between the ranks; mg_dd_attach for every peer's comm block, the two
+ * neighbours' slab levels and every rank's coarsest slab level.  Then every rank enqueues the same sequence of
+ * mg_dd_exchange / mg_dd_norm / mg_dd_launch calls.  Results are bitwise those of the single-domain solve
+ * (norms: the rank-ordered sum of the ranks' partial sums of squares). */
+int mg_dd_init(mg_workspace* slab, int rank, int world, mg_workspace* coarse);
+int mg_dd_describe(mg_workspace* slab, int level, uint64_t* desc8, void* ipc_handle64);
+int mg_dd_attach(mg_workspace* slab, int peer, int level, const uint64_t* desc8, const void* ipc_handle64);
+/* halo exchange of 1 or 2 boundary planes of a field (MG_SOL / MG_RHS / MG_RES) with both neighbours, enqueued */
+int mg_dd_exchange(mg_workspace* slab, int field_kind, int level, int planes);
+/* the unfused op list of one cycle (every rank the same; smoother handles of ops on levels <= the coarsest slab
+ * level are the coarse workspace's); the engine inserts exchanges, the gather of the coarsest slab level's
+ * right-hand side and the fused kernels where they apply */
+int mg_dd_build_cycle(mg_workspace* slab, const mg_op* ops, int n_ops, int* cycle);
+int mg_dd_prepare(mg_workspace* slab, int cycle);              /* instantiate the graphs outside a timed region */
+int mg_dd_launch(mg_workspace* slab, int cycle, int n);        /* enqueue n cycles, each followed by the norm */
+int mg_dd_norm(mg_workspace* slab);                            /* enqueue the combined residual norm alone */
+int mg_dd_read_norm(mg_workspace* slab, double* out);          /* synchronise; MG_ERR_STATE if a peer never arrived */
+int mg_dd_error(mg_workspace* slab, int* flag);
+
 /* ---- nonlinear FAS stages ------------------------------------------ */
 /* -Laplace(u) + gamma u e^u = f: the statements of example_problems/FAS_2D_Basic/FAS_2D_Basic.exa4
  * (replaces the Layer-4 text ProgramGeneratorFAS.traverse_graph emits, code_generation/
