@@ -134,6 +134,10 @@ class SlabComm:
         if self.dist is not None:
             self.dist.barrier(group=self.group)
 
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier(group=self.group)
+
     def sum_in_rank_order(self, values: Dict[int, float]) -> float:
         """Deterministic: every rank adds the world's values in rank order."""
         import torch
@@ -406,6 +410,26 @@ class DomainDecomposedSolver:
                     "halo_exchanges_per_cycle": self.halo_exchanges / cycles,
                     "dd_min_level": self.dd_min_level, "splits": self.splits}
 
+    def time_cycles(self, ops: Sequence[object], cycles: int, warmup: int = 1):
+        """`cycles` cycles back to back between device-synchronised barriers -> (ms per cycle, record)."""
+        import time
+        for _ in range(warmup):
+            self.run_ops(ops)
+        self.comm.bytes_sent = 0
+        self.halo_exchanges = 0
+        self.comm.barrier()
+        self._sync()
+        t0 = time.perf_counter()
+        for _ in range(cycles):
+            self.run_ops(ops)
+        self._sync()
+        self.comm.barrier()
+        ms = (time.perf_counter() - t0) * 1e3 / cycles
+        return ms, {"driver": "op-by-op host driver, NCCL send/recv halo exchange (no graph)",
+                    "halo_bytes_per_cycle_rank0": self.comm.bytes_sent / cycles,
+                    "halo_exchanges_per_cycle": self.halo_exchanges / cycles,
+                    "dd_min_level": self.dd_min_level, "splits": self.splits}
+
     def solve(self, ops: Sequence[object], tol: float, max_its: int):
         """Outer iteration of the generated solver (same conventions as mg_solve)
         -> (history, converged, milliseconds)."""
@@ -429,5 +453,228 @@ class DomainDecomposedSolver:
 
 def make_solver(problem, min_level: int, max_level: int, comm: SlabComm, device: int = 0, dd_min_level=None):
     """The decomposed solver for this process' rank(s) on `device`."""
+    return DomainDecomposedSolver(problem, min_level, max_level, comm, dd_min_level=dd_min_level,
+                                  device_of=lambda r: device)
+
+
+# ----------------------------------------------------------------------------------------
+# peer-to-peer transport: halo planes stored straight into the neighbour's memory (csrc/mg_dd.cuh)
+# ----------------------------------------------------------------------------------------
+
+def encode_for_slabs(slab, coarse, ops):
+    """MgOp array of the unfused cycle for mg_dd_build_cycle: smoother tables of ops on levels up to the
+    coarsest slab level are registered with (and numbered by) the coarse workspace, the others with the slab."""
+    from .engine import MgOp
+    flat = []
+    base = slab.min_level
+    for op in ops:
+        ws = coarse if op.level <= base else slab
+        flat.extend(ws.encode([op]))
+    return (MgOp * len(flat))(*flat)
+
+
+class PeerSlabSolver:
+    """One 3D solve over `world` z-slabs whose ranks exchange halo planes, the agglomerated right-hand side
+    and the partial norms by peer-to-peer stores / loads inside the engine's own kernels (NVLink between the
+    GPUs of a node; CUDA IPC maps the neighbours' arrays) -- torch.distributed only ships the memory
+    descriptors once at set-up.  A cycle of a rank is one CUDA-graph launch; the host reads one double per
+    cycle.  Ranks are virtual like in `DomainDecomposedSolver`: with `dist` a process drives its own rank, in
+    the single-GPU tests one process drives all of them (same kernels, same handshakes, plain pointers).
+    Results are bitwise those of the single-domain engine."""
+
+    def __init__(self, problem, min_level: int, max_level: int, world: int, local_ranks: Sequence[int], dist=None,
+                 group=None, dd_min_level: Optional[int] = None, device_of=None, params: Optional[dict] = None):
+        from .engine import EngineError, Workspace
+        if problem.dimension != 3 or problem.n_fields != 1 or problem.dtype != "f64":
+            raise EngineError("the peer-to-peer decomposition is implemented for scalar fp64 3D problems")
+        if dist is not None and len(local_ranks) != 1:
+            raise ValueError("with torch.distributed a process drives exactly one rank")
+        if dist is None and sorted(local_ranks) != list(range(world)):
+            raise ValueError("without torch.distributed one process must drive every rank")
+        self.problem, self.world, self.dist, self.group = problem, world, dist, group
+        self.min_level, self.max_level = min_level, max_level
+        self.dd_min_level = (min(max_level, default_dd_min_level(min_level, world)) if dd_min_level is None
+                             else dd_min_level)
+        if not min_level < self.dd_min_level <= max_level:
+            raise EngineError("dd_min_level must lie in (min_level, max_level]")
+        self.base = self.dd_min_level - 1
+        self.splits = slab_splits(max_level, self.dd_min_level, world)
+        self.params = dict(problem.parameters)
+        self.params.update(params or {})
+        device_of = device_of or (lambda rank: 0)
+        self.locals: List[_Local] = []
+        for r in local_ranks:
+            ranges = slab_ranges(self.base, max_level, self.splits, r)
+            slab = Workspace(3, self.base, max_level, 1, "f64", device_of(r), slab=ranges)
+            coarse = Workspace(3, min_level, self.base, 1, "f64", device_of(r))
+            for ws in (slab, coarse):
+                for level in range(ws.min_level, ws.max_level + 1):
+                    ws.set_operator(level, lowering.operator_table(problem.system_operator(level, 0, self.params)))
+            coarse.set_coarse_solver(problem.solver.cgs, problem.solver.cgs_max_iterations,
+                                     problem.solver.cgs_target_reduction)
+            slab.dd_init(r, world, coarse)
+            self.locals.append(_Local(r, slab, coarse))
+        self._connect()
+        self._cycles: Dict[int, int] = {}
+
+    # -- set-up: every rank learns where its peers' arrays live ----------------------------------------
+    def _connect(self):
+        ipc = self.dist is not None
+        mine = {}
+        for loc in self.locals:
+            table = {-1: loc.slab.dd_describe(-1, ipc)}
+            for level in range(self.base, self.max_level + 1):
+                table[level] = loc.slab.dd_describe(level, ipc)
+            mine[loc.rank] = table
+        if ipc:
+            gathered = [None] * self.world
+            self.dist.all_gather_object(gathered, mine, group=self.group)
+            everyone = {}
+            for part in gathered:
+                everyone.update(part)
+        else:
+            everyone = mine
+        for loc in self.locals:
+            for q in range(self.world):
+                loc.slab.dd_attach(q, -1, *everyone[q][-1])
+                loc.slab.dd_attach(q, self.base, *everyone[q][self.base])
+            for q in (loc.rank - 1, loc.rank + 1):
+                if 0 <= q < self.world:
+                    for level in range(self.base + 1, self.max_level + 1):
+                        loc.slab.dd_attach(q, level, *everyone[q][level])
+        self.barrier()
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier(group=self.group)
+
+    def close(self):
+        for loc in self.locals:
+            loc.slab.synchronize()
+        self.barrier()                      # nobody unmaps memory a peer's kernel may still touch
+        for loc in self.locals:
+            loc.slab.close()
+            loc.coarse.close()
+        self.locals = []
+
+    # -- data --------------------------------------------------------------------------------------------
+    def plane_range(self, rank: int, level: int) -> Tuple[int, int]:
+        zb, ze = owned_planes(level, self.max_level, self.splits, rank)
+        return zb - 1, ze + 2
+
+    def set_fields(self, rhs, u0):
+        """rhs, u0: per field either a full host array [n][n][n] or a callable (z_lo, z_hi) -> slab array.
+        The second ghost planes of the solution (read by the one-pass smoother) are filled by an exchange."""
+        L = self.max_level
+        for loc in self.locals:
+            z_lo, z_hi = self.plane_range(loc.rank, L)
+            for kind, src in (("rhs", rhs[0]), ("sol", u0[0])):
+                loc.slab.upload(kind, L, 0, src(z_lo, z_hi) if callable(src) else src[z_lo:z_hi])
+        self.barrier()
+        for loc in self.locals:
+            loc.slab.dd_exchange("sol", L, 2)
+        for loc in self.locals:
+            loc.slab.synchronize()
+
+    def local_solution(self, rank: int):
+        """Host copy [nz][n][n] of a local rank's finest-level slab (ghost planes included)."""
+        (loc,) = [l for l in self.locals if l.rank == rank]
+        return loc.slab.download("sol", self.max_level, 0)
+
+    def gather_solution(self):
+        """Full finest-level solution on the host; needs every rank local (tests)."""
+        import numpy as np
+        L = self.max_level
+        n = 2 ** L + 1
+        out = np.zeros((n, n, n))
+        for loc in self.locals:
+            z_lo, z_hi = self.plane_range(loc.rank, L)
+            slab = loc.slab.download("sol", L, 0)
+            zb, ze = owned_planes(L, L, self.splits, loc.rank)
+            out[zb:ze + 1] = slab[zb - z_lo: ze + 1 - z_lo]
+            if loc.rank == 0:
+                out[0] = slab[0]
+            if loc.rank == self.world - 1:
+                out[-1] = slab[-1]
+        return out
+
+    # -- execution ---------------------------------------------------------------------------------------
+    def cycle_handle(self, ops) -> int:
+        key = id(ops)
+        if key not in self._cycles:
+            handle = None
+            for loc in self.locals:
+                h = loc.slab.dd_build_cycle(encode_for_slabs(loc.slab, loc.coarse, ops))
+                assert handle is None or handle == h
+                handle = h
+                loc.slab.dd_prepare(h)
+            self._cycles[key] = handle
+            self._keep = getattr(self, "_keep", []) + [ops]       # ids stay unique while the list lives
+            self.barrier()                   # every rank's graphs exist before anybody's kernels wait for a peer
+        return self._cycles[key]
+
+    def launch(self, ops, n: int = 1):
+        handle = self.cycle_handle(ops)
+        for loc in self.locals:
+            loc.slab.dd_launch(handle, n)
+
+    def read_norm(self) -> float:
+        values = [loc.slab.dd_read_norm() for loc in self.locals]
+        assert all(v == values[0] or (v != v and values[0] != values[0]) for v in values), values
+        return values[0]
+
+    def residual_norm(self) -> float:
+        for loc in self.locals:
+            loc.slab.dd_norm()
+        return self.read_norm()
+
+    def solve(self, ops: Sequence[object], tol: float, max_its: int):
+        """Outer iteration of the generated solver (same conventions as mg_solve) -> (history, converged, ms)."""
+        import time
+        handle = self.cycle_handle(ops)
+        t0 = time.perf_counter()
+        history = [self.residual_norm()]
+        converged = False
+        for _ in range(max_its):
+            for loc in self.locals:
+                loc.slab.dd_launch(handle, 1)
+            r = self.read_norm()
+            history.append(r)
+            if not math.isfinite(r):
+                break
+            if r < tol * history[0]:
+                converged = True
+                break
+        return history, converged, (time.perf_counter() - t0) * 1e3
+
+    def time_cycles(self, ops: Sequence[object], cycles: int, warmup: int = 1):
+        """`cycles` graph launches back to back -> (device ms per cycle on this process, record)."""
+        handle = self.cycle_handle(ops)
+        launches0 = sum(loc.slab.launch_count() for loc in self.locals)
+        for loc in self.locals:
+            loc.slab.dd_launch(handle, warmup)
+        self.read_norm()
+        self.barrier()
+        for loc in self.locals:
+            loc.slab.mark(0)
+            loc.slab.dd_launch(handle, cycles)
+            loc.slab.mark(1)
+        self.read_norm()
+        ms = max(loc.slab.elapsed() for loc in self.locals) / cycles
+        self.barrier()
+        kernels = (sum(loc.slab.launch_count() for loc in self.locals) - launches0) / (cycles + warmup) / len(self.locals)
+        return ms, {"driver": "one CUDA graph per cycle and rank; halo planes, gathered right-hand side and partial "
+                              "norms move by peer-to-peer stores / loads inside the engine's kernels (no NCCL call)",
+                    "kernels_per_cycle_and_rank": kernels, "dd_min_level": self.dd_min_level, "splits": self.splits,
+                    "timing": "CUDA events on the rank's stream around the launches"}
+
+
+def make_solver(problem, min_level: int, max_level: int, comm: SlabComm, device: int = 0, dd_min_level=None,
+                transport: str = "peer"):
+    """The decomposed solver for this process' rank(s) on `device`: `peer` = PeerSlabSolver (the product
+    path), `nccl` = the op-by-op driver with torch.distributed send/recv (kept for comparison)."""
+    if transport == "peer":
+        return PeerSlabSolver(problem, min_level, max_level, comm.world, comm.local_ranks, comm.dist, comm.group,
+                              dd_min_level=dd_min_level, device_of=lambda r: device)
     return DomainDecomposedSolver(problem, min_level, max_level, comm, dd_min_level=dd_min_level,
                                   device_of=lambda r: device)

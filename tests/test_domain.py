@@ -163,3 +163,134 @@ def test_decomposed_solve_with_the_specialised_3d_kernels(monkeypatch):
     monkeypatch.setenv("MG_TAIL_LEVEL", "3")
     test_decomposed_solve_is_bitwise_the_single_domain_solve(2, 2, 7)
     test_decomposed_solve_is_bitwise_the_single_domain_solve(4, 3, 7)
+
+
+# ---- peer-to-peer transport (csrc/mg_dd.cuh): one CUDA graph per cycle and rank ---------------------------------
+
+def _single_domain(problem, program, lo, hi, fs, us, cycles):
+    from evostencils_b200 import lowering
+    from evostencils_b200.engine import Workspace
+    ws = Workspace(3, lo, hi, 1, "f64", 0)
+    for level in range(lo, hi + 1):
+        ws.set_operator(level, lowering.operator_table(problem.system_operator(level, 0)))
+    ws.set_coarse_solver(problem.solver.cgs, problem.solver.cgs_max_iterations, problem.solver.cgs_target_reduction)
+    ws.upload("rhs", hi, 0, fs[0])
+    ws.upload("sol", hi, 0, us[0])
+    hist = [ws.residual_norm()]
+    for _ in range(cycles):
+        ws.exec_ops(program.ops, fused=False)
+        hist.append(ws.residual_norm())
+    u = ws.download("sol", hi, 0)
+    ws.close()
+    return hist, u
+
+
+def _case(lo, hi, seed=5):
+    from evostencils_b200 import lowering, problems
+    from evostencils_b200.grammar import Grammar, v_cycle_string
+    problem = problems.POISSON_3D
+    expression, _ = Grammar(problem, lo, hi).compile(v_cycle_string(hi - lo, 2, 1, 23, "red_black"))
+    program = lowering.lower(expression, lo, hi)
+    us, fs = problem.initial_fields(hi, {})
+    fs = [f + 0 for f in fs]
+    fs[0][1:-1, 1:-1, 1:-1] += np.random.default_rng(seed).standard_normal(fs[0][1:-1, 1:-1, 1:-1].shape)
+    return problem, program, us, fs
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world,lo,hi,dd", [(2, 2, 5, 3), (4, 2, 6, 4), (3, 2, 5, 3), (2, 2, 6, 6)])
+@pytest.mark.parametrize("graph", ["1", "0"])
+def test_peer_transport_is_bitwise_the_single_domain_solve(world, lo, hi, dd, graph, monkeypatch):
+    """Virtual ranks on one GPU: the ranks' kernels run on different streams of the same device and hand
+    halo planes, the gathered right-hand side and the partial norms to each other through the flag
+    handshakes of mg_dd.cuh (plain pointers instead of CUDA IPC mappings).  Graph replays and direct
+    launches, decomposition down to level `dd`."""
+    monkeypatch.setenv("MG_DD_GRAPH", graph)
+    problem, program, us, fs = _case(lo, hi)
+    want_hist, want = _single_domain(problem, program, lo, hi, fs, us, 3)
+    solver = domain.PeerSlabSolver(problem, lo, hi, world, list(range(world)), dd_min_level=dd)
+    solver.set_fields(fs, us)
+    hist, converged, ms = solver.solve(program.ops, 0.0, 3)
+    got = solver.gather_solution()
+    solver.close()
+    assert np.array_equal(got, want)
+    assert np.allclose(hist, want_hist, rtol=1e-12, atol=0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 3])
+def test_peer_transport_with_the_one_pass_kernels_on_slabs(world, monkeypatch):
+    """129^3 with the thresholds of k_rbgs3d / k_resrestrict3d lowered to 65: levels 6 and 7 are slabs with two
+    ghost planes, one exchange per sweep, fused residual + restriction on the slabs -- still bitwise the
+    single-domain result (which runs the same kernels on the whole grid)."""
+    monkeypatch.setenv("MG_RBGS3D_MIN_N", "65")
+    monkeypatch.setenv("MG_RESTRICT3D_MIN_N", "65")
+    lo, hi = 2, 7
+    problem, program, us, fs = _case(lo, hi, seed=6)
+    want_hist, want = _single_domain(problem, program, lo, hi, fs, us, 2)
+    solver = domain.PeerSlabSolver(problem, lo, hi, world, list(range(world)), dd_min_level=6)
+    solver.set_fields(fs, us)
+    hist, converged, ms = solver.solve(program.ops, 0.0, 2)
+    got = solver.gather_solution()
+    ms_cycle, info = solver.time_cycles(program.ops, 2, warmup=1)
+    solver.close()
+    assert np.array_equal(got, want)
+    assert np.allclose(hist, want_hist, rtol=1e-12, atol=0)
+    # V(2,1): 3 sweeps + fused restriction + prolongation per slab level, far fewer launches than exchanges + ops
+    assert info["kernels_per_cycle_and_rank"] < 60 and ms_cycle > 0
+
+
+def _peer_worker(rank, world, port, queue):
+    sys.path.insert(0, REPO)
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from evostencils_b200 import domain as d
+    lo, hi = 2, 7
+    problem, program, us, fs = _case(lo, hi, seed=7)
+    os.environ["MG_RBGS3D_MIN_N"] = "65"
+    os.environ["MG_RESTRICT3D_MIN_N"] = "65"
+    solver = d.PeerSlabSolver(problem, lo, hi, world, [rank], dist, dd_min_level=6, device_of=lambda r: rank)
+    solver.set_fields(fs, us)
+    hist, converged, ms = solver.solve(program.ops, 0.0, 3)
+    z_lo, z_hi = solver.plane_range(rank, hi)
+    mine = solver.local_solution(rank)
+    solver.close()
+    queue.put((rank, hist, z_lo, z_hi, mine))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_peer_transport_between_two_processes_over_cuda_ipc():
+    """Two processes, two GPUs (run with `gpurun --gpus 2`; skipped on a single-GPU box): the neighbours'
+    arrays are mapped with cudaIpcOpenMemHandle and the halo planes travel over NVLink."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    lo, hi = 2, 7
+    os.environ["MG_RBGS3D_MIN_N"] = "65"
+    os.environ["MG_RESTRICT3D_MIN_N"] = "65"
+    try:
+        problem, program, us, fs = _case(lo, hi, seed=7)
+        want_hist, want = _single_domain(problem, program, lo, hi, fs, us, 3)
+    finally:
+        del os.environ["MG_RBGS3D_MIN_N"], os.environ["MG_RESTRICT3D_MIN_N"]
+    ctx = mp.get_context("spawn")
+    queue = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_peer_worker, args=(r, 2, port, queue)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = [queue.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for rank, hist, z_lo, z_hi, mine in got:
+        assert np.allclose(hist, want_hist, rtol=1e-12, atol=0), rank
+        assert np.array_equal(mine[1:-1], want[z_lo + 1:z_hi - 1]), rank
+    assert got[0][1] == got[1][1]                    # the rank-ordered norm is bitwise the same on both ranks
