@@ -178,6 +178,11 @@ static void free_cycles_graphs(mg_workspace* ws) {
 extern "C" int mg_destroy(mg_workspace* ws) {
     if (!ws) return MG_OK;
     cudaSetDevice(ws->device);
+    if (ws->own_stream && ws->stream != ws->own_stream) {
+        // running on a caller's stream (mg_set_stream, mg_dd_init), which may be gone by now: wait for the device
+        cudaDeviceSynchronize();
+        ws->stream = ws->own_stream;
+    }
     if (ws->stream) cudaStreamSynchronize(ws->stream);
     free_cycles(ws);
     free_smoothers(ws);

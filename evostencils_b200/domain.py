@@ -553,8 +553,8 @@ class PeerSlabSolver:
             loc.slab.synchronize()
         self.barrier()                      # nobody unmaps memory a peer's kernel may still touch
         for loc in self.locals:
+            loc.coarse.close()              # first: it runs on the slab workspace's stream (mg_dd_init)
             loc.slab.close()
-            loc.coarse.close()
         self.locals = []
 
     # -- data --------------------------------------------------------------------------------------------

@@ -199,13 +199,13 @@ def _case(lo, hi, seed=5):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("world,lo,hi,dd", [(2, 2, 5, 3), (4, 2, 6, 4), (3, 2, 5, 3), (2, 2, 6, 6)])
-@pytest.mark.parametrize("graph", ["1", "0"])
-def test_peer_transport_is_bitwise_the_single_domain_solve(world, lo, hi, dd, graph, monkeypatch):
+def test_peer_transport_is_bitwise_the_single_domain_solve(world, lo, hi, dd):
     """Virtual ranks on one GPU: the ranks' kernels run on different streams of the same device and hand
     halo planes, the gathered right-hand side and the partial norms to each other through the flag
-    handshakes of mg_dd.cuh (plain pointers instead of CUDA IPC mappings).  Graph replays and direct
-    launches, decomposition down to level `dd`."""
-    monkeypatch.setenv("MG_DD_GRAPH", graph)
+    handshakes of mg_dd.cuh (plain pointers instead of CUDA IPC mappings); decomposition down to level `dd`.
+    (Graph replays only: one host thread drives all ranks here, and direct launches synchronise a rank's
+    stream now and then -- the tail program ring -- before the peers' work is enqueued.  Direct launches
+    are covered by the two-process test.)"""
     problem, program, us, fs = _case(lo, hi)
     want_hist, want = _single_domain(problem, program, lo, hi, fs, us, 3)
     solver = domain.PeerSlabSolver(problem, lo, hi, world, list(range(world)), dd_min_level=dd)
@@ -240,8 +240,9 @@ def test_peer_transport_with_the_one_pass_kernels_on_slabs(world, monkeypatch):
     assert info["kernels_per_cycle_and_rank"] < 60 and ms_cycle > 0
 
 
-def _peer_worker(rank, world, port, queue):
+def _peer_worker(rank, world, port, queue, graph):
     sys.path.insert(0, REPO)
+    os.environ["MG_DD_GRAPH"] = graph
     import torch
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -265,7 +266,8 @@ def _peer_worker(rank, world, port, queue):
 
 
 @pytest.mark.gpu
-def test_peer_transport_between_two_processes_over_cuda_ipc():
+@pytest.mark.parametrize("graph", ["1", "0"])
+def test_peer_transport_between_two_processes_over_cuda_ipc(graph):
     """Two processes, two GPUs (run with `gpurun --gpus 2`; skipped on a single-GPU box): the neighbours'
     arrays are mapped with cudaIpcOpenMemHandle and the halo planes travel over NVLink."""
     import torch
@@ -283,7 +285,7 @@ def test_peer_transport_between_two_processes_over_cuda_ipc():
     ctx = mp.get_context("spawn")
     queue = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_peer_worker, args=(r, 2, port, queue)) for r in range(2)]
+    procs = [ctx.Process(target=_peer_worker, args=(r, 2, port, queue, graph)) for r in range(2)]
     for p in procs:
         p.start()
     got = [queue.get(timeout=300) for _ in procs]
