@@ -63,6 +63,14 @@ struct OperatorTable {
     int n_entries[MG_MAX_FIELDS][MG_MAX_FIELDS];
     int off[MG_MAX_FIELDS][MG_MAX_FIELDS][MG_MAX_ENTRIES];     // linear offset in elements
     T val[MG_MAX_FIELDS][MG_MAX_FIELDS][MG_MAX_ENTRIES];
+    // Variable-coefficient operator (mg_set_variable_coefficient; scalar real problems): when vc_kind != 0
+    // the values above are placeholders and every kernel evaluates the (2d+1)-point stencil of
+    // -div(c grad u) at the node from c at the half-grid positions (mg_kernels_generic.cuh vc_apply);
+    // the geometry is repeated here because the operator is applied from a linear element index.
+    int vc_kind;               // mg_vc_kind
+    int vc_dim, vc_n, vc_pitch;
+    long long vc_plane;
+    double vc_kappa, vc_h;
 };
 
 // One `solve locally` statement.

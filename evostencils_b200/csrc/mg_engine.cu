@@ -244,6 +244,33 @@ extern "C" int mg_set_operator(mg_workspace* ws, int level, int row, int col, in
     return MG_OK;
 }
 
+extern "C" int mg_set_variable_coefficient(mg_workspace* ws, int kind, double kappa) {
+    int rc = check_ws(ws);
+    if (rc) return rc;
+    if (kind != MG_VC_NONE && kind != MG_VC_EXP_KAPPA) return fail(MG_ERR_INVALID, "bad variable-coefficient kind");
+    if (kind != MG_VC_NONE && !(ws->dtype == MG_F64 && ws->n_fields == 1))
+        return fail(MG_ERR_INVALID, "variable coefficients exist for scalar real problems only");
+    if (kind != MG_VC_NONE && ws->slab) return fail(MG_ERR_INVALID, "variable coefficients are not available on a z-slab workspace");
+    if (kind != MG_VC_NONE)
+        for (auto& sm : ws->smoothers)
+            if (!sm.point) return fail(MG_ERR_STATE, "tile smoothers registered: clear the smoothers first");
+    ws->vc_kind = kind;
+    ws->vc_kappa = kappa;
+    static const int star2[5][3] = {{0, -1, 0}, {-1, 0, 0}, {0, 0, 0}, {1, 0, 0}, {0, 1, 0}};
+    static const int star3[7][3] = {{0, 0, -1}, {0, -1, 0}, {-1, 0, 0}, {0, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+    for (auto& lv : ws->levels) {
+        lv.op_dirty = true;
+        if (kind == MG_VC_NONE || lv.hop.set[0][0]) continue;
+        // structure of the operator (values are evaluated per node on the device): the (2d+1)-point star
+        const int ne = 2 * ws->dim + 1;
+        lv.hop.n_entries[0][0] = ne;
+        for (int k = 0; k < ne; ++k)
+            for (int c = 0; c < MG_MAX_DIM; ++c) lv.hop.offs[0][0][k][c] = ws->dim == 2 ? star2[k][c] : star3[k][c];
+        lv.hop.set[0][0] = true;
+    }
+    return MG_OK;
+}
+
 extern "C" int mg_set_boundary(mg_workspace* ws, int bc_kind, double k) {
     if (!ws) return fail(MG_ERR_INVALID, "null workspace");
     if (bc_kind == MG_BC_HELMHOLTZ_ROBIN && !(ws->dtype == MG_C128 && ws->dim == 2))
@@ -323,6 +350,8 @@ extern "C" int mg_add_smoother(mg_workspace* ws, int level, int jacobi, int colo
     if (sm.point && n_slots > ws->n_fields) return fail(MG_ERR_INVALID, "point smoother with more slots than fields");
     if (!sm.point && (sm.colored || !sm.jacobi)) return fail(MG_ERR_INVALID, "tile smoothers are Jacobi only");
     if (!sm.point && ws->slab) return fail(MG_ERR_INVALID, "tile smoothers are not available on a z-slab workspace");
+    if (!sm.point && ws->vc_kind) return fail(MG_ERR_INVALID, "tile smoothers are not available for variable-coefficient operators");
+    if (ws->vc_kind && !(n_masks == 1 && n_slots == 1)) return fail(MG_ERR_INVALID, "variable-coefficient point smoother: one slot, one mask");
     rc = ws->dtype == MG_F64 ? add_smoother_t<double>(ws, sm, slot_pos, n_masks, masks, w_table)
                              : add_smoother_t<cplx>(ws, sm, slot_pos, n_masks, masks, w_table);
     if (rc) {

@@ -65,13 +65,29 @@ int upload_operator(mg_workspace* ws, Level& lv) {
                 tab.val[i][j][k] = host_value<T>(lv.hop.val[i][j][k]);
             }
         }
+    if (ws->vc_kind) {
+        const int d = ws->dim;
+        static const int want2[5][3] = {{0, -1, 0}, {-1, 0, 0}, {0, 0, 0}, {1, 0, 0}, {0, 1, 0}};
+        static const int want3[7][3] = {{0, 0, -1}, {0, -1, 0}, {-1, 0, 0}, {0, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+        bool ok = lv.hop.n_entries[0][0] == 2 * d + 1;
+        for (int k = 0; k < 2 * d + 1 && ok; ++k)
+            for (int c = 0; c < d; ++c) ok = ok && lv.hop.offs[0][0][k][c] == (d == 2 ? want2[k][c] : want3[k][c]);
+        if (!ok) return fail(MG_ERR_STATE, "variable-coefficient operator: the stencil must be the (2d+1)-point star");
+        tab.vc_kind = ws->vc_kind;
+        tab.vc_dim = d;
+        tab.vc_n = lv.g.n;
+        tab.vc_pitch = lv.g.pitch;
+        tab.vc_plane = lv.g.plane;
+        tab.vc_kappa = ws->vc_kappa;
+        tab.vc_h = 1.0 / (double)(lv.g.n - 1);
+    }
     if (!lv.d_op) MG_CUDA(cudaMalloc(&lv.d_op, sizeof(OperatorTable<T>)));
     MG_CUDA(cudaMemcpyAsync(lv.d_op, &tab, sizeof(tab), cudaMemcpyHostToDevice, ws->stream));
     MG_CUDA(cudaStreamSynchronize(ws->stream));
     // classify: scalar real star stencil in canonical order (z-, y-, x-, c, x+, y+, z+) with
     // symmetric coefficients per axis -> specialised kernels apply
     lv.star = false;
-    if (ws->dtype == MG_F64 && ws->n_fields == 1) {
+    if (ws->dtype == MG_F64 && ws->n_fields == 1 && !ws->vc_kind) {
         const HostOperator& h = lv.hop;
         const int d = ws->dim, ne = h.n_entries[0][0];
         if (ne == 2 * d + 1) {
@@ -212,6 +228,15 @@ int exec_restrict(mg_workspace* ws, const mg_op& op, bool fused) {
         int rc = upload_operator<T>(ws, lf);
         if (rc) return rc;
         if (ws->use_fast && fast_residual_restrict<T, D, F>(ws, lf, lc)) return MG_OK;
+        if (ws->vc_kind) {
+            // variable coefficients: the fused generic kernel would evaluate the coefficients of 3^D fine nodes
+            // per coarse node; residual + plain restriction evaluates each node once and is bit-identical
+            launch_k(ws, k_residual<T, D, F>, node_grid<D>(lf.g), 128, 0, lf.g, static_cast<const OperatorTable<T>*>(lf.d_op),
+                     cur_sol<T>(lf), fieldset<T>(lf.rhs), fieldset<T>(lf.res));
+            launch_k(ws, k_restrict<T, D, F>, node_grid<D>(lc.g), 128, 0, lc.g, lf.g, fieldset<T>(lf.res), fieldset<T>(lc.rhs));
+            count(ws, 2);
+            return MG_OK;
+        }
         if constexpr (D == 3) {
             // 3D star: the fused generic kernel recomputes 27 residuals per coarse node; the specialised
             // residual kernel + plain restriction moves fewer bytes and is bit-identical

@@ -27,10 +27,80 @@ __device__ __forceinline__ long long node_index(const Geom& g, int x, int y, int
     return (D == 3 ? (long long)z * g.plane : 0ll) + (long long)y * g.pitch + x;
 }
 
+// ---- variable-coefficient Poisson: -div(c grad u), c = exp(kappa * prod_d (x_d - x_d^2)) ----------------
+// stencils/gallery.py:87-185 (get_coefficient_2D / get_coefficient_3D and the `Operator A from Stencil` text
+// of Poisson{2,3}DVariableCoefficients.generate_exa3): the coefficient is evaluated at the half-grid
+// positions around the node, an off-centre value is (-1.0 * c_face) / (h * h), the centre is
+// ((cE + cW) / hh) + ((cN + cS) / hh) [+ ((cT + cB) / hh)].  Node positions i * h, i * h +- 0.5 * h and
+// h * h are exact in fp64 (h = 2^-level), so the oracle forms the same arguments bit for bit; only exp()
+// differs (device vs libm, <= 1 ulp).  A u is accumulated in memory order like every other operator.
+__device__ __forceinline__ double vc_axis(double p) { return p - p * p; }
+
+template <int VD>
+__device__ __forceinline__ double vc_apply_d(const OperatorTable<double>* __restrict__ op, const double* __restrict__ u,
+                                             long long idx, double& diag) {
+    const double h = op->vc_h, hh = h * h, kappa = op->vc_kappa, hf = 0.5 * h;
+    const int pitch = op->vc_pitch;
+    int z = 0;
+    long long r = idx;
+    if (VD == 3) {
+        z = (int)(idx / op->vc_plane);
+        r = idx - (long long)z * op->vc_plane;
+    }
+    const int y = (int)(r / pitch);
+    const int x = (int)(r - (long long)y * pitch);
+    const double px = x * h, py = y * h;
+    const double axc = vc_axis(px), axe = vc_axis(px + hf), axw = vc_axis(px - hf);
+    const double ayc = vc_axis(py), ayn = vc_axis(py + hf), ays = vc_axis(py - hf);
+    if (VD == 2) {
+        const double cE = exp(kappa * (axe * ayc)), cW = exp(kappa * (axw * ayc));
+        const double cN = exp(kappa * (axc * ayn)), cS = exp(kappa * (axc * ays));
+        diag = ((cE + cW) / hh) + ((cN + cS) / hh);
+        double acc = ((-1.0 * cS) / hh) * u[idx - pitch];
+        acc = acc + ((-1.0 * cW) / hh) * u[idx - 1];
+        acc = acc + diag * u[idx];
+        acc = acc + ((-1.0 * cE) / hh) * u[idx + 1];
+        acc = acc + ((-1.0 * cN) / hh) * u[idx + pitch];
+        return acc;
+    } else {
+        const double pz = z * h;
+        const double azc = vc_axis(pz), azt = vc_axis(pz + hf), azb = vc_axis(pz - hf);
+        const double cE = exp(kappa * ((axe * ayc) * azc)), cW = exp(kappa * ((axw * ayc) * azc));
+        const double cN = exp(kappa * ((axc * ayn) * azc)), cS = exp(kappa * ((axc * ays) * azc));
+        const double cT = exp(kappa * ((axc * ayc) * azt)), cB = exp(kappa * ((axc * ayc) * azb));
+        diag = (((cE + cW) / hh) + ((cN + cS) / hh)) + ((cT + cB) / hh);
+        double acc = ((-1.0 * cB) / hh) * u[idx - op->vc_plane];
+        acc = acc + ((-1.0 * cS) / hh) * u[idx - pitch];
+        acc = acc + ((-1.0 * cW) / hh) * u[idx - 1];
+        acc = acc + diag * u[idx];
+        acc = acc + ((-1.0 * cE) / hh) * u[idx + 1];
+        acc = acc + ((-1.0 * cN) / hh) * u[idx + pitch];
+        acc = acc + ((-1.0 * cT) / hh) * u[idx + op->vc_plane];
+        return acc;
+    }
+}
+
+__device__ __forceinline__ double vc_apply(const OperatorTable<double>* __restrict__ op, const double* __restrict__ u,
+                                           long long idx, double& diag) {
+    return op->vc_dim == 3 ? vc_apply_d<3>(op, u, idx, diag) : vc_apply_d<2>(op, u, idx, diag);
+}
+
+template <typename T, int F>
+__device__ __forceinline__ bool is_variable(const OperatorTable<T>* __restrict__ op) {
+    if constexpr (sizeof(T) == sizeof(double) && F == 1) return op->vc_kind != 0;
+    return false;
+}
+
 // (A u)_row at element idx, canonical accumulation order (block column ascending, entries as given)
 template <typename T, int F>
 __device__ __forceinline__ T apply_row(const OperatorTable<T>* __restrict__ op, const FieldSet<T>& u, int row,
                                        long long idx) {
+    if constexpr (sizeof(T) == sizeof(double) && F == 1) {
+        if (op->vc_kind != 0) {
+            double diag;
+            return vc_apply(op, u.p[0], idx, diag);
+        }
+    }
     T acc = t_zero(T());
     bool first = true;
 #pragma unroll
@@ -82,12 +152,20 @@ __device__ __forceinline__ void smooth_point_node(const Geom& g, const OperatorT
         }
         return;
     }
+    const T* wk = w + (long long)sm->mask_index[(1 << m) - 1] * m * m;
+    if constexpr (sizeof(T) == sizeof(double) && F == 1) {
+        if (op->vc_kind != 0) {        // W = omega / a00(node): the table holds omega (mg_add_smoother)
+            double diag;
+            const double r0 = rhs.p[0][idx] - vc_apply(op, src.p[0], idx, diag);
+            dst.p[0][idx] = src.p[0][idx] + (wk[0] / diag) * r0;
+            return;
+        }
+    }
     T r[MG_MAX_FIELDS];
     for (int s = 0; s < m; ++s) {
         int f = sm->slot_field[s];
         r[s] = t_sub(rhs.p[f][idx], apply_row<T, F>(op, src, f, idx));
     }
-    const T* wk = w + (long long)sm->mask_index[(1 << m) - 1] * m * m;
     for (int s = 0; s < m; ++s) {
         T delta = t_mul(wk[s * m + 0], r[0]);
         for (int t = 1; t < m; ++t) delta = t_add(delta, t_mul(wk[s * m + t], r[t]));

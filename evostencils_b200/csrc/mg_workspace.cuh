@@ -107,6 +107,8 @@ struct mg_workspace {
     std::vector<mg::Cycle> cycles;
     int bc_kind = MG_BC_DIRICHLET;
     double bc_k = 0.0;
+    int vc_kind = MG_VC_NONE;                   // variable-coefficient operator (mg_set_variable_coefficient)
+    double vc_kappa = 0.0;
     int cgs_kind = MG_CGS_CG, cgs_max_its = 1000;
     double cgs_reduction = 1e-12;
     void* cgs_work = nullptr;                   // global scratch when the coarse level exceeds smem

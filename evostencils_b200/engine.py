@@ -23,6 +23,7 @@ MG_F64, MG_C128 = 0, 1
 MG_SOL, MG_RHS, MG_RES, MG_COR = 0, 1, 2, 3
 MG_BC_DIRICHLET, MG_BC_HELMHOLTZ_ROBIN = 0, 1
 MG_CGS_CG, MG_CGS_BICGSTAB = 0, 1
+MG_VC_NONE, MG_VC_EXP_KAPPA = 0, 1
 (MG_OP_SMOOTH, MG_OP_RESIDUAL, MG_OP_RESTRICT, MG_OP_RESIDUAL_RESTRICT, MG_OP_ZERO, MG_OP_PROLONG_ADD,
  MG_OP_PROLONG, MG_OP_CGS) = range(8)
 
@@ -30,7 +31,7 @@ _FIELD = {"sol": MG_SOL, "rhs": MG_RHS, "res": MG_RES, "cor": MG_COR, "": MG_SOL
 
 EXPORTED_SYMBOLS = [
     "mg_create", "mg_create_slab", "mg_field_pointer", "mg_destroy", "mg_last_error", "mg_launch_count", "mg_set_operator", "mg_set_boundary",
-    "mg_set_coarse_solver", "mg_add_smoother", "mg_clear_smoothers", "mg_upload", "mg_download",
+    "mg_set_variable_coefficient", "mg_set_coarse_solver", "mg_add_smoother", "mg_clear_smoothers", "mg_upload", "mg_download",
     "mg_upload_device", "mg_save_initial_guess", "mg_restore_initial_guess", "mg_exec_ops", "mg_enqueue_ops", "mg_set_stream", "mg_build_cycle",
     "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_set_time_limit", "mg_set_outer_operator",
     "mg_solve_bicgstab", "mg_synchronize",
@@ -78,6 +79,7 @@ def _signatures():
         "mg_launch_count": [vp, C.POINTER(C.c_int64)],
         "mg_set_operator": [vp, i32, i32, i32, i32, pi32, pdbl],
         "mg_set_boundary": [vp, i32, dbl],
+        "mg_set_variable_coefficient": [vp, i32, dbl],
         "mg_set_coarse_solver": [vp, i32, i32, dbl],
         "mg_add_smoother": [vp, i32, i32, i32, pi32, i32, pi32, pi32, i32, C.POINTER(C.c_uint32), pdbl, pint],
         "mg_clear_smoothers": [vp],
@@ -236,6 +238,7 @@ class Workspace:
             self._check(self.lib.mg_create(C.byref(self._h), dimension, min_level, max_level, n_fields, code, device))
         self._smoother_cache: Dict[tuple, int] = {}
         self._operators: Dict[int, list] = {}
+        self._variable = None
 
     # -- plumbing ------------------------------------------------------------------------
     def _check(self, rc):
@@ -293,6 +296,21 @@ class Workspace:
         self._check(self.lib.mg_set_boundary(
             self._h, MG_BC_HELMHOLTZ_ROBIN if kind == "helmholtz_robin" else MG_BC_DIRICHLET, float(k)))
 
+    def set_variable_coefficient(self, spec):
+        """`spec` = {"kind": "exp_kappa", "kappa": 10.0} (problems.ProblemSpec.variable_coefficient) or None:
+        the operator of every level becomes -div(c grad u) with c evaluated per node on the device."""
+        spec = dict(spec) if spec else None
+        if spec == self._variable:
+            return
+        if spec is None:
+            self._check(self.lib.mg_set_variable_coefficient(self._h, MG_VC_NONE, 0.0))
+        else:
+            if spec.get("kind") != "exp_kappa":
+                raise EngineError(f"unknown variable coefficient {spec!r}")
+            self.clear_programs(smoothers=True)
+            self._check(self.lib.mg_set_variable_coefficient(self._h, MG_VC_EXP_KAPPA, float(spec["kappa"])))
+        self._variable = spec
+
     def set_coarse_solver(self, kind: str, max_iterations: int, reduction: float):
         self._check(self.lib.mg_set_coarse_solver(
             self._h, MG_CGS_CG if kind == "CG" else MG_CGS_BICGSTAB, int(max_iterations), float(reduction)))
@@ -301,8 +319,15 @@ class Workspace:
         key = (stmt.key(), stmt.matrix)
         if key in self._smoother_cache:
             return self._smoother_cache[key]
-        masks, w = smoother_tables(stmt, self.dimension, self.np_dtype)
         m = len(stmt.slots)
+        if self._variable:
+            # the centre value depends on the node: the table holds omega alone and the kernels divide by
+            # the node's a00 (mg_set_variable_coefficient)
+            if m != 1 or any(p != 1 for p in stmt.period):
+                raise EngineError("block smoothers are not available for variable-coefficient operators")
+            masks, w = np.array([1], dtype=np.uint32), np.array([[[stmt.omega]]], dtype=self.np_dtype)
+        else:
+            masks, w = smoother_tables(stmt, self.dimension, self.np_dtype)
         period = (C.c_int32 * 3)(*(list(stmt.period) + [1] * (3 - len(stmt.period))))
         slot_field = (C.c_int32 * m)(*[f for f, _ in stmt.slots])
         slot_pos = (C.c_int32 * (m * self.dimension))(*[c for _, pos in stmt.slots for c in pos])

@@ -306,6 +306,7 @@ class B200ProgramGenerator:
         merged.update(params)
         for level in range(ws.min_level, ws.max_level + 1):
             ws.set_operator(level, lowering.operator_table(p.system_operator(level, 0, merged)))
+        ws.set_variable_coefficient(p.variable_coefficient_spec(merged))
         ws.set_boundary(p.boundary, merged.get("k", 0.0))
         ws.set_coarse_solver(p.solver.cgs, p.solver.cgs_max_iterations, p.solver.cgs_target_reduction)
 

@@ -60,10 +60,24 @@ class ProblemSpec:
     restriction_names: Optional[List[str]] = None
     prolongation_names: Optional[List[str]] = None
     solver_iteration_limit: Optional[int] = 500  # scripts/optimize.py:32
+    # {"kind": "exp_kappa", "kappa": <parameter name or number>}: the operator is -div(c grad u) with the
+    # coefficient of stencils/gallery.py:87-185 evaluated at every node; `entry_terms` then gives the
+    # stencil at the centre of the domain (structure + a representative for the IR, as the reference's
+    # generate_stencil does for one position)
+    variable_coefficient: Optional[Dict] = None
 
     @property
     def n_fields(self):
         return len(self.field_names)
+
+    def variable_coefficient_spec(self, params=None):
+        """-> {"kind", "kappa": float} with the parameter value substituted, or None."""
+        if not self.variable_coefficient:
+            return None
+        p = dict(self.parameters)
+        p.update(params or {})
+        kappa = self.variable_coefficient["kappa"]
+        return {"kind": self.variable_coefficient["kind"], "kappa": float(p[kappa] if isinstance(kappa, str) else kappa)}
 
     # -- numeric helpers ---------------------------------------------------------------
     def spacing(self, level):
@@ -182,6 +196,64 @@ POISSON_3D = ProblemSpec(
 
 
 # ----------------------------------------------------------------------------------------
+# Variable-coefficient Poisson 2D / 3D: -div(c grad u) = f, c = exp(kappa * prod_d (x_d - x_d^2))
+# (stencils/gallery.py:87-185).  The reference ships the stencil generators but no example problem for them;
+# right-hand side and boundary values are those of the manufactured solution u = prod_d sin(pi x_d)
+# (zero on the boundary), so that the discretisation error of the oracle can be checked against it.
+# ----------------------------------------------------------------------------------------
+
+def _varcoef_terms(spacing, params):
+    centre = (0.5,) * len(spacing)
+    return [[[(None, "A", st.variable_poisson(spacing, centre, params["kappa"]))]]]
+
+
+def varcoef_solution(*coords):
+    u = 1.0
+    for x in coords:
+        u = u * np.sin(np.pi * x)
+    return u
+
+
+def _varcoef_rhs(*coords, h=None, kappa=10.0, **_):
+    # f = -div(c grad u) = c * (d pi^2 u - kappa * sum_a (prod_{b != a} (x_b - x_b^2)) (1 - 2 x_a) du/dx_a)
+    d = len(coords)
+    prod = 1.0
+    for x in coords:
+        prod = prod * (x - x * x)
+    c = np.exp(kappa * prod)
+    u = varcoef_solution(*coords)
+    drift = 0.0
+    for a in range(d):
+        others = 1.0
+        du = np.pi * np.cos(np.pi * coords[a])
+        for b in range(d):
+            if b != a:
+                others = others * (coords[b] - coords[b] * coords[b])
+                du = du * np.sin(np.pi * coords[b])
+        drift = drift + others * (1.0 - 2.0 * coords[a]) * du
+    return [c * (d * np.pi ** 2 * u - kappa * drift)]
+
+
+def _varcoef_bc(*coords, h=None, **_):
+    return [np.zeros(np.broadcast(*coords).shape)]
+
+
+POISSON_2D_VARIABLE = ProblemSpec(
+    name="2D_FD_Poisson_VariableCoefficients", dimension=2, field_names=["u"], rhs_names=["RHS_u"],
+    equation_names=["solEq"], min_level=2, max_level=9, dtype="f64",
+    entry_terms=_varcoef_terms, rhs_function=_varcoef_rhs, boundary_function=_varcoef_bc,
+    solver=SolverDefaults(damping=1.15), parameters={"kappa": 10.0},
+    variable_coefficient={"kind": "exp_kappa", "kappa": "kappa"})
+
+POISSON_3D_VARIABLE = ProblemSpec(
+    name="3D_FD_Poisson_VariableCoefficients", dimension=3, field_names=["u"], rhs_names=["RHS_u"],
+    equation_names=["solEq"], min_level=2, max_level=6, dtype="f64",
+    entry_terms=_varcoef_terms, rhs_function=_varcoef_rhs, boundary_function=_varcoef_bc,
+    solver=SolverDefaults(damping=1.25), parameters={"kappa": 10.0},
+    variable_coefficient={"kind": "exp_kappa", "kappa": "kappa"})
+
+
+# ----------------------------------------------------------------------------------------
 # Nonlinear FAS example: -Laplace(u) + gam u e^u = f   (example_problems/FAS_2D_Basic)
 # ----------------------------------------------------------------------------------------
 
@@ -277,7 +349,8 @@ HELMHOLTZ_2D = ProblemSpec(
     solver_iteration_limit=10000)
 
 
-REGISTRY = {p.name: p for p in (POISSON_2D, POISSON_3D, LINEAR_ELASTICITY_2D, HELMHOLTZ_2D, FAS_2D_BASIC)}
+REGISTRY = {p.name: p for p in (POISSON_2D, POISSON_3D, LINEAR_ELASTICITY_2D, HELMHOLTZ_2D, FAS_2D_BASIC,
+                                POISSON_2D_VARIABLE, POISSON_3D_VARIABLE)}
 
 
 def get_problem(name: str) -> ProblemSpec:

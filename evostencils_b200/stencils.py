@@ -247,6 +247,46 @@ def variable_coefficient_kappa(*pos: float) -> float:
     return math.exp(10.0 * p)
 
 
+def variable_coefficient_exp(kappa: float, *pos: float) -> float:
+    """get_coefficient_2D / get_coefficient_3D (gallery.py:87-90, 137-140) for any kappa:
+    exp(kappa * ((x - x*x) * (y - y*y) [* (z - z*z)])), products grouped left to right."""
+    p = None
+    for x in pos:
+        t = x - (x * x)
+        p = t if p is None else p * t
+    return math.exp(kappa * p)
+
+
+def variable_poisson(spacing: Sequence[float], position: Sequence[float], kappa: float = 10.0) -> Stencil:
+    """Stencil of -div(c grad u) at `position`: Poisson2DVariableCoefficients.generate_stencil /
+    Poisson3DVariableCoefficients.generate_stencil (gallery.py:93-111, 143-161): c at the half-grid
+    positions, off-centre value (-1.0 * c) / (h*h), centre = sum over the axes of (c+ + c-) / (h*h),
+    accumulated axis by axis.  The reference evaluates this at ONE position (for its convergence
+    model); the generated solver evaluates it at every node (`Operator A from Stencil`, :113-131), which
+    is what the engine does (csrc/mg_kernels_generic.cuh vc_apply)."""
+    d = len(spacing)
+    assert len(position) == d
+
+    def face(axis, sign):
+        q = list(position)
+        q[axis] = q[axis] + sign * (0.5 * spacing[axis])
+        return variable_coefficient_exp(kappa, *q)
+
+    centre = None
+    entries = []
+    for axis in range(d):
+        hh = spacing[axis] * spacing[axis]
+        cp, cm = face(axis, +1), face(axis, -1)
+        term = (cp + cm) / hh
+        centre = term if centre is None else centre + term
+        for sign, c in ((+1, cp), (-1, cm)):
+            off = [0] * d
+            off[axis] = sign
+            entries.append((tuple(off), (-1.0 * c) / hh))
+    entries.append(((0,) * d, centre))
+    return Stencil(entries, d)
+
+
 def full_weighting(dimension: int) -> Stencil:
     """Full-weighting restriction, tensor product of [1/4, 1/2, 1/4]; the coarse node I
     gathers from fine nodes 2I+o (reference DSL form `[i] from [2*i + o]`,

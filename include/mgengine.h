@@ -57,6 +57,13 @@ typedef enum {
 
 typedef enum { MG_CGS_CG = 0, MG_CGS_BICGSTAB = 1 } mg_cgs_kind;
 
+/* variable-coefficient operators (stencils/gallery.py:87-185) */
+typedef enum {
+    MG_VC_NONE = 0,
+    MG_VC_EXP_KAPPA = 1         /* -div(c grad u), c(x) = exp(kappa * prod_d (x_d - x_d^2)) on the unit square / cube
+                                   (get_coefficient_2D :87-90, get_coefficient_3D :137-140) */
+} mg_vc_kind;
+
 /* op kinds: the statement vocabulary generate_multigrid emits (exastencils.py:684-925) */
 typedef enum {
     MG_OP_SMOOTH = 0,             /* solve locally ... relax w         (:769-822)  */
@@ -98,6 +105,16 @@ int mg_launch_count(mg_workspace* ws, int64_t* out);
  * = x; values[n] (or [n][2] for MG_C128), in the accumulation order to be used. */
 int mg_set_operator(mg_workspace* ws, int level, int row, int col, int n_entries,
                     const int32_t* offsets, const double* values);
+/* Variable-coefficient Poisson operator on every level of a scalar MG_F64 workspace: replaces the
+ * `Operator A from Stencil` text of Poisson2DVariableCoefficients / Poisson3DVariableCoefficients.generate_exa3
+ * (stencils/gallery.py:113-131, :163-185) and the getCoefficient calls ExaStencils expands from it.  The
+ * kernels evaluate the coefficient at the half-grid positions around each node (nothing is stored: 24 B/DoF
+ * per sweep as for constant coefficients): off-centre value (-1.0 * c_face) / (h*h), centre
+ * ((cE + cW)/(h*h)) + ((cN + cS)/(h*h)) [+ ((cT + cB)/(h*h))].  Values passed to mg_set_operator are then
+ * ignored (its offsets must be the (2d+1)-point star in memory order; set here when absent).  Point
+ * smoothers only (Jacobi / red-black): their W table holds omega alone (1 slot, 1 mask) and the kernels
+ * divide by the node's centre value.  kind = MG_VC_NONE restores constant stencils. */
+int mg_set_variable_coefficient(mg_workspace* ws, int kind, double kappa);
 int mg_set_boundary(mg_workspace* ws, int bc_kind, double k);
 int mg_set_coarse_solver(mg_workspace* ws, int kind, int max_iterations, double reduction);
 

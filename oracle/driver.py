@@ -22,6 +22,13 @@ def make_hierarchy(problem, min_level, max_level, operators=None, params=None, e
     for level in range(lo, max_level + 1):
         table = lowering.operator_table(problem.system_operator(level, 0, p))
         h.operators[level] = table
+    vc = problem.variable_coefficient_spec(p)
+    if vc:
+        # the IR carries the stencil at one position; the solver evaluates it at every node
+        for level in range(lo, max_level + 1):
+            h.operators[level] = mo.variable_poisson_table(problem.dimension, level, vc["kappa"])
+            h.variable_levels.add(level)
+        return h
     if operators:
         for level, table in operators.items():
             assert h.operators[level] == table, f"program operator on level {level} differs from the problem's"

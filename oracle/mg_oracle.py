@@ -228,6 +228,7 @@ class Hierarchy:
             # correction field aliases the solution field below the finest level
             self.cor[level] = self.sol[level] if level < max_level else [np.zeros(shape, dtype) for _ in range(n_fields)]
         self.operators: Dict[int, list] = {}
+        self.variable_levels = set()          # levels whose table holds value arrays (variable_poisson_table)
         self._colour_masks: Dict[int, List[np.ndarray]] = {}
 
     def field(self, kind, level):
@@ -266,6 +267,54 @@ def apply_operator(table, fields: List[np.ndarray], row: int):
     if acc is None:
         acc = np.zeros_like(_interior(fields[0]))
     return acc
+
+
+def variable_poisson_table(dimension: int, level: int, kappa: float):
+    """Operator table of -div(c grad u), c = exp(kappa * prod_d (x_d - x_d^2)), with one VALUE ARRAY
+    (interior nodes) per stencil offset -- `Operator A from Stencil` of
+    Poisson2DVariableCoefficients / Poisson3DVariableCoefficients.generate_exa3
+    (stencils/gallery.py:113-131, 163-185), evaluated at every node as the generated solver does:
+    getCoefficient at nodePosition +- 0.5 * gridWidth (:87-90, 137-140), off-centre value
+    (-1.0 * c) / (h * h), centre ((cE + cW) / hh) + ((cN + cS) / hh) [+ ((cT + cB) / hh)].
+    Entries in memory order of the offsets, like every other table."""
+    n = 2 ** level + 1
+    hw = 1.0 / 2 ** level
+    hh = hw * hw
+    pos = np.arange(1, n - 1, dtype=np.float64) * hw                     # interior node positions, exact
+    shape = [1] * dimension
+
+    def axis_array(values, x_axis):                                      # x_axis 0 = x = last array axis
+        sh = list(shape)
+        sh[dimension - 1 - x_axis] = values.size
+        return values.reshape(sh)
+
+    def coefficient(shift_axis, sign):
+        prod = None
+        for a in range(dimension):                                       # x, y[, z]: the reference's grouping
+            p = pos + sign * (0.5 * hw) if a == shift_axis else pos
+            t = axis_array(p - (p * p), a)
+            prod = t if prod is None else prod * t
+        full = np.broadcast_to(prod, (n - 2,) * dimension)
+        return np.exp(kappa * full)
+
+    faces = {}
+    centre = None
+    for a in range(dimension):
+        cp, cm = coefficient(a, +1), coefficient(a, -1)
+        faces[(a, +1)], faces[(a, -1)] = cp, cm
+        term = (cp + cm) / hh
+        centre = term if centre is None else centre + term
+    entries = []
+    for a in reversed(range(dimension)):                                 # memory order: slowest axis first
+        off = [0] * dimension
+        off[a] = -1
+        entries.append((tuple(off), (-1.0 * faces[(a, -1)]) / hh))
+    entries.append(((0,) * dimension, centre))
+    for a in range(dimension):
+        off = [0] * dimension
+        off[a] = +1
+        entries.append((tuple(off), (-1.0 * faces[(a, +1)]) / hh))
+    return [[entries]]
 
 
 def residual_interior(h: Hierarchy, level, row, sol=None):
@@ -355,15 +404,21 @@ def op_local_solve(h: Hierarchy, stmt):
     period = tuple(stmt.period)
     slots = list(stmt.slots)
     m = len(slots)
-    if all(p == 1 for p in period):
+    if level in h.variable_levels:
+        # variable-coefficient operator: the local 1x1 system has the node's own centre value
+        assert m == 1 and all(p == 1 for p in period), "point smoothers only on variable-coefficient operators"
+        diag = [v for off, v in h.operators[level][0][0] if not any(off)][0]
+        W = [[stmt.omega / diag]]
+    elif all(p == 1 for p in period):
         W = inverse_block(matrix, stmt.omega)
+    if all(p == 1 for p in period):
         colours = (0, 1) if stmt.colored else (None,)
         for colour in colours:
             r = [residual_interior(h, level, f) for f, _ in slots]
             for s, (f, _) in enumerate(slots):
                 delta = None
                 for t in range(m):
-                    term = mul(W[s, t], r[t])
+                    term = mul(W[s][t], r[t])
                     delta = term if delta is None else delta + term
                 target = _interior(sol[f])
                 if colour is None:
