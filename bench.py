@@ -22,6 +22,7 @@ The line also carries
                 halo exchange (N = 1: the single-domain engine);
   small_configs configs[0], [3], [4] (513^2 reference solver, Helmholtz 3..7 k = 80, elasticity
                 4..8): ms per solve and evaluations/s on the GPU, the CPU figure beside each;
+  variable_coefficient  2D variable-coefficient Poisson at the same size: stage rooflines and one solve;
   evals_per_s, clocks, gpu_launches.
 `--impl reference` times the CPU port of the reference path instead (rank 0 only), on the same
 `config`, one cycle of each of the same individuals per step.
@@ -416,6 +417,7 @@ def run_b200(args):
         extras["dd3d"] = dd3d_leg(args, rank, world, local, peak)
         if rank == 0:
             extras["small_configs"] = small_config_records(local)
+            extras["variable_coefficient"] = variable_coefficient_record(local, peak, args.max_level)
     if rank != 0:
         finish(dist, rank, world)
         return
@@ -645,6 +647,47 @@ def small_config_records(device):
     except Exception as exc:
         out["elasticity"] = {"error": "%s: %s" % (type(exc).__name__, exc)}
     return out
+
+
+def variable_coefficient_record(device, peak, level=12):
+    """north_star's "variable stencils": -div(c grad u), c = exp(10 (x - x^2)(y - y^2)) (stencils/gallery.py:87-131)
+    at the size of configs[1].  Stage kernels timed like `stage_rooflines` (24 B/DoF: the coefficients are
+    recomputed per node, nothing but u and f is read; a red-black sweep is two in-place colour passes = 48
+    B/DoF moved for 24 algorithmic), and one V(2,1) solve through the generator."""
+    from evostencils_b200 import ir, lowering, problems
+    from evostencils_b200.generator import B200ProgramGenerator
+    from evostencils_b200.grammar import Grammar, v_cycle_string
+    try:
+        problem, lo, hi = problems.POISSON_2D_VARIABLE, 2, level
+        gen = B200ProgramGenerator(problem=problem, min_level=lo, max_level=hi, device=device)
+        gen.initialize_code_generation(lo, hi)
+        expression, _ = Grammar(problem, lo, hi).compile(v_cycle_string(hi - lo, 2, 1, 21, "red_black"))
+        storages = gen.generate_storage(lo, hi, gen.finest_grid)
+        us, fs = synthetic_inputs(problem, hi)          # as the main leg: u0 = 0, f ~ N(0, 1)
+        gen.set_inputs(rhs=fs, u0=us)
+        gen.generate_and_evaluate(expression, storages, lo, hi, "", evaluation_samples=1)       # warm-up
+        t, rho, n = gen.generate_and_evaluate(expression, storages, lo, hi, "", evaluation_samples=1)
+        ws = gen._workspace
+        op = problem.system_operator(hi, 0)
+        dof = float((2 ** hi - 1) ** 2)
+        stages = {
+            "jacobi": lowering.local_solve_statements(ir.ElementwiseDiagonal(op), op, hi, 0.8, ir.Single),
+            "rbgs": lowering.local_solve_statements(ir.ElementwiseDiagonal(op), op, hi, 1.15, ir.RedBlack),
+            "residual": [lowering.Op("residual", hi, dst="res")],
+        }
+        rec = {}
+        for name, ops in stages.items():
+            ws.time_ops(ops, 3)
+            ws.flush_l2()
+            ms = ws.time_ops(ops, 20) / 20
+            gbs = 24.0 * dof / (ms * 1e-3) / 1e9
+            rec[name] = {"ms": ms, "achieved_gbs": gbs, "frac": gbs / peak, "bytes": 24.0 * dof}
+        gen.close()
+        return {"workload": "2D variable-coefficient Poisson %d^2 fp64, kappa = 10, levels %d..%d" % (2 ** hi, lo, hi),
+                "stages": rec, "solve": {"cycle": "V(2,1) RB-GS w=1.15", "ms": t, "iterations": n, "convergence_factor": rho,
+                                         "value": dof * n / (t * 1e-3) if n < 1e99 else None, "unit": UNIT}}
+    except Exception as exc:
+        return {"error": "%s: %s" % (type(exc).__name__, exc)}
 
 
 def run_stages(args):

@@ -12,6 +12,7 @@
 #include "mg_fast3d.cuh"
 #include "mg_rbgs3d.cuh"
 #include "mg_restrict3d.cuh"
+#include "mg_varcoef.cuh"
 #include "mg_workspace.cuh"
 
 namespace mg {
@@ -75,6 +76,27 @@ inline void launch_star2d(mg_workspace* ws, Level& lv, int r, const double* u, c
 }
 
 inline int valid_rows(int r, int dflt) { return (r == 2 || r == 4 || r == 8) ? r : dflt; }
+
+// ---- 2D variable-coefficient Poisson (mg_varcoef.cuh): levels whose columns tile into strips -----------
+template <int D>
+inline bool vc_level_ok(const mg_workspace* ws, const Level& lv) {
+    static const int enabled = tunable("MG_FAST_VC", 1);
+    return enabled && D == 2 && ws->vc_kind == MG_VC_EXP_KAPPA && ws->dtype == MG_F64 && ws->n_fields == 1 &&
+           (lv.g.n - 1) % (2 * FAST_NT) == 0;
+}
+
+template <int MODE>
+inline dim3 launch_vcstar2d(mg_workspace* ws, Level& lv, int r, const double* u, const double* f, double* out, double w,
+                            int colour, double* partial) {
+    VC2D s;
+    s.kappa = ws->vc_kappa;
+    s.h = 1.0 / (double)(lv.g.n - 1);
+    s.ihh = (double)(lv.g.n - 1) * (double)(lv.g.n - 1);
+    dim3 grid = strip_grid(lv, 2, r, lv.g.n - 2);
+    if (r == 4) launch_k(ws, k_vcstar2d<MODE, FAST_NT, 4>, grid, FAST_NT, 0, lv.g, s, u, f, out, w, colour, partial);
+    else launch_k(ws, k_vcstar2d<MODE, FAST_NT, 2>, grid, FAST_NT, 0, lv.g, s, u, f, out, w, colour, partial);
+    return grid;
+}
 
 // block-Jacobi tiles (px x py <= 4 unknowns) on a scalar star stencil: any level size
 template <typename T, int D, int F>
@@ -294,6 +316,26 @@ inline bool fast_smooth(mg_workspace* ws, Level& lv, Smoother& sm, int c_begin, 
         return true;
     }
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
+        if (ws->vc_kind) {
+            if (zero_in || !vc_level_ok<D>(ws, lv) || !sm.point || sm.m != 1) return false;
+            static const int rows_vc = tunable("MG_VC_ROWS", 0);
+            const int r = (rows_vc == 2 || rows_vc == 4) ? rows_vc : imin_h(4, pick_rows(lv, 2));
+            const double* rhs = static_cast<const double*>(lv.rhs[0]);
+            if (sm.colored) {
+                // two colour passes, each in place on the current buffer (no flip)
+                double* cur = static_cast<double*>(lv.sol[lv.cur[0]][0]);
+                for (int c = c_begin; c < c_end; ++c) {
+                    launch_vcstar2d<STAR_JACOBI>(ws, lv, r, cur, rhs, cur, sm.w00, c, nullptr);
+                    fast_count(ws);
+                }
+            } else {
+                launch_vcstar2d<STAR_JACOBI>(ws, lv, r, static_cast<const double*>(lv.sol[lv.cur[0]][0]), rhs,
+                                             static_cast<double*>(lv.sol[lv.cur[0] ^ 1][0]), sm.w00, -1, nullptr);
+                lv.cur[0] ^= 1;
+                fast_count(ws);
+            }
+            return true;
+        }
         if (sm.colored && !(c_begin == 0 && c_end == 2)) return false;        // single colour passes: generic kernel
         if (!star_level_ok<D>(ws, lv, 2) || !sm.point || sm.m != 1) return false;
         static const int rows_j = tunable("MG_JACOBI_ROWS", 0), rows_rb = tunable("MG_RBGS_ROWS", 0);
@@ -333,6 +375,13 @@ inline bool fast_residual(mg_workspace* ws, Level& lv) {
         return true;
     }
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
+        if (ws->vc_kind) {
+            if (!vc_level_ok<D>(ws, lv)) return false;
+            launch_vcstar2d<STAR_RESIDUAL>(ws, lv, imin_h(4, pick_rows(lv, 2)), static_cast<const double*>(lv.sol[lv.cur[0]][0]),
+                                           static_cast<const double*>(lv.rhs[0]), static_cast<double*>(lv.res[0]), 0.0, -1, nullptr);
+            fast_count(ws);
+            return true;
+        }
         if (!star_level_ok<D>(ws, lv, 2)) return false;
         static const int rows = tunable("MG_RESIDUAL_ROWS", 0);
         launch_star2d<STAR_RESIDUAL>(ws, lv, valid_rows(rows, pick_rows(lv, 2)),
@@ -357,6 +406,17 @@ inline bool fast_norm(mg_workspace* ws, Level& lv) {
         return true;
     }
     if constexpr (D == 2 && F == 1 && sizeof(T) == sizeof(double)) {
+        if (ws->vc_kind) {
+            if (!vc_level_ok<D>(ws, lv)) return false;
+            const int r = imin_h(4, pick_rows(lv, 2, MAX_PARTIALS));
+            dim3 grid = strip_grid(lv, 2, r, lv.g.n - 2);
+            if ((int)(grid.x * grid.y) > MAX_PARTIALS) return false;
+            launch_vcstar2d<STAR_NORM>(ws, lv, r, static_cast<const double*>(lv.sol[lv.cur[0]][0]),
+                                       static_cast<const double*>(lv.rhs[0]), nullptr, 0.0, -1, static_cast<double*>(lv.partial));
+            lv.norm_count = grid.x * grid.y;
+            fast_count(ws);
+            return true;
+        }
         if (!star_level_ok<D>(ws, lv, 2)) return false;
         static const int rows = tunable("MG_NORM_ROWS", 0);
         const int r = valid_rows(rows, pick_rows(lv, 2, MAX_PARTIALS));

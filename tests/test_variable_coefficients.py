@@ -203,6 +203,30 @@ def test_stages_match_the_oracle(dimension, lo, hi, fast):
 
 
 @pytest.mark.gpu
+def test_specialised_kernel_at_2049_squared():
+    """k_vcstar2d with four rows per band (levels >= 10) against the oracle and against the generic kernels."""
+    from oracle import driver, mg_oracle
+    problem = PROBLEMS[2]
+    hi = 11
+    ws, h = _pair(problem, hi - 1, hi, seed=11)
+    settings = driver.settings_for(problem)
+    jac, rb = _stage_ops(problem, hi)
+    for ops, kind, what in (([lowering.Op("residual", hi, dst="res")], "res", "residual"), ([jac], "sol", "jacobi"),
+                            ([rb], "sol", "red-black")):
+        ws.exec_ops(ops)
+        mg_oracle.run_ops(h, ops, settings)
+        _close(ws, h, kind, hi, what)
+    fast = ws.download("sol", hi, 0)
+    norm_fast = ws.residual_norm(hi)
+    assert abs(norm_fast - mg_oracle.residual_norm(h, hi)) <= 1e-12 * norm_fast
+    ws.close()
+    ws, h = _pair(problem, hi - 1, hi, seed=11, fast=False)
+    ws.exec_ops([jac, rb])
+    assert np.array_equal(ws.download("sol", hi, 0), fast), "specialised and generic kernels: same operands, same order"
+    ws.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("dimension", [2, 3])
 def test_coarse_cg_matches_the_oracle(dimension):
     from oracle import driver, mg_oracle
