@@ -193,6 +193,7 @@ extern "C" int mg_destroy(mg_workspace* ws) {
     }
     dd_release(ws);
     if (ws->cgs_work) cudaFree(ws->cgs_work);
+    if (ws->krylov_work) cudaFree(ws->krylov_work);
     for (void* p : ws->fas_raw) cudaFree(p);
     delete ws->tail;
     if (ws->tail_pool) cudaFree(ws->tail_pool);

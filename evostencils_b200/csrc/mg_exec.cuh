@@ -391,6 +391,56 @@ int exec_cgs(mg_workspace* ws, int level) {
     return MG_OK;
 }
 
+// sol += e on interior nodes
+template <typename T, int D, int F>
+__global__ void k_add_interior(Geom g, FieldSet<T> sol, FieldSet<T> e) {
+    pdl_sync();
+    int x, y, z;
+    if (!node_coords<D>(g, x, y, z) || !is_interior<D>(g, x, y, z)) return;
+    const long long idx = node_index<D>(g, x, y, z);
+#pragma unroll
+    for (int i = 0; i < F; ++i) sol.p[i][idx] = t_add(sol.p[i][idx], e.p[i][idx]);
+}
+
+// Krylov method as a smoother (MG_OP_KRYLOV, include/mgengine.h): the residual equation is solved from a
+// zero guess into the idle solution buffers by the coarse-grid solver's kernel, then added
+template <typename T, int D, int F>
+int exec_krylov(mg_workspace* ws, const mg_op& op) {
+    if (ws->slab) return fail(MG_ERR_INVALID, "Krylov smoothers run on whole grids, not on a z-slab");
+    if (op.src != MG_CGS_CG && op.src != MG_CGS_BICGSTAB) return fail(MG_ERR_INVALID, "bad Krylov method");
+    const int n_its = (int)op.omega;
+    if (n_its < 1) return fail(MG_ERR_INVALID, "Krylov smoother without iterations");
+    Level& lv = ws->L(op.level);
+    int rc = materialise_zero<T>(ws, lv);
+    if (rc) return rc;
+    rc = exec_residual<T, D, F>(ws, op.level);
+    if (rc) return rc;
+    const OperatorTable<T>* tab = static_cast<const OperatorTable<T>*>(lv.d_op);
+    FieldSet<T> scratch;
+    for (int i = 0; i < MG_MAX_FIELDS; ++i) {
+        const int f = lv.sol[0][i] ? i : 0;
+        scratch.p[i] = static_cast<T*>(lv.sol[lv.cur[f] ^ 1][f]);
+    }
+    FieldSet<T> res = fieldset<T>(lv.res);
+    const size_t bytes = (size_t)(op.src == MG_CGS_CG ? 4 : 7) * F * lv.g.total * sizeof(T);
+    const bool smem = bytes <= 200 * 1024;
+    if (!smem && ws->krylov_work_bytes < bytes) return fail(MG_ERR_STATE, "Krylov scratch not allocated");
+    T* gwork = static_cast<T*>(ws->krylov_work);
+    const double h = 1.0 / (double)(lv.g.n - 1);
+    const cplx bcf = t_div(make_cplx(1.0, 0.0), make_cplx(1.0, -ws->bc_k * h));
+    const int robin = ws->bc_kind == MG_BC_HELMHOLTZ_ROBIN ? 1 : 0;
+    if (op.src == MG_CGS_CG) {
+        if (smem) launch_k(ws, k_coarse_cg<T, D, F, true>, 1, 256, bytes, lv.g, tab, scratch, res, nullptr, n_its, ws->cgs_reduction);
+        else launch_k(ws, k_coarse_cg<T, D, F, false>, 1, 256, 0, lv.g, tab, scratch, res, gwork, n_its, ws->cgs_reduction);
+    } else {
+        if (smem) launch_k(ws, k_coarse_bicgstab<T, D, F, true>, 1, 256, bytes, lv.g, tab, scratch, res, nullptr, n_its, ws->cgs_reduction, robin, bcf);
+        else launch_k(ws, k_coarse_bicgstab<T, D, F, false>, 1, 256, 0, lv.g, tab, scratch, res, gwork, n_its, ws->cgs_reduction, robin, bcf);
+    }
+    launch_k(ws, k_add_interior<T, D, F>, node_grid<D>(lv.g), 128, 0, lv.g, cur_sol<T>(lv), scratch);
+    count(ws, 2);
+    return apply_bc<T>(ws, lv);
+}
+
 template <typename T, int D, int F>
 int exec_norm(mg_workspace* ws, int level, int squares = 0) {
     Level& lv = ws->L(level);
@@ -663,6 +713,7 @@ int exec_op(mg_workspace* ws, const mg_op& op) {
         case MG_OP_PROLONG_ADD: return exec_prolong<T, D, F>(ws, op, true);
         case MG_OP_PROLONG: return exec_prolong<T, D, F>(ws, op, false);
         case MG_OP_CGS: return exec_cgs<T, D, F>(ws, op.level);
+        case MG_OP_KRYLOV: return exec_krylov<T, D, F>(ws, op);
         default: return fail(MG_ERR_INVALID, "unknown op kind");
     }
 }

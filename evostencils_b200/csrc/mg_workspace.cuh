@@ -113,6 +113,8 @@ struct mg_workspace {
     double cgs_reduction = 1e-12;
     void* cgs_work = nullptr;                   // global scratch when the coarse level exceeds smem
     size_t cgs_work_bytes = 0;
+    void* krylov_work = nullptr;                // global scratch of the Krylov smoother ops (MG_OP_KRYLOV)
+    size_t krylov_work_bytes = 0;
     double* d_norm = nullptr;                   // device scalar
     double* h_norm = nullptr;                   // pinned host scalar
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, mark[2] = {nullptr, nullptr};

@@ -25,7 +25,8 @@ MG_BC_DIRICHLET, MG_BC_HELMHOLTZ_ROBIN = 0, 1
 MG_CGS_CG, MG_CGS_BICGSTAB = 0, 1
 MG_VC_NONE, MG_VC_EXP_KAPPA = 0, 1
 (MG_OP_SMOOTH, MG_OP_RESIDUAL, MG_OP_RESTRICT, MG_OP_RESIDUAL_RESTRICT, MG_OP_ZERO, MG_OP_PROLONG_ADD,
- MG_OP_PROLONG, MG_OP_CGS) = range(8)
+ MG_OP_PROLONG, MG_OP_CGS, MG_OP_KRYLOV) = range(9)
+MG_KRYLOV_METHOD = {"ConjugateGradient": 0, "BiCGStab": 1}
 
 _FIELD = {"sol": MG_SOL, "rhs": MG_RHS, "res": MG_RES, "cor": MG_COR, "": MG_SOL}
 
@@ -377,6 +378,10 @@ class Workspace:
                     add(MG_OP_PROLONG_ADD, op.level, op.omega, _FIELD[op.src or "sol"])
                 elif k == "prolong":
                     add(MG_OP_PROLONG, op.level, 1.0, _FIELD[op.src or "sol"])
+                elif k == "krylov":
+                    if op.method not in MG_KRYLOV_METHOD:
+                        raise EngineError(f"Krylov subspace method '{op.method}' is not executable")
+                    add(MG_OP_KRYLOV, op.level, float(op.iterations), MG_KRYLOV_METHOD[op.method])
                 elif k == "cgs":
                     if op.level == self.min_level:
                         add(MG_OP_CGS, op.level)

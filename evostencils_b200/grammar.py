@@ -56,12 +56,18 @@ class Grammar:
     def __init__(self, problem: ProblemSpec, min_level: int, max_level: int,
                  maximum_local_system_size: int = 8, relaxation_factor_samples: int = 37,
                  enable_partitioning: bool = True, parameters: Optional[Dict] = None,
-                 coarse_grid_solver_expression=None, FAS: bool = False):
+                 coarse_grid_solver_expression=None, FAS: bool = False,
+                 krylov_methods: tuple = (), krylov_iterations: tuple = (2, 4, 8)):
         """`FAS` selects the productions of the full approximation scheme (multigrid.py:275-299,
         323-341, 360-375): Jacobi-Picard / Jacobi-Newton smoothers, the restricted fine solution
-        carried into the coarse right-hand side and subtracted again before the prolongation."""
+        carried into the coarse right-hand side and subtracted again before the prolongation.
+        `krylov_methods` (off by default: the reference's grammar has no production for them) adds
+        `<method>_{d}(iterations, C_d) -> S_d` productions that put a KrylovSubspaceMethod
+        (ir/krylov_subspace.py:4-45) in the place of a smoother: names from
+        {"conjugate_gradient", "bicgstab", "minres", "conjugate_residual"}."""
         depth = max_level - min_level
         assert depth >= 1, "The maximum number of levels must be greater zero"
+        self.krylov_methods = tuple(krylov_methods)
         self.problem = problem
         self.min_level = min_level
         self.max_level = max_level
@@ -89,6 +95,9 @@ class Grammar:
             self._term("red_black", "Partitioning", ir.RedBlack)
         for i in range(relaxation_factor_samples):
             self._term(repr(i), "RelaxationFactorIndex", i, named=False)
+        if self.krylov_methods:
+            for k in krylov_iterations:
+                self._term(f"its_{k}", "KrylovIterations", int(k))
         if not FAS:
             self._add_block_shapes(nf, dim, maximum_local_system_size)
         else:
@@ -226,7 +235,18 @@ class Grammar:
             for i, o in zip(ins, outs):
                 self._prim(name, fixed + [i], o, fn)
 
+        def krylov(make):
+            def production(number_of_iterations, cycle):
+                assert isinstance(cycle.correction, ir.Residual), "Invalid production: expected residual"
+                cycle.correction = ir.Multiplication(make(cycle.correction.operator, number_of_iterations), cycle.correction)
+                return update(len(relax) // 2, ir.Single, cycle)       # the relaxation factor is not applied (exastencils.py:758-768)
+            return production
+
         both(f"residual_{d}", residual, [], [S, Sg], [C, Cg])
+        makers = {"conjugate_gradient": ir.generate_conjugate_gradient, "bicgstab": ir.generate_bicgstab,
+                  "minres": ir.generate_minres, "conjugate_residual": ir.generate_conjugate_residual}
+        for method in self.krylov_methods:
+            both(f"{method}_{d}", krylov(makers[method]), ["KrylovIterations"], [C, Cg], [S, Sg])
         if not scalar_equation:
             both(f"decoupled_jacobi_{d}", decoupled_jacobi, ["RelaxationFactorIndex", "Partitioning"], [C, Cg], [S, Sg])
         if not self.FAS:

@@ -355,6 +355,46 @@ def generate_collective_block_jacobi(operator, block_sizes):
 
 
 # partitionings (partitioning.py:18-47); the grammar passes the *classes* around
+class KrylovSubspaceMethod(Expression):
+    """`name` in {ConjugateGradient, BiCGStab, MinRes, ConjugateResidual} applied for a fixed number of
+    iterations in place of a smoother: Cycle.correction = Multiplication(KrylovSubspaceMethod, Residual)
+    (ir/krylov_subspace.py:4-45; emitted at code_generation/exastencils.py:758-768)."""
+
+    def __init__(self, name, operator, number_of_iterations):
+        super().__init__()
+        self.name = name
+        self.operator = operator
+        self.number_of_iterations = number_of_iterations
+        self.shape = getattr(operator, "shape", None)
+
+    @staticmethod
+    def generate_stencil():
+        return None
+
+    @property
+    def grid(self):
+        return self.operator.grid
+
+    def __repr__(self):
+        return f"KrylovSubspaceMethod({self.name!r}, {self.operator!r}, {self.number_of_iterations!r})"
+
+
+def generate_conjugate_gradient(operator, number_of_iterations):
+    return KrylovSubspaceMethod("ConjugateGradient", operator, number_of_iterations)
+
+
+def generate_bicgstab(operator, number_of_iterations):
+    return KrylovSubspaceMethod("BiCGStab", operator, number_of_iterations)
+
+
+def generate_minres(operator, number_of_iterations):
+    return KrylovSubspaceMethod("MinRes", operator, number_of_iterations)
+
+
+def generate_conjugate_residual(operator, number_of_iterations):
+    return KrylovSubspaceMethod("ConjugateResidual", operator, number_of_iterations)
+
+
 class Single:
     @staticmethod
     def get_name():

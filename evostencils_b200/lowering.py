@@ -34,6 +34,11 @@ from . import stencils as st
 SOL, RHS, RES, COR = "sol", "rhs", "res", "cor"
 
 
+# Krylov subspace methods the engine executes as fixed-iteration smoothers (ir/krylov_subspace.py:32-45 also
+# names MinRes and ConjugateResidual; individuals that use them get the sentinel fitness)
+KRYLOV_METHODS = ("ConjugateGradient", "BiCGStab")
+
+
 class LoweringError(RuntimeError):
     """The graph uses a construct the engine (or ExaStencils) cannot execute."""
 
@@ -62,15 +67,17 @@ class LocalSolve:
 
 @dataclass
 class Op:
-    kind: str                         # residual | restrict | prolong_add | prolong | zero | cgs | copy | richardson
+    kind: str                         # residual | restrict | prolong_add | prolong | zero | cgs | copy | richardson | krylov
     level: int                        # level of the field that is written
     omega: float = 1.0
     src: str = ""                     # source field kind
     dst: str = ""                     # destination field kind
     inner: Optional[list] = None      # cgs on a level above the engine's min level: op list of the inner cycle
+    method: str = ""                  # krylov: "ConjugateGradient" | "BiCGStab"
+    iterations: int = 0               # krylov: number of iterations
 
     def key(self):
-        return (self.kind, self.level, self.omega, self.src, self.dst)
+        return (self.kind, self.level, self.omega, self.src, self.dst, self.method, self.iterations)
 
 
 @dataclass
@@ -364,6 +371,18 @@ class _Lowerer:
                     self.ops.extend(local_solve_statements(self.smoothing_operator(op1.operand, level),
                                                            self.system_operator(residual.operator, level), level,
                                                            weight, expression.partitioning))
+                elif _is(op1, "KrylovSubspaceMethod"):
+                    # exastencils.py:744-768: same preamble as a smoother, then `<Name>_<n>@level()`; the
+                    # relaxation factor of the cycle is not applied (the solver updates the solution itself)
+                    residual = op2
+                    self.preamble(residual.rhs, residual.rhs, residual.approximation, expression.approximation)
+                    self.note_operator(residual.operator, level)
+                    if op1.name not in KRYLOV_METHODS:
+                        raise LoweringError(f"Krylov subspace method '{op1.name}' is not executable by the engine")
+                    n = int(op1.number_of_iterations)
+                    if n < 1:
+                        raise LoweringError("Krylov subspace method with no iterations")
+                    self.ops.append(Op("krylov", level, src=RHS, dst=SOL, method=op1.name, iterations=n))
                 else:
                     raise LoweringError("Unsupported operator")
             else:
@@ -508,6 +527,9 @@ def estimate_cycle_bytes(ops: Sequence[object], dimension: int, bytes_per_value:
             if inner:
                 total += estimate_cycle_bytes(inner, dimension, bytes_per_value, default_cycle)
             continue
+        elif op.kind == "krylov":
+            # residual (3) + per CG iteration: A p (2), p.Ap (2), x and r updates (6), r.r (1), p update (3); + x += e (3)
+            fields = 6.0 + (14.0 if op.method == "ConjugateGradient" else 30.0) * op.iterations
         else:
             fields = 3.0
         total += fields * bytes_per_value * float((2 ** fine_level - 1) ** dimension)

@@ -73,15 +73,21 @@ typedef enum {
     MG_OP_ZERO = 4,               /* sol@level = 0                      (:706-709)  */
     MG_OP_PROLONG_ADD = 5,        /* sol@level += w * P * src@(level-1) (:727-743)  */
     MG_OP_PROLONG = 6,            /* cor@level = P * src@(level-1)      (:855-873)  */
-    MG_OP_CGS = 7                 /* coarse-grid solve on min_level     (:874-911)  */
+    MG_OP_CGS = 7,                /* coarse-grid solve on min_level     (:874-911)  */
+    MG_OP_KRYLOV = 8              /* `<Name>_<n>@level()` in the place of a smoother (:758-768;
+                                     ir/krylov_subspace.py:4-45): src = mg_cgs_kind, omega = n.
+                                     res = rhs - A sol; at most n iterations of the coarse-grid solver's
+                                     method on A e = res from e = 0 (early exit at the reduction set by
+                                     mg_set_coarse_solver); sol += e.  One CTA: meant for the small levels */
 } mg_op_kind;
 
 typedef struct {
     int32_t kind;        /* mg_op_kind */
     int32_t level;       /* level of the field that is written */
-    double  omega;       /* relaxation factor (SMOOTH uses the one baked into its W table) */
+    double  omega;       /* relaxation factor (SMOOTH uses the one baked into its W table); KRYLOV: iterations */
     int32_t src;         /* mg_field read by RESTRICT / PROLONG*; SMOOTH with a coloured smoother:
-                            0 = both colour passes, 1 = first colour only, 2 = second colour only */
+                            0 = both colour passes, 1 = first colour only, 2 = second colour only;
+                            KRYLOV: mg_cgs_kind */
     int32_t smoother;    /* SMOOTH: handle returned by mg_add_smoother */
 } mg_op;
 

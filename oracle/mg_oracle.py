@@ -490,13 +490,15 @@ def _scatter_interior(arrays, flat):
         k += it.size
 
 
-def op_coarse_cg(h: Hierarchy, level, max_its=1000, reduction=1e-12):
-    """Plain CG from a zero guess, stop at ||r|| <= reduction * ||r0|| (Poisson/2D...exa3:12-14)."""
-    x = h.sol[level]
+def op_coarse_cg(h: Hierarchy, level, max_its=1000, reduction=1e-12, rhs=None, into=None):
+    """Plain CG from a zero guess, stop at ||r|| <= reduction * ||r0|| (Poisson/2D...exa3:12-14).
+    `rhs` / `into`: right-hand side and destination arrays other than the level's rhs / sol fields
+    (the Krylov smoother solves the residual equation into a scratch field)."""
+    x = h.sol[level] if into is None else into
     for a in x:
         a[...] = 0
     work = [np.zeros_like(a) for a in x]                             # p with zero Dirichlet rim
-    r = _flat_interior(h.rhs[level]).copy()
+    r = _flat_interior(h.rhs[level] if rhs is None else rhs).copy()
     p = r.copy()
     xs = np.zeros_like(r)
     rs = lane_dot(r, r)
@@ -520,16 +522,16 @@ def op_coarse_cg(h: Hierarchy, level, max_its=1000, reduction=1e-12):
     return its
 
 
-def op_coarse_bicgstab(h: Hierarchy, level, max_its=1000, reduction=1e-6):
+def op_coarse_bicgstab(h: Hierarchy, level, max_its=1000, reduction=1e-6, rhs=None, into=None):
     """Unpreconditioned BiCGStab exactly as Helmholtz/2D_FD_Helmholtz_fromL3.exa3:396-433
-    (dot without conjugation; p and s carry the Robin boundary, :384-391)."""
-    x = h.sol[level]
+    (dot without conjugation; p and s carry the Robin boundary, :384-391).  `rhs` / `into` as op_coarse_cg."""
+    x = h.sol[level] if into is None else into
     for a in x:
         a[...] = 0
     wp = [np.zeros_like(a) for a in x]
     ws = [np.zeros_like(a) for a in x]
     xs = np.zeros_like(_flat_interior(x))
-    res = _flat_interior(h.rhs[level]) - _apply_flat(h, level, x)
+    res = _flat_interior(h.rhs[level] if rhs is None else rhs) - _apply_flat(h, level, x)
     cur = root(lane_dot(res, res))
     init = modulus(cur)
     if cur == 0.0:
@@ -565,6 +567,27 @@ def op_coarse_bicgstab(h: Hierarchy, level, max_its=1000, reduction=1e-6):
     return its
 
 
+def op_krylov(h: Hierarchy, level, method, iterations, reduction):
+    """`<Name>_<n>@level()` in the place of a smoother (code_generation/exastencils.py:758-768;
+    ir/krylov_subspace.py:4-45): at most n iterations of the Krylov method on A x = rhs@level starting from
+    the current solution.  The reference takes the function body from the ExaStencils-generated coarse-grid
+    solver of that level (:1025-1086, marked "either fix or remove" there; its grammar never produces the
+    node), so the statement is restated in the engine's terms: r = rhs - A x into the residual field, the
+    coarse-grid solver's iteration on A e = r from e = 0 (n iterations at most, the `.exa3` block's
+    reduction target as early exit), x += e on interior nodes.  Equivalent to starting the method from x."""
+    op_residual(h, level)
+    scratch = [np.zeros_like(a) for a in h.sol[level]]
+    if method == "ConjugateGradient":
+        op_coarse_cg(h, level, iterations, reduction, rhs=h.res[level], into=scratch)
+    elif method == "BiCGStab":
+        op_coarse_bicgstab(h, level, iterations, reduction, rhs=h.res[level], into=scratch)
+    else:
+        raise NotImplementedError(method)
+    for u, e in zip(h.sol[level], scratch):
+        _interior(u)[...] = _interior(u) + _interior(e)
+    h.apply_bc(level, h.sol[level])
+
+
 # ----------------------------------------------------------------------------------------
 # op-list interpreter and outer solver
 # ----------------------------------------------------------------------------------------
@@ -597,6 +620,8 @@ def run_ops(h: Hierarchy, ops, settings: SolverSettings):
             op_prolong_add(h, op.level, op.omega, op.src or "sol")
         elif kind == "prolong":
             op_prolong(h, op.level, op.src or "sol")
+        elif kind == "krylov":
+            op_krylov(h, op.level, op.method, op.iterations, settings.cgs_target_reduction)
         elif kind == "cgs":
             if op.level == h.min_level:
                 if settings.cgs == "CG":

@@ -23,6 +23,9 @@ class FakeWorkspace:
     def set_operator(self, level, table):
         self._operators[level] = table
 
+    def set_variable_coefficient(self, spec):
+        self.variable = spec
+
     def set_boundary(self, *a):
         pass
 
