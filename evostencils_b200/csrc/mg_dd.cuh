@@ -11,7 +11,11 @@
 //                   (their kernels no longer read the ghost planes I am about to overwrite); copy my
 //                   boundary planes into their ghost planes; fence; "delivered k" (pushed); wait for
 //                   theirs.  The kernel ends when my ghost planes are valid: the next kernel of the
-//                   stream may read them.
+//                   stream may read them.  Inside a decomposed cycle the ack round is dropped
+//                   (need_ack = 0): "pushed k" from a neighbour means all its kernels before its exchange k
+//                   are complete, and the only kernel it runs between its exchanges k and k+1 never reads
+//                   the ghost planes exchange k+1 delivers (an out-of-place sweep reads the other buffer; the
+//                   restriction / prolongation read other fields) -- mg_engine_dd.inc dd_issue_cycle.
 //   agglomeration   k_dd_gather: below the coarsest decomposed level every rank runs the cycle redundantly
 //                   on a whole grid; each rank pulls the owned planes of the restricted right-hand side
 //                   from all ranks (ready / done flags = a full barrier on either side of the reads).
@@ -74,28 +78,40 @@ __device__ inline void dd_wait(const unsigned long long* flag, unsigned long lon
     }
 }
 
-// grid-stride copy of n2 16-byte words
+// grid-stride copy of n2 16-byte words, four independent loads in flight per thread (a pull over NVLink is
+// bound by the number of outstanding loads)
 __device__ __forceinline__ void dd_copy(double2* __restrict__ dst, const double2* __restrict__ src, long long n2) {
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n2; i += (long long)gridDim.x * blockDim.x)
-        dst[i] = src[i];
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n2; i += 4 * stride) {
+        const double2 a = src[i], b = src[i + stride], c = src[i + 2 * stride], d = src[i + 3 * stride];
+        dst[i] = a;
+        dst[i + stride] = b;
+        dst[i + 2 * stride] = c;
+        dst[i + 3 * stride] = d;
+    }
+    for (; i < n2; i += stride) dst[i] = src[i];
 }
 
 // One halo exchange of this rank: src_* = my boundary planes (contiguous), dst_* = the neighbour's ghost
 // planes (peer memory), n2 = 16-byte words per direction; lo / hi = the neighbours' DDComm (null: none).
 __global__ void __launch_bounds__(256) k_dd_exchange(DDComm* me, DDComm* lo, DDComm* hi, const double2* src_lo,
-                                                     double2* dst_lo, const double2* src_hi, double2* dst_hi, long long n2) {
+                                                     double2* dst_lo, const double2* src_hi, double2* dst_hi, long long n2,
+                                                     int need_ack) {
     pdl_sync();
     __shared__ unsigned long long k_s;
     if (threadIdx.x == 0) {
         const unsigned long long k = ld_volatile_u64(&me->epoch_x) + 1;
         k_s = k;
-        if (blockIdx.x == 0) {
-            __threadfence_system();
-            if (lo) st_release_sys(&lo->ack[1], k);        // I am the lower neighbour's upper neighbour
-            if (hi) st_release_sys(&hi->ack[0], k);
+        if (need_ack) {
+            if (blockIdx.x == 0) {
+                __threadfence_system();
+                if (lo) st_release_sys(&lo->ack[1], k);        // I am the lower neighbour's upper neighbour
+                if (hi) st_release_sys(&hi->ack[0], k);
+            }
+            if (lo) dd_wait(&me->ack[0], k, &me->error);
+            if (hi) dd_wait(&me->ack[1], k, &me->error);
         }
-        if (lo) dd_wait(&me->ack[0], k, &me->error);
-        if (hi) dd_wait(&me->ack[1], k, &me->error);
     }
     __syncthreads();
     const unsigned long long k = k_s;

@@ -153,6 +153,7 @@ struct mg_workspace {
     size_t cgs_smem_bytes = 0;                  // dynamic shared memory of the coarse solver (0: global scratch)
     // domain decomposition: this workspace is the z-slab of `dd_rank` (mg_engine_dd.inc)
     int dd_rank = -1, dd_world = 0;
+    int dd_local_peers = 0;                     // other ranks living in this process (virtual ranks on the same GPU)
     void* dd_comm = nullptr;                    // mg::DDComm of this rank (device)
     void* dd_peer_comm[16] = {};                // every rank's DDComm, mapped (own included)
     std::vector<mg::DDPeerLevel> dd_lo, dd_hi;  // neighbours' levels, index = level - min_level
