@@ -11,6 +11,7 @@
 #include "mg_fast2d.cuh"
 #include "mg_fast3d.cuh"
 #include "mg_rbgs3d.cuh"
+#include "mg_rbgs3d2.cuh"
 #include "mg_restrict3d.cuh"
 #include "mg_varcoef.cuh"
 #include "mg_workspace.cuh"
@@ -270,6 +271,33 @@ inline bool launch_rbgs3d_cfg(mg_workspace* ws, Level& lv, const double* u, cons
     return true;
 }
 
+// the same sweep with two tile rows per warp (mg_rbgs3d2.cuh)
+template <int RY, int NS, int NF>
+inline bool launch_rbgs3d2_cfg(mg_workspace* ws, Level& lv, const double* u, const double* f, double* out, double w) {
+    static const int zc_env = tunable("MG_RBGS3D_ZCHUNK", 0), pf_env = tunable("MG_RBGS3D_PF", 0);
+    static bool opted_in[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !opted_in[dev]) {
+        if (cudaFuncSetAttribute(k_rbgs3d2<RY, NS, NF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)rbgs3d_smem_bytes<RY, NS, NF>()) != cudaSuccess)
+            return false;
+        opted_in[dev] = true;
+    }
+    const SlabView v = slab_view(lv);
+    const CUtensorMap* tm_u = plane_tensor_map(u - v.shift, lv.g, RY + 4, v.planes);
+    const CUtensorMap* tm_f = plane_tensor_map(f - v.shift, lv.g, RY + 2, v.planes);
+    if (!tm_u || !tm_f) return false;
+    const int n = lv.g.n, nzo = v.zhi - v.zlo + 1;
+    const int gx = (n + RB3_TW - 1) / RB3_TW, gy = (n + RY - 1) / RY;
+    int zchunk = zc_env >= 3 ? zc_env : 64;
+    while (zc_env < 3 && zchunk > 4 && gx * gy * ((nzo + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
+    launch_k(ws, k_rbgs3d2<RY, NS, NF>, dim3(gx, gy, (nzo + zchunk - 1) / zchunk), 16 * (RY + 2),
+             rbgs3d_smem_bytes<RY, NS, NF>(), lv.g, star3d(lv), *tm_u, *tm_f, out - v.shift, w, zchunk, pf_env,
+             v.zoff, v.zlo, v.zhi);
+    return true;
+}
+
 // would a red-black sweep of this level run as the one-pass kernel?  (the domain-decomposition driver
 // exchanges two ghost planes once per sweep then, instead of one plane per colour pass)
 inline bool rbgs3d_applicable(const mg_workspace* ws, const Level& lv) {
@@ -280,7 +308,17 @@ inline bool rbgs3d_applicable(const mg_workspace* ws, const Level& lv) {
 
 inline bool launch_rbgs3d(mg_workspace* ws, Level& lv, const double* u, const double* f, double* out, double w) {
     static const int cfg = tunable("MG_RBGS3D_CFG", 0);
+    static const int version = tunable("MG_RBGS3D_V", 2);
     if (!rbgs3d_applicable(ws, lv)) return false;
+    if (version == 2) {
+        switch (cfg) {
+            case 1: return launch_rbgs3d2_cfg<14, 6, 5>(ws, lv, u, f, out, w);
+            case 2: return launch_rbgs3d2_cfg<6, 7, 6>(ws, lv, u, f, out, w);
+            case 3: return launch_rbgs3d2_cfg<12, 6, 5>(ws, lv, u, f, out, w);
+            case 4: return launch_rbgs3d2_cfg<8, 6, 5>(ws, lv, u, f, out, w);
+            default: return launch_rbgs3d2_cfg<8, 7, 6>(ws, lv, u, f, out, w);
+        }
+    }
     switch (cfg) {
         // rows per tile, ring sizes of u / f (measured at 513^3, profiles/README.md): the default keeps
         // 3 CTAs per SM (74 KB each) with 3 planes in flight

@@ -54,16 +54,24 @@ __device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* tm, int x, in
     asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(tm), "r"(x), "r"(y), "r"(z)
                  : "memory");
 }
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok;
+}
+__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
+    for (uint32_t tries = 0; !mbar_try_wait(bar, parity); ++tries)
+        if (tries == (1u << 20)) __trap();          // a transfer that never completes: fail, do not hang
+}
+// The first try_wait (which itself suspends the thread for a hardware-defined time) almost always succeeds: the
+// planes are staged three steps ahead.  The bounded retry loop is kept out of line -- inlined, its counter, YIELD and
+// reconvergence barrier cost nine instructions per wait, two waits per plane and warp.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t ok, tries = 0;
-    do {
-        if (++tries == (1u << 20)) __trap();        // a transfer that never completes: fail, do not hang
-        asm volatile(
-            "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
-            : "=r"(ok)
-            : "r"(bar), "r"(parity)
-            : "memory");
-    } while (!ok);
+    if (!mbar_try_wait(bar, parity)) mbar_wait_slow(bar, parity);
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
