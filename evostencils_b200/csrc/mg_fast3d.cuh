@@ -243,4 +243,88 @@ __global__ void __launch_bounds__(NT) k_prolong3d(Geom gf, Geom gc, const double
     }
 }
 
+// ---- the same stage, two fine planes per thread (round 2) -----------------------------------------------------
+// ncu of k_prolong3d<128,8> at 513^3 (profiles/r2/ncu_3d_513.md): DRAM bytes = algorithmic bytes, but the L1 pipe
+// is 84 % busy and 65 % of the stall samples wait on it: 26 load/store instructions per 16 nodes, ten of them
+// 8-byte loads of coarse values, half of which are duplicates on even planes.  The fine planes 2Z+1 and 2Z+2
+// need the coarse planes Z and Z+1 only, so a thread that owns its column pair in BOTH planes loads the coarse
+// values once: 2 (RY/2+1) coarse loads per 4 RY nodes instead of per 2 RY.  Summation order of prolong_at
+// (coarse planes outer, rows, columns inner, then the power-of-two scale): unchanged, bit-identical.
+// grid.z = pairs of fine planes: pair p = global planes 2p+1 (odd) and 2p+2 (even), p0 = first pair of the slab.
+template <int NT, int RY>
+__global__ void __launch_bounds__(NT) k_prolong3d_zz(Geom gf, Geom gc, const double* __restrict__ e, double* __restrict__ u,
+                                                      double omega, int p0) {
+    pdl_sync();
+    const int lane = threadIdx.x & 31;
+    const int x0 = (blockIdx.x * NT + threadIdx.x) * 2;       // even fine column, <= n-3
+    const int X = x0 >> 1;
+    const int n = gf.n;
+    const int y0 = 1 + blockIdx.y * RY;                         // odd
+    const int Z = p0 + blockIdx.z;                              // global coarse plane below the pair
+    const int zo = 2 * Z + 1 - gf.z0, ze = zo + 1;              // local fine planes of the pair (odd, even global index)
+    // a plane of the pair is updated if it is an owned plane of the slab and an interior plane of the grid
+    const bool do_o = zo >= 1 && zo <= gf.nz - 2 && 2 * Z + 1 <= n - 2;
+    const bool do_e = ze >= 1 && ze <= gf.nz - 2 && 2 * Z + 2 <= n - 2;
+    const int Zl = Z - gc.z0;                                   // local coarse plane
+    const int Ylo = y0 >> 1;
+    double a[2][RY / 2 + 1], b[2][RY / 2 + 1];
+    double2 uo[RY], ue[RY];
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+#pragma unroll
+        for (int j = 0; j < RY / 2 + 1; ++j) {
+            const int Y = imin(Ylo + j, gc.n - 1);
+            const int Zk = (k == 0 && !do_o) ? Zl + 1 : Zl + k;   // plane Z is not needed (and may not exist) without the odd plane
+            const double* p = e + (long long)Zk * gc.plane + (long long)Y * gc.pitch + X;
+            a[k][j] = ldf1(p);
+            b[k][j] = 0.0;
+            if (lane == 31) b[k][j] = ldf1(p + 1);
+        }
+#pragma unroll
+    for (int i = 0; i < RY; ++i) {
+        const long long row = (long long)imin(y0 + i, n - 1) * gf.pitch + x0;
+        uo[i] = make_double2(0.0, 0.0);
+        ue[i] = make_double2(0.0, 0.0);
+        if (do_o) uo[i] = ldf2(u + (long long)zo * gf.plane + row);
+        if (do_e) ue[i] = ldf2(u + (long long)ze * gf.plane + row);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+#pragma unroll
+        for (int j = 0; j < RY / 2 + 1; ++j) {
+            const double nb = __shfl_down_sync(0xffffffffu, a[k][j], 1);
+            if (lane != 31) b[k][j] = nb;
+        }
+#pragma unroll
+    for (int i = 0; i < RY; ++i) {
+        const int y = y0 + i;
+        if (y > n - 2) continue;
+        const int py = y & 1;
+        const int j = (y >> 1) - Ylo;
+        if (do_o) {                                             // pz = 1: coarse planes Z, Z+1
+            double s0 = a[0][j], s1 = a[0][j] + b[0][j];
+            if (py) { s0 = s0 + a[0][j + 1]; s1 = s1 + a[0][j + 1]; s1 = s1 + b[0][j + 1]; }
+            s0 = s0 + a[1][j]; s1 = s1 + a[1][j]; s1 = s1 + b[1][j];
+            if (py) { s0 = s0 + a[1][j + 1]; s1 = s1 + a[1][j + 1]; s1 = s1 + b[1][j + 1]; }
+            s0 = (py ? 0.25 : 0.5) * s0;
+            s1 = (py ? 0.125 : 0.25) * s1;
+            double2 v = uo[i];
+            if (x0 >= 1) v.x = v.x + omega * s0;
+            v.y = v.y + omega * s1;
+            st2(u + (long long)zo * gf.plane + (long long)y * gf.pitch + x0, v);
+        }
+        if (do_e) {                                             // pz = 0: coarse plane Z+1 alone
+            double s0 = a[1][j], s1 = a[1][j] + b[1][j];
+            if (py) { s0 = s0 + a[1][j + 1]; s1 = s1 + a[1][j + 1]; s1 = s1 + b[1][j + 1]; }
+            if (py) s0 = 0.5 * s0;
+            s1 = (py ? 0.25 : 0.5) * s1;
+            double2 v = ue[i];
+            if (x0 >= 1) v.x = v.x + omega * s0;
+            v.y = v.y + omega * s1;
+            st2(u + (long long)ze * gf.plane + (long long)y * gf.pitch + x0, v);
+        }
+    }
+}
+
 }  // namespace mg

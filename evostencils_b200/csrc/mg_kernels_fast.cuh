@@ -316,6 +316,10 @@ inline bool launch_rbgs3d(mg_workspace* ws, Level& lv, const double* u, const do
             case 2: return launch_rbgs3d2_cfg<6, 7, 6>(ws, lv, u, f, out, w);
             case 3: return launch_rbgs3d2_cfg<12, 6, 5>(ws, lv, u, f, out, w);
             case 4: return launch_rbgs3d2_cfg<8, 6, 5>(ws, lv, u, f, out, w);
+            case 5: return launch_rbgs3d2_cfg<8, 5, 4>(ws, lv, u, f, out, w);
+            case 6: return launch_rbgs3d2_cfg<10, 6, 5>(ws, lv, u, f, out, w);
+            case 7: return launch_rbgs3d2_cfg<12, 5, 4>(ws, lv, u, f, out, w);
+            case 8: return launch_rbgs3d2_cfg<10, 5, 4>(ws, lv, u, f, out, w);
             default: return launch_rbgs3d2_cfg<8, 7, 6>(ws, lv, u, f, out, w);
         }
     }
@@ -568,6 +572,26 @@ inline bool fast_prolong_add(mg_workspace* ws, Level& lf, Level& lc, const Field
         const int ry_env = ry_tuned ? ry_tuned : (lf.g.n >= 257 ? 8 : 4);
         const double* e = reinterpret_cast<const double*>(src.p[0]);
         double* u = static_cast<double*>(lf.sol[lf.cur[0]][0]);
+        static const int version = tunable("MG_PROLONG3D_V", 2);
+        if (version == 2) {
+            // pairs of fine planes (2Z+1, 2Z+2) that contain an owned interior plane of this level
+            const int zg_first = imax_h(1, lf.g.z0 + 1), zg_last = imin_h(lf.g.n - 2, lf.g.z0 + lf.g.nz - 2);
+            if (zg_last < zg_first) return true;
+            const int p_lo = (zg_first - 1) >> 1, p_hi = (zg_last - 1) >> 1;
+            auto launch2 = [&](auto ry_tag) {
+                constexpr int RY = decltype(ry_tag)::value;
+                dim3 grid((lf.g.n - 1) / (2 * nt), (lf.g.n - 2 + RY - 1) / RY, p_hi - p_lo + 1);
+                if (nt == 128) launch_k(ws, k_prolong3d_zz<128, RY>, grid, 128, 0, lf.g, lc.g, e, u, omega, p_lo);
+                else if (nt == 64) launch_k(ws, k_prolong3d_zz<64, RY>, grid, 64, 0, lf.g, lc.g, e, u, omega, p_lo);
+                else launch_k(ws, k_prolong3d_zz<32, RY>, grid, 32, 0, lf.g, lc.g, e, u, omega, p_lo);
+            };
+            static const int ry2 = tunable("MG_PROLONG3D_RY", 0);
+            if (ry2 == 8) launch2(std::integral_constant<int, 8>{});
+            else if (ry2 == 2) launch2(std::integral_constant<int, 2>{});
+            else launch2(std::integral_constant<int, 4>{});
+            fast_count(ws);
+            return true;
+        }
         auto launch = [&](auto ry_tag) {
             constexpr int RY = decltype(ry_tag)::value;
             dim3 grid((lf.g.n - 1) / (2 * nt), (lf.g.n - 2 + RY - 1) / RY, lf.g.nz - 2);
