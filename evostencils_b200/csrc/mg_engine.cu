@@ -148,7 +148,14 @@ static void free_smoothers(mg_workspace* ws) {
     ws->smoothers.clear();
 }
 
+static void free_captured(mg_workspace* ws) {
+    for (auto& c : ws->captured)
+        if (c.exec) cudaGraphExecDestroy(c.exec);
+    ws->captured.clear();
+}
+
 static void free_cycles(mg_workspace* ws) {
+    free_captured(ws);
     if (ws->outer_graph) {
         cudaGraphExecDestroy(ws->outer_graph);
         ws->outer_graph = nullptr;
@@ -162,6 +169,7 @@ static void free_cycles(mg_workspace* ws) {
 
 // drop the instantiated graphs (they are bound to a stream's capture) but keep the op lists
 static void free_cycles_graphs(mg_workspace* ws) {
+    free_captured(ws);           // they may reference tail programs of the pool that is reset below
     for (auto& c : ws->cycles) {
         for (auto& kv : c.variants)
             if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);

@@ -89,6 +89,14 @@ struct GraphVariant {
     long long kernels = 0;
 };
 
+// kernels captured between mg_capture_begin / mg_capture_end (the FAS statements, mg_enqueue_ops): valid for the
+// ping-pong state of the solution buffers it was captured in
+struct CapturedGraph {
+    cudaGraphExec_t exec = nullptr;
+    std::vector<int> begin, end;               // lv.cur[f] of every level and field before / after the captured calls
+    long long kernels = 0;
+};
+
 struct Cycle {
     std::vector<mg_op> ops;
     std::map<int, GraphVariant> variants;      // keyed by the finest level's buffer state
@@ -105,6 +113,10 @@ struct mg_workspace {
     std::vector<mg::Level> levels;              // index = level - min_level
     std::vector<mg::Smoother> smoothers;
     std::vector<mg::Cycle> cycles;
+    std::vector<mg::CapturedGraph> captured;    // mg_capture_begin / mg_capture_end
+    bool capturing = false;
+    std::vector<int> capture_begin_state;
+    long long capture_begin_count = 0;
     int bc_kind = MG_BC_DIRICHLET;
     double bc_k = 0.0;
     int vc_kind = MG_VC_NONE;                   // variable-coefficient operator (mg_set_variable_coefficient)

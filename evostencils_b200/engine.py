@@ -34,7 +34,7 @@ EXPORTED_SYMBOLS = [
     "mg_create", "mg_create_slab", "mg_field_pointer", "mg_destroy", "mg_last_error", "mg_launch_count", "mg_set_operator", "mg_set_boundary",
     "mg_set_variable_coefficient", "mg_set_coarse_solver", "mg_add_smoother", "mg_clear_smoothers", "mg_upload", "mg_download",
     "mg_upload_device", "mg_save_initial_guess", "mg_restore_initial_guess", "mg_exec_ops", "mg_enqueue_ops", "mg_set_stream", "mg_build_cycle",
-    "mg_free_cycles", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_set_time_limit", "mg_set_outer_operator",
+    "mg_free_cycles", "mg_capture_begin", "mg_capture_end", "mg_graph_launch", "mg_run_cycles", "mg_residual_norm", "mg_solve", "mg_set_time_limit", "mg_set_outer_operator",
     "mg_solve_bicgstab", "mg_synchronize",
     "mg_time_ops", "mg_profile_ops", "mg_mark", "mg_elapsed", "mg_flush_l2", "mg_set_fast_kernels",
     "mg_fas_smooth", "mg_fas_residual", "mg_fas_restrict", "mg_fas_subtract_approximation", "mg_fas_residual_norm",
@@ -84,6 +84,9 @@ def _signatures():
         "mg_set_coarse_solver": [vp, i32, i32, dbl],
         "mg_add_smoother": [vp, i32, i32, i32, pi32, i32, pi32, pi32, i32, C.POINTER(C.c_uint32), pdbl, pint],
         "mg_clear_smoothers": [vp],
+        "mg_capture_begin": [vp],
+        "mg_capture_end": [vp, pint],
+        "mg_graph_launch": [vp, i32, i32],
         "mg_upload": [vp, i32, i32, i32, vp],
         "mg_download": [vp, i32, i32, i32, vp],
         "mg_upload_device": [vp, i32, i32, i32, vp],
@@ -466,6 +469,22 @@ class Workspace:
         cycle = C.c_int()
         self._check(self.lib.mg_build_cycle(self._h, enc, len(enc), C.byref(cycle)))
         return cycle.value
+
+    def capture_begin(self):
+        self._check(self.lib.mg_capture_begin(self._h))
+
+    def capture_end(self) -> int:
+        handle = C.c_int()
+        self._check(self.lib.mg_capture_end(self._h, C.byref(handle)))
+        return handle.value
+
+    def graph_launch(self, graph: int, n: int = 1) -> bool:
+        """-> False when the solution buffers are not in the state the graph was captured in."""
+        rc = self.lib.mg_graph_launch(self._h, graph, n)
+        if rc == -3:                       # MG_ERR_STATE
+            return False
+        self._check(rc)
+        return True
 
     def run_cycles(self, cycle: int, n: int) -> float:
         ms = C.c_float()

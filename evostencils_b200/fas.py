@@ -21,7 +21,7 @@ from typing import List, Tuple
 import numpy as np
 
 from . import lowering
-from .engine import Workspace
+from .engine import EngineError, Workspace
 
 GAMMA = 10.0                  # Globals { Val gam : Real = 10.0 }  (.exa4:32-34)
 SMOOTHER_WEIGHT = 0.8         # Smoother@all                        (.exa4:65-75)
@@ -206,8 +206,9 @@ class FasSolver:
     """FAS_2D_Basic on one GPU: level hierarchy, right-hand side of the enhanced test problem, zero
     initial guess; `solve` runs a cycle until the `.exa4`'s stopping rule holds."""
 
-    def __init__(self, min_level: int, max_level: int, gamma: float = GAMMA, device: int = 0):
+    def __init__(self, min_level: int, max_level: int, gamma: float = GAMMA, device: int = 0, use_graph: bool = True):
         self.min_level, self.max_level, self.gamma = min_level, max_level, gamma
+        self.use_graph = use_graph
         self.ws = self._make_workspace(device)
         for level in range(min_level, max_level + 1):
             self.ws.set_operator(level, laplace_table(level))
@@ -234,21 +235,46 @@ class FasSolver:
             elif op.kind == "subtract":
                 ws.fas_subtract_approximation(op.level)
             elif op.kind == "prolong_add":
-                ws.exec_ops([lowering.Op("prolong_add", op.level, omega=op.omega, src="sol", dst="sol")])
+                self._prolong_add(op)
             else:
                 raise ValueError(f"unknown FAS op '{op.kind}'")
+
+    def _prolong_add(self, op):
+        # enqueued, not executed-and-waited-for: the cycle is one stream of kernels (and can be captured)
+        self.ws.enqueue_ops([lowering.Op("prolong_add", op.level, omega=op.omega, src="sol", dst="sol")])
+
+    def _timer(self, stop: bool):
+        """CUDA events on the engine stream, as mg_solve; -> ms on stop."""
+        self.ws.mark(1 if stop else 0)
+        return self.ws.elapsed() if stop else None
 
     def solve(self, ops: List[FasOp], target: float = TARGET_REDUCTION,
               max_iterations: int = MAX_ITERATIONS) -> Tuple[List[float], float]:
         """-> (residual history, solve time in ms): `Solve` of the `.exa4` (:118-187)."""
-        history = [self.ws.fas_residual_norm(self.max_level, self.gamma)]
-        t0 = time.perf_counter()
+        ws = self.ws
+        history = [ws.fas_residual_norm(self.max_level, self.gamma)]
+        graphs: List[int] = []
+        self._timer(False)
         while not (history[-1] < target * history[0] or len(history) - 1 >= max_iterations):
-            self.run_cycle(ops)
-            history.append(self.ws.fas_residual_norm(self.max_level, self.gamma))
+            if not self.use_graph or len(history) == 1:
+                self.run_cycle(ops)             # the first cycle runs directly: it allocates the Approximation fields
+            elif not any(ws.graph_launch(g) for g in graphs):
+                # the cycle as ONE CUDA graph per ping-pong state of the solution buffers (a cycle with an odd
+                # number of Jacobi sweeps on a level alternates between two states): ~35 launches -> 1
+                ws.capture_begin()
+                try:
+                    self.run_cycle(ops)
+                finally:
+                    graphs.append(ws.capture_end())
+                if not ws.graph_launch(graphs[-1]):
+                    raise EngineError("a freshly captured FAS cycle does not match the buffer state")
+            history.append(ws.fas_residual_norm(self.max_level, self.gamma))
             if not math.isfinite(history[-1]):
                 break
-        return history, (time.perf_counter() - t0) * 1e3
+        ms = self._timer(True)
+        if graphs:
+            ws.clear_programs()
+        return history, ms
 
     def solution(self) -> np.ndarray:
         return self.ws.download("sol", self.max_level, 0)

@@ -160,6 +160,16 @@ int mg_set_stream(mg_workspace* ws, void* cuda_stream);
 /* capture the op list (plus the fused residual-norm of the finest level) as a CUDA graph */
 int mg_build_cycle(mg_workspace* ws, const mg_op* ops, int n_ops, int* cycle);
 int mg_free_cycles(mg_workspace* ws);
+/* Caller-driven capture (the FAS statements below are separate calls, exastencils_FAS.py:99-319): the kernels that
+ * mg_fas_smooth / mg_fas_residual / mg_fas_restrict / mg_fas_subtract_approximation / mg_enqueue_ops issue between
+ * begin and end become ONE CUDA graph instead of running; synchronising calls (mg_exec_ops, norms, uploads) are not
+ * allowed in between, and everything the calls allocate on first use must exist (run the sequence once before).
+ * mg_graph_launch enqueues n replays; it returns MG_ERR_STATE when the solution buffers are not in the ping-pong
+ * state of the capture (a sequence with an odd number of Jacobi sweeps on a level alternates between two states:
+ * capture both).  mg_free_cycles drops the graphs. */
+int mg_capture_begin(mg_workspace* ws);
+int mg_capture_end(mg_workspace* ws, int* graph);
+int mg_graph_launch(mg_workspace* ws, int graph, int n);
 /* replay `n_cycles` cycles without convergence checks (throughput measurements) */
 int mg_run_cycles(mg_workspace* ws, int cycle, int n_cycles, float* ms);
 /* sqrt(sum over interior nodes and fields of (rhs - A sol)^2) on `level` */

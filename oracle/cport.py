@@ -56,4 +56,17 @@ class FasSolver(fas.FasSolver):
     """The host-side FAS driver of the product on the C port's stages (CPU figure / checker)."""
 
     def _make_workspace(self, device):
+        self.use_graph = False                      # no stream, no graph: the port runs every statement at once
         return workspace(2, self.min_level, self.max_level)
+
+    def _prolong_add(self, op):
+        from evostencils_b200 import lowering
+        self.ws.exec_ops([lowering.Op("prolong_add", op.level, omega=op.omega, src="sol", dst="sol")])
+
+    def _timer(self, stop):
+        import time
+        now = time.perf_counter()
+        if not stop:
+            self._t0 = now
+            return None
+        return (now - self._t0) * 1e3

@@ -380,3 +380,24 @@ def test_generator_mirror_evaluates_like_the_oracle():
     # the last residuals sit at 1e-10 of the first, where exp() round-off shows: the n-th root agrees to 1e-3
     assert abs(c - (want[-1] / want[0]) ** (1.0 / n)) <= 1e-3 * c
     gen.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pre,post", [(2, 1), (1, 1)])
+def test_graph_replays_are_bitwise_the_direct_launches(pre, post):
+    """The cycle captured as one CUDA graph per ping-pong state (V(2,1) with Jacobi smoothing alternates between
+    two states, V(1,1) keeps one) against statement-by-statement launches: identical histories and fields."""
+    lo, hi = 5, 8
+    ops = fas.v_cycle_ops(hi, lo, pre, post)
+    direct = fas.FasSolver(lo, hi, use_graph=False)
+    want, _ = direct.solve(ops, max_iterations=9)
+    u_want = direct.solution()
+    direct.close()
+    solver = fas.FasSolver(lo, hi)
+    got, ms = solver.solve(ops, max_iterations=9)
+    u_got = solver.solution()
+    launches = solver.ws.launch_count()
+    solver.close()
+    assert got == want and len(got) == 10
+    assert np.array_equal(u_got, u_want)
+    assert ms > 0 and launches > 0
