@@ -9,6 +9,8 @@
 // row-major), then the xor-butterfly of block_sum_256 -- the oracle mirrors this order exactly, so
 // the real-valued coarse solve is bit-reproducible against it.
 #pragma once
+#include <type_traits>
+
 #include "mg_kernels_generic.cuh"
 
 namespace mg {
@@ -48,23 +50,46 @@ __device__ __forceinline__ FieldSet<T> as_fields(T* base, const Geom& g) {
 // coarsest levels a thread owns at most one unknown, so no iteration pays the index arithmetic).
 template <int D>
 struct ElemCache {
-    int f0;
-    long long idx0;
-    bool has0;
-    __device__ ElemCache(const Geom& g, const InteriorIter<D>& it) : f0(0), idx0(0), has0(krylov_tid() < it.total) {
-        if (has0) it.decode(krylov_tid(), g, f0, idx0);
+    static constexpr int K = 4;              // elements of a thread whose index is decoded once (33^2: all four)
+    int f[K];
+    int idx[K];                              // coarse levels are far below 2^31 elements
+    int count;
+    __device__ ElemCache(const Geom& g, const InteriorIter<D>& it) : count(0) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            f[k] = 0;
+            idx[k] = 0;
+            const int e = krylov_tid() + 256 * k;
+            if (krylov_tid() < 256 && e < it.total) {
+                long long i;
+                it.decode(e, g, f[k], i);
+                idx[k] = (int)i;
+                count = k + 1;
+            }
+        }
     }
     template <class Fn>
     __device__ __forceinline__ void each(const Geom& g, const InteriorIter<D>& it, Fn fn) const {
-        if (!has0) return;
-        fn(f0, idx0);
-        for (int e = krylov_tid() + 256; e < it.total; e += 256) {
-            int f; long long idx;
-            it.decode(e, g, f, idx);
-            fn(f, idx);
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+            if (k < count) fn(f[k], (long long)idx[k]);
+        if (count < K) return;
+        for (int e = krylov_tid() + 256 * K; e < it.total; e += 256) {
+            int ff; long long i;
+            it.decode(e, g, ff, i);
+            fn(ff, i);
         }
     }
 };
+
+// (A u)(idx) for a scalar operator whose NE entries sit in registers (same entry order as apply_row)
+template <typename T, int NE>
+__device__ __forceinline__ T apply_cached(const int (&off)[NE], const T (&val)[NE], const T* __restrict__ u, long long idx) {
+    T acc = t_mul(val[0], u[idx + off[0]]);
+#pragma unroll
+    for (int k = 1; k < NE; ++k) acc = t_add(acc, t_mul(val[k], u[idx + off[k]]));
+    return acc;
+}
 
 template <typename T, int D>
 __device__ T coarse_dot(const T* a, const T* b, const Geom& g, const InteriorIter<D>& it, T* s8) {
@@ -137,23 +162,44 @@ __device__ void coarse_cg_body(const Geom& g, const OperatorTable<T>* __restrict
     const double r0 = t_abs(t_sqrt(rs));
     if (r0 != 0.0) {
         FieldSet<T> pf = as_fields<T, F>(p, g);
+        // the loop, with (A p)(idx) supplied by the caller: the operator entries of a scalar constant stencil are
+        // held in registers (the table lives in global memory: five dependent loads per node and iteration
+        // otherwise -- the coarse solve on 33^2 is most of a configs[0] cycle)
+        auto iterate = [&](auto&& apply_p) {
         for (int iter = 1; iter <= max_its; ++iter) {
-            ec.each(g, it, [&](int f, long long idx) { ap[idx] = apply_row<T, F>(op, pf, f, idx - (long long)f * g.total); });
-            __syncthreads();
+            // ap, x and r are only ever touched by the thread that owns the element (the dot products read a
+            // thread's own elements too), so no barrier is needed until p changes
+            ec.each(g, it, [&](int f, long long idx) { ap[idx] = apply_p(f, idx); });
             T pap = coarse_dot<T, D>(p, ap, g, it, ec, s8);
             T alpha = t_div(rs, pap);
             ec.each(g, it, [&](int, long long idx) {
                 x[idx] = t_add(x[idx], t_mul(alpha, p[idx]));
                 r[idx] = t_sub(r[idx], t_mul(alpha, ap[idx]));
             });
-            __syncthreads();
             T rs_new = coarse_dot<T, D>(r, r, g, it, ec, s8);
+            T beta = t_div(rs_new, rs);                  // issued before the test: overlaps the square root
             if (t_abs(t_sqrt(rs_new)) <= reduction * r0) break;
-            T beta = t_div(rs_new, rs);
             ec.each(g, it, [&](int, long long idx) { p[idx] = t_add(r[idx], t_mul(beta, p[idx])); });
             rs = rs_new;
             __syncthreads();
         }
+        };
+        const int ne = F == 1 ? op->n_entries[0][0] : 0;
+        auto cached = [&](auto ne_tag) {
+            constexpr int NE = decltype(ne_tag)::value;
+            int off[NE];
+            T val[NE];
+#pragma unroll
+            for (int k = 0; k < NE; ++k) {
+                off[k] = op->off[0][0][k];
+                val[k] = op->val[0][0][k];
+            }
+            iterate([&](int, long long idx) { return apply_cached<T, NE>(off, val, p, idx); });
+        };
+        if (F == 1 && !is_variable<T, F>(op) && ne == 5) cached(std::integral_constant<int, 5>{});
+        else if (F == 1 && !is_variable<T, F>(op) && ne == 7) cached(std::integral_constant<int, 7>{});
+        else if (F == 1 && !is_variable<T, F>(op) && ne == 9) cached(std::integral_constant<int, 9>{});
+        else iterate([&](int f, long long idx) { return apply_row<T, F>(op, pf, f, idx - (long long)f * g.total); });
     }
     __syncthreads();
     // solution field: whole array (boundary = 0 for the error equation)
