@@ -202,6 +202,37 @@ def lower(expression, template_smoother: bool = False, cgs_sweeps: int = CGS_SWE
     return merged
 
 
+ABORT_AFTER_MS = 1200000.0          # FAS_2D_Basic.exa4:154: the generated solver gives up beyond this cycle time
+
+
+def printed_residuals(history):
+    """(res_initial, res_final) as `parse_output` reads them from the solver's stdout
+    (exastencils_FAS.py:370-393): the `.exa4` prints the initial residual with `std::cout.precision(4)`
+    (:141-146) and the residual after an iteration with 4, 3, 2 or 1 significant digits depending on its
+    size -- and not at all once it is <= 1e-12 ('EFFECTIVELY ZERO', :160-183) -- so the convergence factor
+    of the reference is formed from those rounded numbers, and `res_final` is the last residual that was
+    printed (0.0 if none was)."""
+    def shown(value, digits):
+        return float(f"{value:.{digits}g}")          # C++ stream default format = %g with that precision
+
+    res_initial = shown(history[0], 4) if len(history) else 0.0
+    res_final = 0.0
+    for r in history[1:]:
+        if not (r == r):                              # NaN prints as nan and parses as nan
+            res_final = r
+        elif r <= 1.0e-12:
+            continue
+        elif r <= 1.0e-11:
+            res_final = shown(r, 1)
+        elif r <= 1.0e-10:
+            res_final = shown(r, 2)
+        elif r <= 1.0e-9:
+            res_final = shown(r, 3)
+        else:
+            res_final = shown(r, 4)
+    return res_initial, res_final
+
+
 class FasSolver:
     """FAS_2D_Basic on one GPU: level hierarchy, right-hand side of the enhanced test problem, zero
     initial guess; `solve` runs a cycle until the `.exa4`'s stopping rule holds."""
@@ -438,7 +469,13 @@ class B200ProgramGeneratorFAS:
             history, ms = solver.solve(ops)
             self.last_residual_history = history
             n = len(history) - 1
-            c = (history[-1] / history[0]) ** (1.0 / n) if n > 0 and history[0] > 0 else float("nan")
+            if ms > ABORT_AFTER_MS:                 # 'Aborting solve after ... ms' (.exa4:154-157) -> parse_output :386-387
+                return infinity, infinity, infinity
+            res_initial, res_final = printed_residuals(history)
+            try:
+                c = (res_final / res_initial) ** (1.0 / n)
+            except (ZeroDivisionError, OverflowError):
+                c = float("nan")
             if math.isinf(c) or math.isnan(c):
                 return infinity, infinity, infinity
             times.append(ms)

@@ -401,3 +401,14 @@ def test_graph_replays_are_bitwise_the_direct_launches(pre, post):
     assert got == want and len(got) == 10
     assert np.array_equal(u_got, u_want)
     assert ms > 0 and launches > 0
+
+
+def test_convergence_factor_is_formed_from_the_printed_residuals():
+    """parse_output (exastencils_FAS.py:370-393) reads what the `.exa4` prints: 4 significant digits, fewer for
+    tiny residuals, nothing below 1e-12."""
+    hist = [123.456789, 1.23456789, 4.56789e-10, 7.89123e-12, 3.3e-13]
+    r0, rn = fas.printed_residuals(hist)
+    assert r0 == 123.5
+    assert rn == 8e-12                       # the last line printed: 1 significant digit; 3.3e-13 prints 'EFFECTIVELY ZERO'
+    assert fas.printed_residuals([5.0, 7.89e-11])[1] == 7.9e-11 and fas.printed_residuals([5.0, 2.567e-10])[1] == 2.57e-10
+    assert fas.printed_residuals([5.0, 1e-13]) == (5.0, 0.0)
