@@ -57,7 +57,7 @@ def parse_args():
     ap.add_argument("--schedule", default="dynamic", choices=["dynamic", "static"],
                     help="dynamic: ranks take the next individual of the step from a shared counter "
                          "(population.WorkQueue); static: the reference's i %% nprocs striding")
-    ap.add_argument("--streams", type=int, default=2,
+    ap.add_argument("--streams", type=int, default=3,
                     help="engine workspaces (= CUDA streams, one host thread each) per GPU: individuals of a rank are "
                          "evaluated concurrently, the coarse levels of one under the fine levels of another")
     ap.add_argument("--max-level", type=int, default=12)

@@ -290,8 +290,14 @@ inline bool launch_rbgs3d2_cfg(mg_workspace* ws, Level& lv, const double* u, con
     if (!tm_u || !tm_f) return false;
     const int n = lv.g.n, nzo = v.zhi - v.zlo + 1;
     const int gx = (n + RB3_TW - 1) / RB3_TW, gy = (n + RY - 1) / RY;
-    int zchunk = zc_env >= 3 ? zc_env : 64;
+    // planes per chunk: as long as possible (every chunk pays the pipeline fill of four planes) with at least
+    // two waves of CTAs, chunks of equal length (513 planes: three chunks of 171, 0.531 ms against 0.545 with 64)
+    int zchunk = zc_env >= 3 ? zc_env : 256;
     while (zc_env < 3 && zchunk > 4 && gx * gy * ((nzo + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
+    if (zc_env < 3) {
+        const int chunks = (nzo + zchunk - 1) / zchunk;
+        zchunk = (nzo + chunks - 1) / chunks;
+    }
     launch_k(ws, k_rbgs3d2<RY, NS, NF>, dim3(gx, gy, (nzo + zchunk - 1) / zchunk), 16 * (RY + 2),
              rbgs3d_smem_bytes<RY, NS, NF>(), lv.g, star3d(lv), *tm_u, *tm_f, out - v.shift, w, zchunk, pf_env,
              v.zoff, v.zlo, v.zhi);
