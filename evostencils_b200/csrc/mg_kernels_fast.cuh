@@ -509,6 +509,35 @@ inline bool launch_resrestrict3d_cfg(mg_workspace* ws, Level& lf, Level& lc, con
     return true;
 }
 
+// the same stage with two fine rows per warp (k_resrestrict3d2)
+template <int RYC, int NS, int NF>
+inline bool launch_resrestrict3d2_cfg(mg_workspace* ws, Level& lf, Level& lc, const double* u, const double* f, double* out) {
+    static const int zc_env = tunable("MG_RESTRICT3D_ZCHUNK", 0);
+    static bool opted_in[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !opted_in[dev]) {
+        if (cudaFuncSetAttribute(k_resrestrict3d2<RYC, NS, NF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)resrestrict3d_smem_bytes<RYC, NS, NF>()) != cudaSuccess)
+            return false;
+        opted_in[dev] = true;
+    }
+    const SlabView v = slab_view(lf);
+    const CUtensorMap* tm_u = plane_tensor_map(u - v.shift, lf.g, 2 * RYC + 3, v.planes);
+    const CUtensorMap* tm_f = plane_tensor_map(f - v.shift, lf.g, 2 * RYC + 1, v.planes);
+    if (!tm_u || !tm_f) return false;
+    const int m = lc.g.n - 2;
+    const int Zlo = imax_h(1, lc.g.z0 + 1), Zhi = imin_h(lc.g.n - 2, lc.g.z0 + lc.g.nz - 2), mz = Zhi - Zlo + 1;
+    if (mz < 1) return true;
+    const int gx = (m + RS3_TXC - 1) / RS3_TXC, gy = (m + RYC - 1) / RYC;
+    int zchunk = zc_env >= 2 ? zc_env : 32;
+    while (zc_env < 2 && zchunk > 2 && gx * gy * ((mz + zchunk - 1) / zchunk) < 888) zchunk >>= 1;
+    launch_k(ws, k_resrestrict3d2<RYC, NS, NF>, dim3(gx, gy, (mz + zchunk - 1) / zchunk), 32 * (RYC + 1),
+             resrestrict3d_smem_bytes<RYC, NS, NF>(), lc.g, lf.g, star3d(lf), *tm_u, *tm_f, out, zchunk,
+             v.zoff, lc.g.z0, Zlo, Zhi);
+    return true;
+}
+
 // would residual + restriction from this fine level run as the fused TMA kernel?
 inline bool resrestrict3d_applicable(const mg_workspace* ws, const Level& lf) {
     static const int enabled = tunable("MG_RESTRICT3D", 1);
@@ -525,6 +554,18 @@ inline bool fast_residual_restrict(mg_workspace* ws, Level& lf, Level& lc) {
         const double* f = static_cast<const double*>(lf.rhs[0]);
         double* out = static_cast<double*>(lc.rhs[0]);
         bool done;
+        static const int version = tunable("MG_RESTRICT3D_V", 1);   // 2: two rows per warp (k_resrestrict3d2): measured no gain (0.4225 against 0.418 ms at 513^3)
+        if (version == 2) {
+            switch (cfg) {
+                case 1: done = launch_resrestrict3d2_cfg<4, 4, 3>(ws, lf, lc, u, f, out); break;
+                case 2: done = launch_resrestrict3d2_cfg<8, 5, 3>(ws, lf, lc, u, f, out); break;
+                case 3: done = launch_resrestrict3d2_cfg<6, 5, 4>(ws, lf, lc, u, f, out); break;
+                case 4: done = launch_resrestrict3d2_cfg<4, 6, 5>(ws, lf, lc, u, f, out); break;
+                default: done = launch_resrestrict3d2_cfg<4, 5, 4>(ws, lf, lc, u, f, out); break;
+            }
+            if (done) fast_count(ws);
+            return done;
+        }
         switch (cfg) {
             case 1: done = launch_resrestrict3d_cfg<4, 4, 3>(ws, lf, lc, u, f, out); break;
             case 2: done = launch_resrestrict3d_cfg<8, 5, 3>(ws, lf, lc, u, f, out); break;
