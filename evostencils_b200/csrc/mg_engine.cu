@@ -71,8 +71,11 @@ static int create_impl(mg_workspace** out, int dimension, int min_level, int max
     ws->elem = dtype == MG_F64 ? 8 : 16;
     // small levels run in the tail kernel: a cluster of 16 CTAs up to 129^2 nodes (2D; measured best:
     // level 7, CTA 0 alone up to level 5), a single CTA up to 17^3 nodes (3D)
-    ws->tail_max_level = dimension == 3 ? 4 : 7;
-    ws->tail_ctas = dimension == 3 ? 1 : 16;
+    // 3D (round 2): one cluster of 16 CTAs up to 33^3 (level 5), CTA 0 alone up to 9^3: a 129^3 V(2,1) cycle -- the
+    // replicated part of a decomposed 513^3 solve on 8 GPUs -- 0.270 -> 0.236 ms; with 65^3 in the cluster it is slower
+    // (0.308 ms: 8192 threads against full-grid kernels)
+    ws->tail_max_level = dimension == 3 ? 5 : 7;
+    ws->tail_ctas = 16;
     if (const char* v = std::getenv("MG_TAIL_CTAS")) ws->tail_ctas = std::atoi(v);
     if (ws->tail_ctas < 1 || ws->tail_ctas > 16) ws->tail_ctas = 1;
     ws->tail_solo_level = dimension == 3 ? 3 : 5;
