@@ -82,14 +82,7 @@ struct ElemCache {
     }
 };
 
-// (A u)(idx) for a scalar operator whose NE entries sit in registers (same entry order as apply_row)
-template <typename T, int NE>
-__device__ __forceinline__ T apply_cached(const int (&off)[NE], const T (&val)[NE], const T* __restrict__ u, long long idx) {
-    T acc = t_mul(val[0], u[idx + off[0]]);
-#pragma unroll
-    for (int k = 1; k < NE; ++k) acc = t_add(acc, t_mul(val[k], u[idx + off[k]]));
-    return acc;
-}
+
 
 template <typename T, int D>
 __device__ T coarse_dot(const T* a, const T* b, const Geom& g, const InteriorIter<D>& it, T* s8) {

@@ -341,7 +341,11 @@ int prepare(mg_workspace* ws) {
     // The opt-in is a property of the function, not of the workspace: several workspaces live in
     // one process (slab + replicated coarse levels, one per virtual rank), so always allow the
     // maximum instead of this workspace's size.
+#ifdef MG_TAIL_TIMING
+    const int smem_cap = 196 * 1024;           // the per-command clock array is static shared memory of the tail kernel
+#else
     const int smem_cap = 200 * 1024;
+#endif
     MG_CUDA(cudaFuncSetAttribute(k_coarse_cg<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
     MG_CUDA(cudaFuncSetAttribute(k_coarse_bicgstab<T, D, F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
     MG_CUDA(cudaFuncSetAttribute(k_tail<T, D, F, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
@@ -632,7 +636,12 @@ int tail_append(mg_workspace* ws, const mg_op& op) {
                 tail_set<T>(cmd.c, dst);
                 for (int f = 0; f < F; ++f)
                     if (flip[f]) lv.cur[f] ^= 1;
-                if (robin) tail_set<T>(tail_new(ws, T_BC, op.level).c, cur_sol<T>(lv));
+                // Robin columns: written by the sweep itself where the kernel's scalar path applies (mg_tail.cuh),
+                // else by a boundary command after it
+                const int ne00 = lv.hop.n_entries[0][0];
+                const bool fused_bc = robin && F == 1 && D == 2 && sm.point && sm.m == 1 && !ws->vc_kind && (ne00 == 5 || ne00 == 9);
+                cmd.bc = fused_bc ? 1 : 0;
+                if (robin && !fused_bc) tail_set<T>(tail_new(ws, T_BC, op.level).c, cur_sol<T>(lv));
             }
             return 1;
         }

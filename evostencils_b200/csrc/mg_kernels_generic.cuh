@@ -115,6 +115,24 @@ __device__ __forceinline__ T apply_row(const OperatorTable<T>* __restrict__ op, 
     return acc;
 }
 
+// (A u)(idx) for a scalar operator whose NE entries sit in registers (same entry order as apply_row: results are
+// bit-identical); the table itself lives in global memory, which costs NE dependent loads per node otherwise
+template <typename T, int NE>
+__device__ __forceinline__ T apply_cached(const int (&off)[NE], const T (&val)[NE], const T* __restrict__ u, long long idx) {
+    T acc = t_mul(val[0], u[idx + off[0]]);
+#pragma unroll
+    for (int k = 1; k < NE; ++k) acc = t_add(acc, t_mul(val[k], u[idx + off[k]]));
+    return acc;
+}
+template <typename T, int NE>
+__device__ __forceinline__ void load_row_entries(const OperatorTable<T>* __restrict__ op, int (&off)[NE], T (&val)[NE]) {
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+        off[k] = op->off[0][0][k];
+        val[k] = op->val[0][0][k];
+    }
+}
+
 // res = rhs - A sol
 template <typename T, int D, int F>
 __device__ __forceinline__ void residual_node(const Geom& g, const OperatorTable<T>* __restrict__ op,

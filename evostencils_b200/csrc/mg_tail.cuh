@@ -20,6 +20,7 @@
 // Coloured star sweeps run in place and visit only the nodes of their colour (a node of one
 // colour reads only nodes of the other), which halves the work of a Gauss-Seidel step.
 #pragma once
+#include <type_traits>
 #include "../../include/mgengine.h"
 #include "mg_coarse.cuh"
 
@@ -42,7 +43,8 @@ struct TailCmd {
     int inplace;                   // coloured star sweep in place (c == a): only nodes of `colour` are visited
     int wide;                      // executed by every CTA of the cluster (else by CTA 0 alone)
     int next_wide;                 // `wide` of the following command (1 after the last): selects the barrier
-    int pad_[2];
+    int bc;                        // SMOOTH_POINT (scalar complex, Robin): the sweep also writes the slaved columns x = 0, n-1
+    int pad_;
     double omega;
     const void* sm;                // SmootherTable<T>
     const void* w;                 // W tables
@@ -243,6 +245,54 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                 if constexpr (!LEAN) {
                     const SmootherTable<T>* sm = static_cast<const SmootherTable<T>*>(cmd.sm);
                     const T* w = static_cast<const T*>(cmd.w);
+                    if constexpr (F == 1) {
+                        // scalar operator with 5 / 9 entries (complex Helmholtz; real non-star stencils): entries and
+                        // weight in registers, the arithmetic of smooth_point_node for one slot.  bc: the slaved Robin
+                        // columns are written by the thread that updates their interior neighbour (the rows y = 0, n-1
+                        // are zero and are never written), which replaces the T_BC command after the sweep
+                        const int ne = op->n_entries[0][0];
+                        if (!is_variable<T, F>(op) && (ne == 5 || ne == 9) && D == 2) {
+                            const T w0 = w[(long long)sm->mask_index[1]];
+                            const T* __restrict__ src = A.p[0];
+                            const T* __restrict__ rhs = B.p[0];
+                            T* __restrict__ dst = C.p[0];
+                            const bool bc = cmd.bc != 0;
+                            const cplx bcf = prog.lv[cmd.lv].bc_factor;
+                            auto sweep = [&](auto ne_tag) {
+                                constexpr int NE = decltype(ne_tag)::value;
+                                int off[NE];
+                                T val[NE];
+                                load_row_entries<T, NE>(op, off, val);
+                                for (int i = first; i < nodes; i += stride) {
+                                    tail_decode<D>(i, g.n, x, y, z);
+                                    const long long idx = node_index<D>(g, x, y, z);
+                                    const bool active = is_interior<D>(g, x, y, z) &&
+                                                        (cmd.colour < 0 || ((x + y + z + g.z0) & 1) == cmd.colour);
+                                    if (!active) {
+                                        // a slaved column node is written by the thread of its interior neighbour
+                                        // when that one is updated in this pass
+                                        bool slaved = false;
+                                        if (bc && (x == 0 || x == g.n - 1) && y >= 1 && y <= g.n - 2) {
+                                            const int xn = x == 0 ? 1 : g.n - 2;
+                                            slaved = cmd.colour < 0 || ((xn + y + g.z0) & 1) == cmd.colour;
+                                        }
+                                        if (!slaved) dst[idx] = src[idx];
+                                        continue;
+                                    }
+                                    const T r = t_sub(rhs[idx], apply_cached<T, NE>(off, val, src, idx));
+                                    const T v = t_add(src[idx], t_mul(w0, r));
+                                    dst[idx] = v;
+                                    if constexpr (sizeof(T) == sizeof(cplx)) {
+                                        if (bc && x == 1) dst[idx - 1] = t_mul(v, bcf);
+                                        if (bc && x == g.n - 2) dst[idx + 1] = t_mul(v, bcf);
+                                    }
+                                }
+                            };
+                            if (ne == 5) sweep(std::integral_constant<int, 5>{});
+                            else sweep(std::integral_constant<int, 9>{});
+                            break;
+                        }
+                    }
                     for (int i = first; i < nodes; i += stride) {
                         tail_decode<D>(i, g.n, x, y, z);
                         smooth_point_node<T, D, F>(g, op, sm, w, A, B, C, cmd.colour, x, y, z);
@@ -278,11 +328,32 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                         break;
                     }
                 }
-                if constexpr (!LEAN)
+                if constexpr (!LEAN) {
+                    if constexpr (F == 1) {
+                        const int ne = op->n_entries[0][0];
+                        if (!is_variable<T, F>(op) && (ne == 5 || ne == 9)) {
+                            auto pass = [&](auto ne_tag) {
+                                constexpr int NE = decltype(ne_tag)::value;
+                                int off[NE];
+                                T val[NE];
+                                load_row_entries<T, NE>(op, off, val);
+                                for (int i = first; i < nodes; i += stride) {
+                                    tail_decode<D>(i, g.n, x, y, z);
+                                    if (!is_interior<D>(g, x, y, z)) continue;
+                                    const long long idx = node_index<D>(g, x, y, z);
+                                    C.p[0][idx] = t_sub(B.p[0][idx], apply_cached<T, NE>(off, val, A.p[0], idx));
+                                }
+                            };
+                            if (ne == 5) pass(std::integral_constant<int, 5>{});
+                            else pass(std::integral_constant<int, 9>{});
+                            break;
+                        }
+                    }
                     for (int i = first; i < nodes; i += stride) {
                         tail_decode<D>(i, g.n, x, y, z);
                         residual_node<T, D, F>(g, op, A, B, C, x, y, z);
                     }
+                }
                 break;
             case T_RESTRICT:
             case T_RESIDUAL_RESTRICT: {
@@ -317,6 +388,41 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                                     }
                             dst[node_index<D>(g, x, y, z)] = acc;
                         }
+                        break;
+                    }
+                }
+                if constexpr (!LEAN && F == 1 && D == 2) {
+                    const int ne = opf->n_entries[0][0];
+                    if (cmd.kind == T_RESIDUAL_RESTRICT && !is_variable<T, F>(opf) && (ne == 5 || ne == 9)) {
+                        // residual_restrict_node with the fine operator's entries in registers (same order of the
+                        // nine terms, same accumulation inside each)
+                        auto pass = [&](auto ne_tag) {
+                            constexpr int NE = decltype(ne_tag)::value;
+                            int off[NE];
+                            T val[NE];
+                            load_row_entries<T, NE>(opf, off, val);
+                            const double w1[3] = {0.25, 0.5, 0.25};
+                            for (int i = first; i < nodes; i += stride) {
+                                tail_decode<D>(i, g.n, x, y, z);
+                                if (!is_interior<D>(g, x, y, z)) continue;
+                                T acc = t_zero(T());
+                                bool first_term = true;
+#pragma unroll
+                                for (int oy = -1; oy <= 1; ++oy)
+#pragma unroll
+                                    for (int ox = -1; ox <= 1; ++ox) {
+                                        const double wgt = w1[ox + 1] * w1[oy + 1];
+                                        const long long fidx = node_index<D>(gf, 2 * x + ox, 2 * y + oy, 0);
+                                        const T r = t_sub(B.p[0][fidx], apply_cached<T, NE>(off, val, A.p[0], fidx));
+                                        const T term = t_scale(wgt, r);
+                                        acc = first_term ? term : t_add(acc, term);
+                                        first_term = false;
+                                    }
+                                C.p[0][node_index<D>(g, x, y, z)] = acc;
+                            }
+                        };
+                        if (ne == 5) pass(std::integral_constant<int, 5>{});
+                        else pass(std::integral_constant<int, 9>{});
                         break;
                     }
                 }

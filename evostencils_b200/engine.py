@@ -150,10 +150,11 @@ def load_library():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        raise EngineError(f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+    path = os.environ.get("MG_ENGINE_LIB", LIB_PATH)      # another build of the same sources (e.g. -DMG_TAIL_TIMING)
+    if not os.path.exists(path):
+        raise EngineError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                           "(the engine has no CPU fallback)", fatal=True)
-    _lib = bind(C.CDLL(LIB_PATH))
+    _lib = bind(C.CDLL(path))
     return _lib
 
 
