@@ -189,9 +189,9 @@ __device__ void coarse_cg_body(const Geom& g, const OperatorTable<T>* __restrict
             }
             iterate([&](int, long long idx) { return apply_cached<T, NE>(off, val, p, idx); });
         };
-        if (F == 1 && !is_variable<T, F>(op) && ne == 5) cached(std::integral_constant<int, 5>{});
-        else if (F == 1 && !is_variable<T, F>(op) && ne == 7) cached(std::integral_constant<int, 7>{});
-        else if (F == 1 && !is_variable<T, F>(op) && ne == 9) cached(std::integral_constant<int, 9>{});
+        // one cached instantiation per dimension (the star: 2 D + 1 entries): every copy of the loop is code the tail
+        // kernel has to fetch
+        if (F == 1 && !is_variable<T, F>(op) && ne == 2 * D + 1) cached(std::integral_constant<int, 2 * D + 1>{});
         else iterate([&](int f, long long idx) { return apply_row<T, F>(op, pf, f, idx - (long long)f * g.total); });
     }
     __syncthreads();

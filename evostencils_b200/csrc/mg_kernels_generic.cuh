@@ -80,8 +80,10 @@ __device__ __forceinline__ double vc_apply_d(const OperatorTable<double>* __rest
     }
 }
 
-__device__ __forceinline__ double vc_apply(const OperatorTable<double>* __restrict__ op, const double* __restrict__ u,
-                                           long long idx, double& diag) {
+// out of line: the call sits behind a run-time flag in every kernel that applies an operator (apply_row), and the
+// 4-6 inlined exp() bodies would otherwise be copied into all of them (code size is what bounds the tail kernel)
+__device__ __noinline__ double vc_apply(const OperatorTable<double>* __restrict__ op, const double* __restrict__ u,
+                                        long long idx, double& diag) {
     return op->vc_dim == 3 ? vc_apply_d<3>(op, u, idx, diag) : vc_apply_d<2>(op, u, idx, diag);
 }
 

@@ -44,7 +44,7 @@ struct TailCmd {
     int wide;                      // executed by every CTA of the cluster (else by CTA 0 alone)
     int next_wide;                 // `wide` of the following command (1 after the last): selects the barrier
     int bc;                        // SMOOTH_POINT (scalar complex, Robin): the sweep also writes the slaved columns x = 0, n-1
-    int pad_;
+    int scalar1;                   // SMOOTH_POINT: single-slot point smoother (the register-cached scalar path applies)
     double omega;
     const void* sm;                // SmootherTable<T>
     const void* w;                 // W tables
@@ -182,6 +182,10 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
         for (int k = threadIdx.x; k < n * TAIL_CMD_WORDS; k += TAIL_NT) s_cmd[k] = csrc[k];
     }
     __syncthreads();
+    // LEAN selects a small interpreter (instruction fetch is what a command costs: the full one is ~400 KB of code):
+    // real data: star sweeps / star residual + restriction / CG only; complex data: the register-cached scalar
+    // paths and BiCGStab only (the Helmholtz cycle)
+    constexpr bool LEAN_STAR = LEAN && sizeof(T) == sizeof(double);
     const TailHeader& prog = *reinterpret_cast<const TailHeader*>(s_head);
     const int n_cmds = prog.n_cmds;
     const int n_ctas = (int)cluster_size(), rank = (int)cluster_rank();
@@ -242,7 +246,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                         break;
                     }
                 }
-                if constexpr (!LEAN) {
+                if constexpr (!LEAN_STAR) {
                     const SmootherTable<T>* sm = static_cast<const SmootherTable<T>*>(cmd.sm);
                     const T* w = static_cast<const T*>(cmd.w);
                     if constexpr (F == 1) {
@@ -293,10 +297,11 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                             break;
                         }
                     }
-                    for (int i = first; i < nodes; i += stride) {
-                        tail_decode<D>(i, g.n, x, y, z);
-                        smooth_point_node<T, D, F>(g, op, sm, w, A, B, C, cmd.colour, x, y, z);
-                    }
+                    if constexpr (!LEAN)
+                        for (int i = first; i < nodes; i += stride) {
+                            tail_decode<D>(i, g.n, x, y, z);
+                            smooth_point_node<T, D, F>(g, op, sm, w, A, B, C, cmd.colour, x, y, z);
+                        }
                 }
                 break;
             }
@@ -328,7 +333,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                         break;
                     }
                 }
-                if constexpr (!LEAN) {
+                if constexpr (!LEAN_STAR) {
                     if constexpr (F == 1) {
                         const int ne = op->n_entries[0][0];
                         if (!is_variable<T, F>(op) && (ne == 5 || ne == 9)) {
@@ -349,10 +354,11 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                             break;
                         }
                     }
-                    for (int i = first; i < nodes; i += stride) {
-                        tail_decode<D>(i, g.n, x, y, z);
-                        residual_node<T, D, F>(g, op, A, B, C, x, y, z);
-                    }
+                    if constexpr (!LEAN)
+                        for (int i = first; i < nodes; i += stride) {
+                            tail_decode<D>(i, g.n, x, y, z);
+                            residual_node<T, D, F>(g, op, A, B, C, x, y, z);
+                        }
                 }
                 break;
             case T_RESTRICT:
@@ -391,7 +397,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                         break;
                     }
                 }
-                if constexpr (!LEAN && F == 1 && D == 2) {
+                if constexpr (!LEAN_STAR && F == 1 && D == 2) {
                     const int ne = opf->n_entries[0][0];
                     if (cmd.kind == T_RESIDUAL_RESTRICT && !is_variable<T, F>(opf) && (ne == 5 || ne == 9)) {
                         // residual_restrict_node with the fine operator's entries in registers (same order of the
@@ -491,15 +497,22 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
             }
             case T_CGS: {
                 T* work = prog.cgs_in_smem ? reinterpret_cast<T*>(smem_raw) : static_cast<T*>(prog.gwork);
-                if (LEAN || prog.cgs_kind == MG_CGS_CG)
+                if constexpr (LEAN_STAR) {
                     coarse_cg_body<T, D, F>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, s8);
-                else if constexpr (!LEAN)
+                } else if constexpr (LEAN) {
                     coarse_bicgstab_body<T, D, F>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, prog.robin,
                                                   prog.lv[cmd.lv].bc_factor, s8);
+                } else {
+                    if (prog.cgs_kind == MG_CGS_CG)
+                        coarse_cg_body<T, D, F>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, s8);
+                    else
+                        coarse_bicgstab_body<T, D, F>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, prog.robin,
+                                                      prog.lv[cmd.lv].bc_factor, s8);
+                }
                 break;
             }
             case T_BC:
-                if constexpr (!LEAN)
+                if constexpr (!LEAN_STAR)
                     for (int f = 0; f < F; ++f) tail_bc(g, C.p[f], prog.lv[cmd.lv].bc_factor);
                 break;
             default: break;
