@@ -551,7 +551,7 @@ int tail_flush(mg_workspace* ws) {
     }
     if (F == 1 && D == 2 && sizeof(T) == sizeof(cplx) && ws->cgs_kind == MG_CGS_BICGSTAB && ws->tail_lean && !ws->vc_kind) {
         // complex scalar cycle (Helmholtz): the lean interpreter holds the register-cached scalar paths, which need a
-        // 5- or 9-entry operator on every level a command touches and single-slot point smoothers
+        // 5-entry operator on every level a command touches and single-slot point smoothers
         lean = true;
         for (int i = 0; i < p.h.n_cmds && lean; ++i) {
             const TailCmd& c = p.cmd[i];
@@ -559,8 +559,8 @@ int tail_flush(mg_workspace* ws) {
             const int top = (c.kind == T_RESIDUAL_RESTRICT) ? level + 1 : level;
             const int ne = ws->has_level(top) ? ws->L(top).hop.n_entries[0][0] : 0;
             switch (c.kind) {
-                case T_SMOOTH_POINT: lean = c.scalar1 != 0 && (ne == 5 || ne == 9); break;
-                case T_RESIDUAL: case T_RESIDUAL_RESTRICT: lean = ne == 5 || ne == 9; break;
+                case T_SMOOTH_POINT: lean = c.scalar1 != 0 && ne == 5; break;
+                case T_RESIDUAL: case T_RESIDUAL_RESTRICT: lean = ne == 5; break;
                 case T_RESTRICT: case T_ZERO: case T_PROLONG: case T_CGS: case T_BC: break;
                 default: lean = false;
             }
@@ -656,7 +656,7 @@ int tail_append(mg_workspace* ws, const mg_op& op) {
                 // Robin columns: written by the sweep itself where the kernel's scalar path applies (mg_tail.cuh),
                 // else by a boundary command after it
                 const int ne00 = lv.hop.n_entries[0][0];
-                const bool fused_bc = robin && F == 1 && D == 2 && sm.point && sm.m == 1 && !ws->vc_kind && (ne00 == 5 || ne00 == 9);
+                const bool fused_bc = robin && F == 1 && D == 2 && sm.point && sm.m == 1 && !ws->vc_kind && ne00 == 5;
                 cmd.bc = fused_bc ? 1 : 0;
                 cmd.scalar1 = (sm.point && sm.m == 1) ? 1 : 0;
                 if (robin && !fused_bc) tail_set<T>(tail_new(ws, T_BC, op.level).c, cur_sol<T>(lv));

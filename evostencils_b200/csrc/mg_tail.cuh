@@ -185,7 +185,10 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
     // LEAN selects a small interpreter (instruction fetch is what a command costs: the full one is ~400 KB of code):
     // real data: star sweeps / star residual + restriction / CG only; complex data: the register-cached scalar
     // paths and BiCGStab only (the Helmholtz cycle)
-    constexpr bool LEAN_STAR = LEAN && sizeof(T) == sizeof(double);
+    constexpr bool LEAN_STAR = LEAN && sizeof(T) == sizeof(double) && F == 1;
+    // (a lean interpreter for two-field real cycles -- generic node functions + CG only -- was measured: no gain for the
+    // elasticity configuration, 5.87 against 5.79 ms per solve, so those cycles use the full one)
+    constexpr bool GENERIC = !LEAN;
     const TailHeader& prog = *reinterpret_cast<const TailHeader*>(s_head);
     const int n_cmds = prog.n_cmds;
     const int n_ctas = (int)cluster_size(), rank = (int)cluster_rank();
@@ -250,12 +253,12 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                     const SmootherTable<T>* sm = static_cast<const SmootherTable<T>*>(cmd.sm);
                     const T* w = static_cast<const T*>(cmd.w);
                     if constexpr (F == 1) {
-                        // scalar operator with 5 / 9 entries (complex Helmholtz; real non-star stencils): entries and
+                        // scalar operator with 5 entries (the complex Helmholtz star): entries and
                         // weight in registers, the arithmetic of smooth_point_node for one slot.  bc: the slaved Robin
                         // columns are written by the thread that updates their interior neighbour (the rows y = 0, n-1
                         // are zero and are never written), which replaces the T_BC command after the sweep
                         const int ne = op->n_entries[0][0];
-                        if (!is_variable<T, F>(op) && (ne == 5 || ne == 9) && D == 2) {
+                        if (!is_variable<T, F>(op) && ne == 5 && D == 2) {
                             const T w0 = w[(long long)sm->mask_index[1]];
                             const T* __restrict__ src = A.p[0];
                             const T* __restrict__ rhs = B.p[0];
@@ -292,12 +295,11 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                                     }
                                 }
                             };
-                            if (ne == 5) sweep(std::integral_constant<int, 5>{});
-                            else sweep(std::integral_constant<int, 9>{});
+                            sweep(std::integral_constant<int, 5>{});
                             break;
                         }
                     }
-                    if constexpr (!LEAN)
+                    if constexpr (GENERIC)
                         for (int i = first; i < nodes; i += stride) {
                             tail_decode<D>(i, g.n, x, y, z);
                             smooth_point_node<T, D, F>(g, op, sm, w, A, B, C, cmd.colour, x, y, z);
@@ -336,7 +338,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                 if constexpr (!LEAN_STAR) {
                     if constexpr (F == 1) {
                         const int ne = op->n_entries[0][0];
-                        if (!is_variable<T, F>(op) && (ne == 5 || ne == 9)) {
+                        if (!is_variable<T, F>(op) && ne == 5) {
                             auto pass = [&](auto ne_tag) {
                                 constexpr int NE = decltype(ne_tag)::value;
                                 int off[NE];
@@ -349,12 +351,11 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                                     C.p[0][idx] = t_sub(B.p[0][idx], apply_cached<T, NE>(off, val, A.p[0], idx));
                                 }
                             };
-                            if (ne == 5) pass(std::integral_constant<int, 5>{});
-                            else pass(std::integral_constant<int, 9>{});
+                            pass(std::integral_constant<int, 5>{});
                             break;
                         }
                     }
-                    if constexpr (!LEAN)
+                    if constexpr (GENERIC)
                         for (int i = first; i < nodes; i += stride) {
                             tail_decode<D>(i, g.n, x, y, z);
                             residual_node<T, D, F>(g, op, A, B, C, x, y, z);
@@ -399,7 +400,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                 }
                 if constexpr (!LEAN_STAR && F == 1 && D == 2) {
                     const int ne = opf->n_entries[0][0];
-                    if (cmd.kind == T_RESIDUAL_RESTRICT && !is_variable<T, F>(opf) && (ne == 5 || ne == 9)) {
+                    if (cmd.kind == T_RESIDUAL_RESTRICT && !is_variable<T, F>(opf) && ne == 5) {
                         // residual_restrict_node with the fine operator's entries in registers (same order of the
                         // nine terms, same accumulation inside each)
                         auto pass = [&](auto ne_tag) {
@@ -427,15 +428,14 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                                 C.p[0][node_index<D>(g, x, y, z)] = acc;
                             }
                         };
-                        if (ne == 5) pass(std::integral_constant<int, 5>{});
-                        else pass(std::integral_constant<int, 9>{});
+                        pass(std::integral_constant<int, 5>{});
                         break;
                     }
                 }
                 for (int i = first; i < nodes; i += stride) {
                     tail_decode<D>(i, g.n, x, y, z);
                     if (cmd.kind == T_RESTRICT) restrict_node<T, D, F>(g, gf, A, C, x, y, z);
-                    else if constexpr (!LEAN) residual_restrict_node<T, D, F>(g, gf, opf, A, B, C, x, y, z);
+                    else if constexpr (GENERIC) residual_restrict_node<T, D, F>(g, gf, opf, A, B, C, x, y, z);
                 }
                 break;
             }
