@@ -50,39 +50,57 @@ __device__ __forceinline__ FieldSet<T> as_fields(T* base, const Geom& g) {
 // coarsest levels a thread owns at most one unknown, so no iteration pays the index arithmetic).
 template <int D>
 struct ElemCache {
-    static constexpr int K = 4;              // elements of a thread whose index is decoded once (33^2: all four)
-    int f[K];
-    int idx[K];                              // coarse levels are far below 2^31 elements
-    int count;
-    __device__ ElemCache(const Geom& g, const InteriorIter<D>& it) : count(0) {
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            f[k] = 0;
-            idx[k] = 0;
-            const int e = krylov_tid() + 256 * k;
-            if (krylov_tid() < 256 && e < it.total) {
-                long long i;
-                it.decode(e, g, f[k], i);
-                idx[k] = (int)i;
-                count = k + 1;
-            }
+    // The first element of a thread is decoded once; for a single field the following ones (e + 256, e + 512, ...)
+    // are reached by stepping the node coordinates -- no integer division per element and loop, and no arrays of cached
+    // indices (four of them cost the tail kernel, 512 threads, its registers: 60 -> 128 + spills).
+    int f0, x, y, z, dx, dy, dz, m;
+    long long idx0;
+    bool has0, single;
+    __device__ ElemCache(const Geom& g, const InteriorIter<D>& it)
+        : f0(0), x(0), y(0), z(0), dx(0), dy(0), dz(0), m(it.m), idx0(0), has0(krylov_tid() < it.total),
+          single(it.total == it.per_field) {
+        if (has0) {
+            it.decode(krylov_tid(), g, f0, idx0);
+            const int q = krylov_tid() - f0 * it.per_field;
+            x = q % m;
+            const int t = q / m;
+            y = t % m;
+            z = (D == 3) ? t / m : 0;
         }
+        dx = 256 % m;
+        const int t = 256 / m;
+        dy = t % m;
+        dz = (D == 3) ? t / m : 0;
     }
     template <class Fn>
     __device__ __forceinline__ void each(const Geom& g, const InteriorIter<D>& it, Fn fn) const {
+        if (!has0) return;
+        fn(f0, idx0);
+        if (single) {
+            // three elements per round, indices first: their loads overlap (33^2: a thread owns at most four)
+            int xx = x, yy = y, zz = z;
+            for (int e = krylov_tid() + 256; e < it.total; e += 768) {
+                int id[3];
 #pragma unroll
-        for (int k = 0; k < K; ++k)
-            if (k < count) fn(f[k], (long long)idx[k]);
-        if (count < K) return;
-        for (int e = krylov_tid() + 256 * K; e < it.total; e += 256) {
+                for (int k = 0; k < 3; ++k) {
+                    xx += dx; yy += dy; zz += dz;
+                    if (xx >= m) { xx -= m; ++yy; }
+                    if (yy >= m) { yy -= m; ++zz; }
+                    id[k] = (int)node_index<D>(g, xx + 1, yy + 1, (D == 3) ? zz + 1 : 0);
+                }
+#pragma unroll
+                for (int k = 0; k < 3; ++k)
+                    if (e + 256 * k < it.total) fn(0, (long long)id[k]);
+            }
+            return;
+        }
+        for (int e = krylov_tid() + 256; e < it.total; e += 256) {
             int ff; long long i;
             it.decode(e, g, ff, i);
             fn(ff, i);
         }
     }
 };
-
-
 
 template <typename T, int D>
 __device__ T coarse_dot(const T* a, const T* b, const Geom& g, const InteriorIter<D>& it, T* s8) {
@@ -133,7 +151,10 @@ __device__ inline bool t_is_zero(cplx a) { return a.re == 0.0 && a.im == 0.0; }
 
 // ---- CG --------------------------------------------------------------------------------------------
 // work: 4 vectors of F * g.total elements (x, r, p, ap), shared or global.
-template <typename T, int D, int F>
+// CACHED_ONLY: the caller guarantees a scalar (2 D + 1)-entry constant operator (the lean tail interpreter): the generic
+// loop -- and with it apply_row and its out-of-line variable-coefficient call, whose ABI costs the whole kernel its
+// register allocation -- is not instantiated
+template <typename T, int D, int F, bool CACHED_ONLY = false>
 __device__ void coarse_cg_body(const Geom& g, const OperatorTable<T>* __restrict__ op, const FieldSet<T>& sol,
                                const FieldSet<T>& rhs, T* work, int max_its, double reduction, T* s8) {
     const long long vec = (long long)F * g.total;
@@ -191,8 +212,12 @@ __device__ void coarse_cg_body(const Geom& g, const OperatorTable<T>* __restrict
         };
         // one cached instantiation per dimension (the star: 2 D + 1 entries): every copy of the loop is code the tail
         // kernel has to fetch
-        if (F == 1 && !is_variable<T, F>(op) && ne == 2 * D + 1) cached(std::integral_constant<int, 2 * D + 1>{});
-        else iterate([&](int f, long long idx) { return apply_row<T, F>(op, pf, f, idx - (long long)f * g.total); });
+        if constexpr (CACHED_ONLY) {
+            cached(std::integral_constant<int, 2 * D + 1>{});
+        } else {
+            if (F == 1 && !is_variable<T, F>(op) && ne == 2 * D + 1) cached(std::integral_constant<int, 2 * D + 1>{});
+            else iterate([&](int f, long long idx) { return apply_row<T, F>(op, pf, f, idx - (long long)f * g.total); });
+        }
     }
     __syncthreads();
     // solution field: whole array (boundary = 0 for the error equation)

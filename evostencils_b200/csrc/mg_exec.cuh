@@ -545,7 +545,8 @@ int tail_flush(mg_workspace* ws) {
         const TailCmd& c = p.cmd[i];
         switch (c.kind) {
             case T_SMOOTH_POINT: case T_RESIDUAL: case T_RESIDUAL_RESTRICT: lean = c.star != 0; break;
-            case T_RESTRICT: case T_ZERO: case T_PROLONG: case T_CGS: break;
+            case T_CGS: lean = ws->use_fast && ws->L(ws->min_level).star; break;       // the lean CG holds the star in registers
+            case T_RESTRICT: case T_ZERO: case T_PROLONG: break;
             default: lean = false;
         }
     }

@@ -498,7 +498,7 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
             case T_CGS: {
                 T* work = prog.cgs_in_smem ? reinterpret_cast<T*>(smem_raw) : static_cast<T*>(prog.gwork);
                 if constexpr (LEAN_STAR) {
-                    coarse_cg_body<T, D, F>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, s8);
+                    coarse_cg_body<T, D, F, true>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, s8);
                 } else if constexpr (LEAN) {
                     coarse_bicgstab_body<T, D, F>(g, op, C, B, work, prog.cgs_max_its, prog.cgs_reduction, prog.robin,
                                                   prog.lv[cmd.lv].bc_factor, s8);
