@@ -34,8 +34,11 @@ __device__ __forceinline__ double vc_node(const VC2D& s, double cS, double cW, d
     return a;
 }
 
+#ifndef MG_VC_MIN_CTAS
+#define MG_VC_MIN_CTAS 5
+#endif
 template <int MODE, int NT, int R>
-__global__ void __launch_bounds__(NT) k_vcstar2d(Geom g, VC2D s, const double* u, const double* __restrict__ f,
+__global__ void __launch_bounds__(NT, MG_VC_MIN_CTAS) k_vcstar2d(Geom g, VC2D s, const double* u, const double* __restrict__ f,
                                                   double* out, double w, int colour, double* __restrict__ partial) {
     pdl_sync();
     const int lane = threadIdx.x & 31;
