@@ -5,7 +5,7 @@
 Step  = the first N x `--individuals-per-gpu` individuals of the stored 256-individual population
         (weak scaling; 32 per GPU = the whole population on 8 GPUs) are evaluated once through
         B200ProgramGenerator.generate_and_evaluate; ranks take individuals from a shared counter and
-        evaluate `--streams` (default 2) of them at a time, each on its own workspace and CUDA stream.
+        evaluate `--streams` (default 3) of them at a time, each on its own workspace and CUDA stream.
         `--strong`: every step evaluates all 256 individuals whatever N is.
 value = fine-grid DoF updates per second = sum over individuals of (interior DoF x multigrid
         cycles executed) / step time, whole job, inputs resident in HBM.
