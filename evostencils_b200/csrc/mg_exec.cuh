@@ -646,6 +646,19 @@ int tail_append(mg_workspace* ws, const mg_op& op) {
                     dst = src;
                     flip[0] = false;
                 }
+                // complex scalar 5-point star (Helmholtz): the colour pass of the register-cached path runs in place
+                // too -- a node of one colour reads only nodes of the other
+                bool star_offsets = F == 1 && D == 2 && lv.hop.n_entries[0][0] == 5;
+                {
+                    static const int want2[5][2] = {{0, -1}, {-1, 0}, {0, 0}, {1, 0}, {0, 1}};
+                    for (int k = 0; k < 5 && star_offsets; ++k)
+                        star_offsets = lv.hop.offs[0][0][k][0] == want2[k][0] && lv.hop.offs[0][0][k][1] == want2[k][1];
+                }
+                if (sizeof(T) == sizeof(cplx) && star_offsets && sm.point && sm.m == 1 && cmd.colour >= 0 && !ws->vc_kind) {
+                    cmd.inplace = 1;
+                    dst = src;
+                    flip[0] = false;
+                }
                 cmd.omega = sm.w00;
                 cmd.sm = sm.d_table;
                 cmd.w = sm.d_w;

@@ -260,9 +260,9 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                         const int ne = op->n_entries[0][0];
                         if (!is_variable<T, F>(op) && ne == 5 && D == 2) {
                             const T w0 = w[(long long)sm->mask_index[1]];
-                            const T* __restrict__ src = A.p[0];
+                            const T* src = A.p[0];                      // == dst for an in-place colour pass
                             const T* __restrict__ rhs = B.p[0];
-                            T* __restrict__ dst = C.p[0];
+                            T* dst = C.p[0];
                             const bool bc = cmd.bc != 0;
                             const cplx bcf = prog.lv[cmd.lv].bc_factor;
                             auto sweep = [&](auto ne_tag) {
@@ -270,6 +270,26 @@ __global__ void __launch_bounds__(TAIL_NT) k_tail(const TailProgram* __restrict_
                                 int off[NE];
                                 T val[NE];
                                 load_row_entries<T, NE>(op, off, val);
+                                if (cmd.inplace) {
+                                    // colour pass in place (dst == src, set by the host for the 5-point star only): the
+                                    // nodes of the colour alone, decoded by shifts (n - 1 = 2^L) -- half the nodes of the
+                                    // out-of-place pass, no copy of the others
+                                    const int half = (g.n - 1) >> 1, sh = 31 - __clz(half);
+                                    for (int i = first; i < (g.n - 2) * half; i += stride) {
+                                        y = 1 + (i >> sh);
+                                        x = 1 + 2 * (i & (half - 1)) + ((1 + y + g.z0 + cmd.colour) & 1);
+                                        if (x > g.n - 2) continue;
+                                        const long long idx = node_index<D>(g, x, y, 0);
+                                        const T r = t_sub(rhs[idx], apply_cached<T, NE>(off, val, dst, idx));
+                                        const T v = t_add(dst[idx], t_mul(w0, r));
+                                        dst[idx] = v;
+                                        if constexpr (sizeof(T) == sizeof(cplx)) {
+                                            if (bc && x == 1) dst[idx - 1] = t_mul(v, bcf);
+                                            if (bc && x == g.n - 2) dst[idx + 1] = t_mul(v, bcf);
+                                        }
+                                    }
+                                    return;
+                                }
                                 for (int i = first; i < nodes; i += stride) {
                                     tail_decode<D>(i, g.n, x, y, z);
                                     const long long idx = node_index<D>(g, x, y, z);
